@@ -1,0 +1,67 @@
+# Build of the flextree-b200 native libraries and tools.
+#   make host     -> build/libflextree_host.so  (planner + CPU world; g++ only, runs anywhere)
+#   make cuda     -> allreduce-over-mpi_b200/lib/libflextree.so (everything; nvcc, sm_100a)
+#   make tools    -> build/ft_plan, build/ft_bench, build/nccl_bench
+# Capability parity with the reference build files: allreduce_over_mpi/CMakeLists.txt (flags, version
+# stamping), allreduce_over_mpi/Makefile (build/clean), cost_model/CMakeLists.txt.
+NVCC ?= nvcc
+# The image exports CXX=/opt/gcc/bin/g++, a wrapper that links libstdc++ statically; a second copy of
+# libstdc++ inside a dlopen()ed library crashes once numpy/torch have loaded the system one.
+CXX := $(shell test -x /usr/bin/g++ && echo /usr/bin/g++ || echo g++)
+PKG := allreduce-over-mpi_b200
+LIBDIR := $(PKG)/lib
+B := build
+ARCH := -gencode arch=compute_100a,code=sm_100a
+
+GIT_DESCRIBE := $(shell git describe --always --dirty 2>/dev/null || echo unknown)
+GIT_DATE := $(shell git log -1 --format=%cd --date=short 2>/dev/null || echo unknown)
+GIT_HASH := $(shell git rev-parse --short HEAD 2>/dev/null || echo unknown)
+VERDEFS := -DFT_GIT_DESCRIBE='"$(GIT_DESCRIBE)"' -DFT_GIT_DATE='"$(GIT_DATE)"' -DFT_GIT_HASH='"$(GIT_HASH)"'
+
+CXXFLAGS := -std=c++17 -O2 -fPIC -Wall -Wextra -Wno-unknown-pragmas -Wno-maybe-uninitialized -Wno-uninitialized -Iinclude $(VERDEFS)
+NVFLAGS := -std=c++17 -O3 $(ARCH) -lineinfo -Xcompiler -fPIC -Xcompiler -Wall -Iinclude $(VERDEFS) --expt-relaxed-constexpr
+
+PLANNER_SRC := csrc/planner/factorize.cc csrc/planner/cost_model.cc csrc/planner/schedule.cc csrc/planner/c_api.cc
+HOST_SRC := csrc/host/host_world.cc csrc/host/host_run_all.cc $(wildcard csrc/host/host_run_g*.cc)
+CUDA_SRC := $(wildcard csrc/kernels/*.cu) $(wildcard csrc/runtime/*.cu)
+RT_CC_SRC := $(wildcard csrc/runtime/*.cc)
+
+PLANNER_OBJ := $(PLANNER_SRC:%.cc=$(B)/%.o)
+HOST_OBJ := $(HOST_SRC:%.cc=$(B)/%.o)
+CUDA_OBJ := $(CUDA_SRC:%.cu=$(B)/%.cu.o)
+RT_CC_OBJ := $(RT_CC_SRC:%.cc=$(B)/%.o)
+
+.PHONY: all host cuda tools clean
+all: host cuda tools
+host: $(B)/libflextree_host.so
+cuda: $(LIBDIR)/libflextree.so
+tools: $(B)/ft_plan $(B)/ft_bench
+
+$(B)/%.o: %.cc
+	@mkdir -p $(dir $@)
+	$(CXX) $(CXXFLAGS) -MMD -MP -c $< -o $@
+
+$(B)/%.cu.o: %.cu
+	@mkdir -p $(dir $@)
+	$(NVCC) $(NVFLAGS) -MMD -MP -c $< -o $@
+
+$(B)/libflextree_host.so: $(PLANNER_OBJ) $(HOST_OBJ)
+	$(CXX) -shared -o $@ $^ -lpthread
+
+$(LIBDIR)/libflextree.so: $(PLANNER_OBJ) $(HOST_OBJ) $(RT_CC_OBJ) $(CUDA_OBJ)
+	@mkdir -p $(LIBDIR)
+	$(NVCC) $(ARCH) -shared -o $@ $^ -lpthread -ldl
+
+$(B)/ft_plan: csrc/tools/ft_plan.cc $(PLANNER_OBJ)
+	$(CXX) $(CXXFLAGS) -o $@ $^
+
+$(B)/ft_bench: csrc/tools/ft_bench.cu $(LIBDIR)/libflextree.so
+	$(NVCC) $(NVFLAGS) -o $@ $< -L$(LIBDIR) -lflextree -Xlinker -rpath -Xlinker '$$ORIGIN/../$(LIBDIR)'
+
+$(B)/nccl_bench: csrc/tools/nccl_bench.cu
+	$(NVCC) $(NVFLAGS) -o $@ $< -lnccl
+
+clean:
+	rm -rf $(B) $(LIBDIR)/*.so
+
+-include $(PLANNER_OBJ:.o=.d) $(HOST_OBJ:.o=.d) $(CUDA_OBJ:.o=.d) $(RT_CC_OBJ:.o=.d)

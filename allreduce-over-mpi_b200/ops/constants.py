@@ -1,0 +1,37 @@
+"""Enum values of the C ABI (include/flextree.h) and dtype tables."""
+import numpy as np
+
+UINT8, INT8, UINT16, INT16, INT32, INT64, FLOAT, DOUBLE, BOOL, LONG_LONG, UINT32, UINT64, HALF, BFLOAT16 = range(14)
+SUM, BAND, MAX, MIN, BOR = range(5)
+ALGO_AUTO, ALGO_ONESHOT, ALGO_STAGES, ALGO_NVLS, ALGO_RING = range(5)
+MODE_STAGING, MODE_REGISTERED = 0, 1
+
+OPS = {"sum": SUM, "band": BAND, "max": MAX, "min": MIN, "bor": BOR}
+ALGOS = {"auto": ALGO_AUTO, "oneshot": ALGO_ONESHOT, "stages": ALGO_STAGES, "nvls": ALGO_NVLS, "ring": ALGO_RING}
+ALGO_NAMES = {v: k for k, v in ALGOS.items()}
+
+DTYPE_SIZE = {UINT8: 1, INT8: 1, BOOL: 1, UINT16: 2, INT16: 2, HALF: 2, BFLOAT16: 2, INT32: 4, UINT32: 4,
+              FLOAT: 4, INT64: 8, UINT64: 8, DOUBLE: 8, LONG_LONG: 8}
+
+NUMPY_DTYPE = {
+    np.dtype(np.uint8): UINT8, np.dtype(np.int8): INT8, np.dtype(np.uint16): UINT16,
+    np.dtype(np.int16): INT16, np.dtype(np.int32): INT32, np.dtype(np.int64): INT64,
+    np.dtype(np.float32): FLOAT, np.dtype(np.float64): DOUBLE, np.dtype(np.bool_): BOOL,
+    np.dtype(np.uint32): UINT32, np.dtype(np.uint64): UINT64, np.dtype(np.float16): HALF,
+}
+
+
+def torch_dtype_code(dt):
+    import torch
+    table = {torch.uint8: UINT8, torch.int8: INT8, torch.int16: INT16, torch.int32: INT32,
+             torch.int64: INT64, torch.float32: FLOAT, torch.float64: DOUBLE, torch.bool: BOOL,
+             torch.float16: HALF, torch.bfloat16: BFLOAT16}
+    for name, code in (("uint16", UINT16), ("uint32", UINT32), ("uint64", UINT64)):
+        if hasattr(torch, name):
+            table[getattr(torch, name)] = code
+    if dt not in table:
+        raise TypeError(f"flextree: unsupported dtype {dt}")
+    return table[dt]
+
+
+__all__ = [n for n in dir() if n.isupper()] + ["torch_dtype_code"]

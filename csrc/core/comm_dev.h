@@ -1,0 +1,79 @@
+// Device-visible communicator state, flag-pad layout and kernel argument blocks.
+//
+// What this replaces in the reference: MPI_Isend/Irecv request arrays + MPI_Waitall + one
+// MPI_Barrier per stage (allreduce_over_mpi/mpi_mod.hpp:969-972, :1003, :1027-1028, :1058-1059) and
+// the grow-only host staging buffer (:932-950). Here a stage boundary is a 64-bit flag per
+// (phase, CTA, source rank) that the producer pushes into the consumer's pad with a system-scope
+// release store; flags carry a device-resident epoch so that nothing is ever reset from the host
+// (CUDA-graph replays just keep counting).
+#pragma once
+#include <stddef.h>
+#include <stdint.h>
+
+#include "plan.h"
+
+namespace ft {
+
+// Flag phases. RS stage k uses PH_RS0 + k, AG stage k uses PH_AG0 + k.
+enum Phase {
+  PH_IN = 0,                          // "my window holds this tile's input"
+  PH_RS0 = 1,
+  PH_AG0 = 1 + FT_MAX_STAGES,
+  PH_END = 1 + 2 * FT_MAX_STAGES,     // "I have finished reading everybody's window" (registered mode)
+  PH_COUNT = 2 + 2 * FT_MAX_STAGES
+};
+
+FT_HD size_t pad_slot(int phase, int cta, int src) {
+  return ((size_t)phase * FT_MAX_CTAS + (size_t)cta) * FT_MAX_RANKS + (size_t)src;
+}
+static const size_t FT_PAD_WORDS = (size_t)PH_COUNT * FT_MAX_CTAS * FT_MAX_RANKS;
+static const size_t FT_PAD_BYTES = FT_PAD_WORDS * sizeof(uint64_t);
+
+// Flag value for "tile j of the call with this epoch is done": strictly increasing across calls.
+static const int FT_EPOCH_SHIFT = 20;  // up to 2^20 - 1 tiles per CTA per call
+FT_HD uint64_t epoch_base(uint64_t epoch) { return (epoch + 1) << FT_EPOCH_SHIFT; }
+
+// Error word layout (nonzero == failed): code | phase << 8 | src << 16 | rank << 24
+enum ErrCode { ERR_NONE = 0, ERR_TIMEOUT = 1, ERR_PEER = 2 };
+
+// One per (logical) rank, resident in that rank's device memory.
+struct CommDev {
+  int rank;
+  int nranks;
+  uint64_t* pad[FT_MAX_RANKS];  // flag pad of every rank as mapped into this rank's address space
+  char* ll[FT_MAX_RANKS];       // LL (one-shot) receive buffers of every rank
+  uint64_t* epoch;              // local: number of collectives completed on this communicator
+  unsigned* done;               // local: CTAs of the current kernel that have finished
+  unsigned* err;                // local: sticky error word
+  size_t ll_bytes;              // capacity of one parity half of an LL buffer
+};
+
+enum Mode {
+  MODE_STAGING = 0,     // user buffers are private: copy-in to the symmetric window, parity double-buffer
+  MODE_REGISTERED = 1   // the user buffer IS the symmetric window (in place): zero copy + exit barrier
+};
+
+// Per logical rank, per call.
+struct RankCall {
+  const CommDev* comm;
+  const void* send;   // user input (local memory of this rank)
+  void* recv;         // user output
+  char* const* win;   // device table [nranks]: base of the window segment of every rank
+  char* mc;           // multicast alias of the window segment base (NVLS), or null
+};
+
+struct StagedArgs {
+  Plan plan;
+  Layout lay;
+  int nlocal;  // logical ranks served by this launch (1 in multi-process / multi-device mode)
+  int ctas;    // CTAs per logical rank
+  int mode;    // Mode
+  int apply_scale;
+  double scale;
+  long long win_off0;    // window byte offset inside the segment ...
+  long long win_stride;  // ... plus (epoch & 1) * win_stride (0 in registered mode)
+  unsigned long long timeout_ns;  // 0 = spin forever
+  RankCall rc[FT_MAX_LOCAL];
+};
+
+}  // namespace ft

@@ -1,0 +1,748 @@
+// The generalized multi-stage reduce-scatter + all-gather, written once for two back ends:
+//   * CudaBE (kernels/backend.cuh): one CTA of the sm_100a kernel, peers are NVLink-mapped pointers
+//   * CpuBE  (host/cpu_backend.h) : one std::thread per "CTA"; used by the CPU tests to check the
+//                                   index math, the hazard analysis and the flag protocol without a GPU
+//
+// Capability parity: FlexTree::tree_allreduce (allreduce_over_mpi/mpi_mod.hpp:953-1111) -
+//   reduce-scatter loop :988-1029, all-gather loop :1050-1060, k-way reduce handle_reduce :769-878.
+// Design differences (deliberate):
+//   * receiver-PULL over peer-mapped memory instead of send/recv messages; the k-way reduction is
+//     done in registers in the same loop that loads the peer data (no staging copy, no second pass)
+//   * the message is cut into tiles; tile t is a self-contained allreduce over chunk t of every block,
+//     always owned by CTA (t mod G) on every rank, so stages pipeline tile by tile and the only
+//     cross-rank dependencies are between same-index CTAs (deadlock-free while grids are resident)
+//   * stage fences are per-(phase, CTA, source) release/acquire flags instead of world barriers
+//   * summation order inside a stage is "own value first, then peers in ascending rank order", the
+//     same order handle_reduce uses (:787, :809-817), so fp32 results match the reference bit for bit
+//     whenever the block split is the same.
+//
+// Hazard analysis for the in-place window W (r = this rank, gn = g_{k+1}):
+//   RS stage k : r writes W_r[b == r (mod gn)], peers p read W_r[b == p (mod gn)], p != r  -> disjoint
+//   AG stage k : r writes W_r[b == p (mod gn)] only after p's flag for a *later* phase of the same
+//                tile, which p's CTA releases after its own RS-stage-k reads of W_r         -> ordered
+//   next call  : staging mode alternates two windows by epoch parity (any allreduce makes every rank
+//                depend on every rank having *started* the call, hence finished the previous one);
+//                registered mode ends with an exit barrier instead.
+#pragma once
+#include "comm_dev.h"
+#include "types.h"
+
+namespace ft {
+
+#if defined(__CUDACC__)
+#define FT_DEV __device__ __forceinline__
+#else
+#define FT_DEV inline
+#endif
+
+template <typename X, typename Y> struct SameType { static constexpr bool value = false; };
+template <typename X> struct SameType<X, X> { static constexpr bool value = true; };
+
+template <class BE, typename T, typename IO, class Op, int VE>
+struct StagedCta {
+  using EL = Elem<T>;
+  using EU = Elem<IO>;
+  using A = typename EL::acc;
+  using PackT = Pack<T, VE>;
+  using PackIO = Pack<IO, VE>;
+  static constexpr bool kRawIO = SameType<T, IO>::value;
+
+  BE& be;
+  const StagedArgs& a;
+  const RankCall& rc;
+  const CommDev& cd;
+  const int r;       // my rank
+  const int cta;     // my CTA index within the rank
+  uint64_t E;        // flag base of this call
+  long long woff;    // byte offset of the window inside the segment
+  int* abort_flag;
+
+  FT_DEV StagedCta(BE& be_, const StagedArgs& a_, const RankCall& rc_, int cta_)
+      : be(be_), a(a_), rc(rc_), cd(*rc_.comm), r(rc_.comm->rank), cta(cta_) {
+    uint64_t epoch = be.load_epoch(cd.epoch);
+    E = epoch_base(epoch);
+    woff = a.win_off0 + (long long)(epoch & 1) * a.win_stride;
+    abort_flag = be.abort_ptr();
+  }
+
+  // ---- flags --------------------------------------------------------------------------------------
+  FT_DEV void spin(const uint64_t* slot, uint64_t target, int phase, int src) {
+    if (*abort_flag) return;
+    uint64_t t0 = 0;
+    unsigned it = 0;
+    while (be.flag_ld(slot) < target) {
+      if (((++it) & 0x3ff) == 0) {
+        if (be.err_ld(cd.err)) { *abort_flag = 1; return; }
+        if (a.timeout_ns) {
+          uint64_t now = be.now_ns();
+          if (!t0) t0 = now;
+          else if (now - t0 > a.timeout_ns) {
+            be.err_set(cd.err, (unsigned)ERR_TIMEOUT | ((unsigned)phase << 8) | ((unsigned)src << 16) |
+                                   ((unsigned)r << 24));
+            *abort_flag = 1;
+            return;
+          }
+        }
+      }
+      be.pause();
+    }
+  }
+
+  // Tell every other member of my stage-k group that `phase` reached `val` on my side.
+  // Precondition: be.sync() after the data writes being published.
+  FT_DEV void signal_group(int phase, int k, uint64_t val) {
+    const int w = a.plan.width[k], g = a.plan.gap[k], base = stage_base(a.plan, r, k);
+    for (int j = be.tid(); j < w; j += be.nthr()) {
+      int p = base + j * g;
+      if (p == r) continue;
+      be.fence();
+      be.flag_st(cd.pad[p] + pad_slot(phase, cta, r), val);
+    }
+  }
+  // Wait until every other member of my stage-k group has signalled `phase` >= val to me.
+  FT_DEV void wait_group(int phase, int k, uint64_t val) {
+    const int w = a.plan.width[k], g = a.plan.gap[k], base = stage_base(a.plan, r, k);
+    for (int j = be.tid(); j < w; j += be.nthr()) {
+      int p = base + j * g;
+      if (p == r) continue;
+      spin(cd.pad[r] + pad_slot(phase, cta, p), val, phase, p);
+      be.fence();
+    }
+    be.sync();
+  }
+
+  // ---- element access -------------------------------------------------------------------------------
+  FT_DEV static PackT ld_win(const char* base, long long byte_off, bool remote) {
+    PackT v;
+    BE::template ld<(int)sizeof(PackT)>(&v, base + byte_off, remote);
+    return v;
+  }
+  FT_DEV static void st_win(char* base, long long byte_off, const PackT& v) {
+    BE::template st<(int)sizeof(PackT)>(base + byte_off, &v);
+  }
+  // nvalid < VE only for the very last vector of the message: user buffers hold exactly `count`
+  // elements, so the ragged end is touched element by element.
+  FT_DEV static PackIO ld_user(const IO* x, long long elem, int nvalid) {
+    PackIO v;
+    if (nvalid >= VE) {
+      BE::template ld<(int)sizeof(PackIO)>(&v, x + elem, false);
+    } else {
+      for (int i = 0; i < VE; ++i) {
+        if (i < nvalid) BE::template ld<(int)sizeof(IO)>(&v.e[i], x + elem + i, false);
+        else v.e[i] = v.e[0];
+      }
+    }
+    return v;
+  }
+  FT_DEV static void st_user(IO* y, long long elem, const PackIO& v, int nvalid) {
+    if (nvalid >= VE) {
+      BE::template st<(int)sizeof(PackIO)>(y + elem, &v);
+    } else {
+      for (int i = 0; i < nvalid; ++i) BE::template st<(int)sizeof(IO)>(y + elem + i, &v.e[i]);
+    }
+  }
+  FT_DEV static PackT io_to_wire(const PackIO& x) {
+    PackT o;
+#pragma unroll
+    for (int i = 0; i < VE; ++i) {
+      if constexpr (kRawIO) o.e[i] = x.e[i];
+      else o.e[i] = EL::down((A)EU::up(x.e[i]));
+    }
+    return o;
+  }
+  FT_DEV PackIO wire_to_io(const PackT& x) const {
+    PackIO o;
+#pragma unroll
+    for (int i = 0; i < VE; ++i) {
+      if constexpr (EL::is_float) {
+        A v = EL::up(x.e[i]);
+        if (a.apply_scale) v = (A)(v * (A)a.scale);
+        o.e[i] = EU::down((typename EU::acc)v);
+      } else {
+        if constexpr (kRawIO) o.e[i] = x.e[i];
+        else o.e[i] = EU::down((typename EU::acc)EL::up(x.e[i]));
+      }
+    }
+    return o;
+  }
+
+  // Valid element count of block b inside tile t, relative to the tile start (may be <= 0).
+  FT_DEV long long tile_valid(long long b, int t, long long* start) const {
+    long long lo, hi;
+    tile_range(a.lay, b, t, &lo, &hi);
+    *start = lo;
+    return hi - lo;
+  }
+
+  // ---- phase IN: private user buffer -> my window (only the blocks some peer will pull) -------------
+  template <int UNR> FT_DEV void copy_in_tile(int t) {
+    const Layout& L = a.lay;
+    const int N = a.plan.nranks, g1 = a.plan.gap[1];
+    const int CV = (int)((L.tile + VE - 1) / VE);
+    const long long total = (long long)N * CV;
+    const IO* x = (const IO*)rc.send;
+    char* wr = rc.win[r] + woff;
+    const int nth = be.nthr(), tid = be.tid();
+    for (long long q0 = 0; q0 < total; q0 += (long long)nth * UNR) {
+      PackIO v[UNR];
+      long long el[UNR];
+      int nv[UNR];
+#pragma unroll
+      for (int u = 0; u < UNR; ++u) {
+        long long q = q0 + (long long)u * nth + tid;
+        nv[u] = 0;
+        if (q < total) {
+          int b = (int)(q / CV), vi = (int)(q - (long long)b * CV);
+          if ((b % g1) != (r % g1)) {  // blocks I own after stage 0 are read straight from `send`
+            long long start, n = tile_valid(b, t, &start) - (long long)vi * VE;
+            if (n > 0) {
+              nv[u] = n < VE ? (int)n : VE;
+              el[u] = start + (long long)vi * VE;
+              v[u] = ld_user(x, el[u], nv[u]);
+            }
+          }
+        }
+      }
+#pragma unroll
+      for (int u = 0; u < UNR; ++u)
+        if (nv[u]) st_win(wr, el[u] * (long long)sizeof(T), io_to_wire(v[u]));
+    }
+  }
+
+  // ---- reduce-scatter stage k on tile t ---------------------------------------------------------------
+  // For every block b == r (mod g_{k+1}): W_r[b] = own[b] (+) peers' W_p[b], peers ascending.
+  template <int UNR, int PB> FT_DEV void rs_tile(int k, int t) {
+    const Plan& P = a.plan;
+    const Layout& L = a.lay;
+    const int w = P.width[k], g = P.gap[k], gn = P.gap[k + 1], base = stage_base(P, r, k);
+    const int nb = P.nranks / gn, rmod = r % gn;
+    const int CV = (int)((L.tile + VE - 1) / VE);
+    const long long total = (long long)nb * CV;
+    const int npeers = w - 1;
+    const char* pp[PB];
+#pragma unroll
+    for (int j = 0; j < PB; ++j) {
+      int p = base + (j + (base + j * g >= r ? 1 : 0)) * g;  // j-th peer in ascending order, self skipped
+      pp[j] = (j < npeers) ? (rc.win[p] + woff) : nullptr;
+    }
+    char* wr = rc.win[r] + woff;
+    const IO* x = (const IO*)rc.send;
+    const bool own_from_user = (k == 0) && (a.mode == MODE_STAGING);
+    const int nth = be.nthr(), tid = be.tid();
+
+    for (long long q0 = 0; q0 < total; q0 += (long long)nth * UNR) {
+      PackT own[UNR];
+      PackT in[UNR][PB];
+      long long el[UNR];
+      int nv[UNR];
+#pragma unroll
+      for (int u = 0; u < UNR; ++u) {
+        long long q = q0 + (long long)u * nth + tid;
+        nv[u] = 0;
+        if (q < total) {
+          int bi = (int)(q / CV), vi = (int)(q - (long long)bi * CV);
+          long long b = rmod + (long long)bi * gn;
+          long long start, n = tile_valid(b, t, &start) - (long long)vi * VE;
+          if (n > 0) {
+            nv[u] = n < VE ? (int)n : VE;
+            el[u] = start + (long long)vi * VE;
+            const long long off = el[u] * (long long)sizeof(T);
+            if (own_from_user) own[u] = io_to_wire(ld_user(x, el[u], nv[u]));
+            else own[u] = ld_win(wr, off, false);
+#pragma unroll
+            for (int j = 0; j < PB; ++j)
+              if (j < npeers) in[u][j] = ld_win(pp[j], off, true);
+          }
+        }
+      }
+#pragma unroll
+      for (int u = 0; u < UNR; ++u) {
+        if (!nv[u]) continue;
+        A acc[VE];
+#pragma unroll
+        for (int i = 0; i < VE; ++i) acc[i] = EL::up(own[u].e[i]);
+#pragma unroll
+        for (int j = 0; j < PB; ++j) {
+          if (j < npeers) {
+#pragma unroll
+            for (int i = 0; i < VE; ++i) acc[i] = Op::apply(acc[i], EL::up(in[u][j].e[i]));
+          }
+        }
+        const long long off = el[u] * (long long)sizeof(T);
+        for (int j = PB; j < npeers; ++j) {  // widths beyond PB+1: one peer at a time
+          int p = base + (j + (base + j * g >= r ? 1 : 0)) * g;
+          PackT xin = ld_win(rc.win[p] + woff, off, true);
+#pragma unroll
+          for (int i = 0; i < VE; ++i) acc[i] = Op::apply(acc[i], EL::up(xin.e[i]));
+        }
+        PackT o;
+#pragma unroll
+        for (int i = 0; i < VE; ++i) o.e[i] = EL::down(acc[i]);
+        st_win(wr, off, o);
+      }
+    }
+  }
+
+  // ---- all-gather stage k on tile t ---------------------------------------------------------------------
+  // Pull blocks b == p (mod g_{k+1}) from every group peer p. k > 0: into my window. k == 0: into the
+  // user's recv buffer through the scale/cast epilogue, including my own blocks.
+  template <int UNR> FT_DEV void ag_tile(int k, int t) {
+    const Plan& P = a.plan;
+    const Layout& L = a.lay;
+    const int w = P.width[k], g = P.gap[k], gn = P.gap[k + 1], base = stage_base(P, r, k);
+    const int nb = P.nranks / gn;
+    const int CV = (int)((L.tile + VE - 1) / VE);
+    const bool last = (k == 0);
+    // In registered mode recv aliases my window: my own blocks are already in place unless the
+    // epilogue changes them.
+    const bool self_needed = last && !(a.mode == MODE_REGISTERED && kRawIO && !(EL::is_float && a.apply_scale));
+    const long long per_src = (long long)nb * CV;
+    const long long total = per_src * w;
+    char* wr = rc.win[r] + woff;
+    IO* y = (IO*)rc.recv;
+    const int nth = be.nthr(), tid = be.tid();
+
+    for (long long q0 = 0; q0 < total; q0 += (long long)nth * UNR) {
+      PackT v[UNR];
+      long long el[UNR];
+      int nv[UNR];
+#pragma unroll
+      for (int u = 0; u < UNR; ++u) {
+        long long q = q0 + (long long)u * nth + tid;
+        nv[u] = 0;
+        if (q < total) {
+          // vector index fastest, then source, then block group: neighbouring CV-runs hit different peers
+          int vi = (int)(q % CV);
+          long long rest = q / CV;
+          int s = (int)(rest % w), bi = (int)(rest / w);
+          int p = base + s * g;
+          if (p != r || self_needed) {
+            long long b = (p % gn) + (long long)bi * gn;
+            long long start, n = tile_valid(b, t, &start) - (long long)vi * VE;
+            if (n > 0) {
+              nv[u] = n < VE ? (int)n : VE;
+              el[u] = start + (long long)vi * VE;
+              v[u] = ld_win(rc.win[p] + woff, el[u] * (long long)sizeof(T), p != r);
+            }
+          }
+        }
+      }
+#pragma unroll
+      for (int u = 0; u < UNR; ++u) {
+        if (!nv[u]) continue;
+        if (last) st_user(y, el[u], wire_to_io(v[u]), nv[u]);
+        else st_win(wr, el[u] * (long long)sizeof(T), v[u]);
+      }
+    }
+  }
+
+  // ---- NVLS (multicast) pieces ---------------------------------------------------------------------------
+  // Copy every block of tile t from the user buffer into my window (the switch reads all of them).
+  template <int UNR> FT_DEV void copy_in_all_tile(int t) {
+    const Layout& L = a.lay;
+    const int N = a.plan.nranks;
+    const int CV = (int)((L.tile + VE - 1) / VE);
+    const long long total = (long long)N * CV;
+    const IO* x = (const IO*)rc.send;
+    char* wr = rc.win[r] + woff;
+    const int nth = be.nthr(), tid = be.tid();
+    for (long long q0 = 0; q0 < total; q0 += (long long)nth * UNR) {
+      PackIO v[UNR];
+      long long el[UNR];
+      int nv[UNR];
+#pragma unroll
+      for (int u = 0; u < UNR; ++u) {
+        long long q = q0 + (long long)u * nth + tid;
+        nv[u] = 0;
+        if (q < total) {
+          int b = (int)(q / CV), vi = (int)(q - (long long)b * CV);
+          long long start, n = tile_valid(b, t, &start) - (long long)vi * VE;
+          if (n > 0) {
+            nv[u] = n < VE ? (int)n : VE;
+            el[u] = start + (long long)vi * VE;
+            v[u] = ld_user(x, el[u], nv[u]);
+          }
+        }
+      }
+#pragma unroll
+      for (int u = 0; u < UNR; ++u)
+        if (nv[u]) st_win(wr, el[u] * (long long)sizeof(T), io_to_wire(v[u]));
+    }
+  }
+
+  // In-switch reduction of my block of tile t: one multimem.ld_reduce pulls and sums the N copies,
+  // one multimem.st broadcasts the result into every rank's window.
+  template <int UNR> FT_DEV void nvls_reduce_tile(int t) {
+    const Layout& L = a.lay;
+    long long start, n = tile_valid(r, t, &start);
+    if (n <= 0) return;
+    const long long nvec = (n + VE - 1) / VE;
+    const int nth = be.nthr(), tid = be.tid();
+    for (long long q0 = 0; q0 < nvec; q0 += (long long)nth * UNR) {
+      PackT v[UNR];
+      bool ok[UNR];
+#pragma unroll
+      for (int u = 0; u < UNR; ++u) {
+        long long q = q0 + (long long)u * nth + tid;
+        ok[u] = q < nvec;
+        if (ok[u]) v[u] = be.template mc_ld_reduce<T, Op, VE>(rc, woff + (start + q * VE) * (long long)sizeof(T), a.plan.nranks);
+      }
+#pragma unroll
+      for (int u = 0; u < UNR; ++u) {
+        long long q = q0 + (long long)u * nth + tid;
+        if (ok[u]) be.template mc_st<T, VE>(rc, woff + (start + q * VE) * (long long)sizeof(T), v[u], a.plan.nranks);
+      }
+    }
+    (void)L;
+  }
+
+  // Local copy of every block of tile t from my window to the user buffer through the epilogue.
+  template <int UNR> FT_DEV void out_tile(int t) {
+    const Layout& L = a.lay;
+    const int N = a.plan.nranks;
+    const int CV = (int)((L.tile + VE - 1) / VE);
+    const long long total = (long long)N * CV;
+    IO* y = (IO*)rc.recv;
+    const char* wr = rc.win[r] + woff;
+    const int nth = be.nthr(), tid = be.tid();
+    for (long long q0 = 0; q0 < total; q0 += (long long)nth * UNR) {
+      PackT v[UNR];
+      long long el[UNR];
+      int nv[UNR];
+#pragma unroll
+      for (int u = 0; u < UNR; ++u) {
+        long long q = q0 + (long long)u * nth + tid;
+        nv[u] = 0;
+        if (q < total) {
+          int b = (int)(q / CV), vi = (int)(q - (long long)b * CV);
+          long long start, n = tile_valid(b, t, &start) - (long long)vi * VE;
+          if (n > 0) {
+            nv[u] = n < VE ? (int)n : VE;
+            el[u] = start + (long long)vi * VE;
+            v[u] = ld_win(wr, el[u] * (long long)sizeof(T), false);
+          }
+        }
+      }
+#pragma unroll
+      for (int u = 0; u < UNR; ++u)
+        if (nv[u]) st_user(y, el[u], wire_to_io(v[u]), nv[u]);
+    }
+  }
+
+  // NVLS allreduce. Plan must be the flat {N} plan (stage-0 group == everybody).
+  FT_DEV void run_nvls() {
+    const int G = a.ctas, nt = a.lay.ntiles;
+    const int mine = cta < nt ? (nt - cta + G - 1) / G : 0;
+    constexpr int CU = (VE == 1) ? 1 : 4;
+    if (a.mode == MODE_STAGING) {
+      for (int j = 0; j < mine; ++j) {
+        copy_in_all_tile<CU>(cta + j * G);
+        be.sync();
+        signal_group(PH_IN, 0, E + j + 1);
+      }
+    } else {
+      signal_group(PH_IN, 0, E + mine);
+    }
+    for (int j = 0; j < mine; ++j) {
+      wait_group(PH_IN, 0, E + j + 1);
+      nvls_reduce_tile<CU>(cta + j * G);
+      be.sync();
+      signal_group(PH_RS0, 0, E + j + 1);
+    }
+    const bool need_out = !(a.mode == MODE_REGISTERED && kRawIO && !(EL::is_float && a.apply_scale));
+    for (int j = 0; j < mine; ++j) {
+      wait_group(PH_RS0, 0, E + j + 1);
+      if (need_out) out_tile<CU>(cta + j * G);
+    }
+    if (a.mode == MODE_REGISTERED) {
+      be.sync();
+      signal_group(PH_END, 0, E + 1);
+      wait_group(PH_END, 0, E + 1);
+    }
+    be.finish(cd, a.ctas);
+  }
+
+  // ---- one-shot LL ----------------------------------------------------------------------------------------
+  // Every rank pushes its whole (small) message to every peer as 16-byte lines {data, flag, data, flag}
+  // and then reduces the N-1 received copies with its own; a line is valid when both flags carry this
+  // call's tag, so there is no separate barrier: latency is one NVLink store hop.
+  // (No counterpart in the reference, which has no latency-optimised path.)
+  static constexpr int LE = 8 / (int)sizeof(T) > 0 ? 8 / (int)sizeof(T) : 1;  // elements per line
+  FT_DEV void run_oneshot() {
+    const int N = a.plan.nranks, G = a.ctas;
+    const long long count = a.lay.count;
+    const long long nlines = (count + LE - 1) / LE;
+    const uint32_t tag = (uint32_t)(E >> FT_EPOCH_SHIFT);  // epoch + 1, never 0 for 2^32 calls
+    const size_t region = (cd.ll_bytes / (size_t)N) & ~(size_t)15;
+    const size_t par_off = ((E >> FT_EPOCH_SHIFT) & 1) ? cd.ll_bytes : 0;
+    const IO* x = (const IO*)rc.send;
+    IO* y = (IO*)rc.recv;
+    const long long stride = (long long)G * be.nthr();
+    for (long long i = (long long)cta * be.nthr() + be.tid(); i < nlines; i += stride) {
+      const long long e0 = i * LE;
+      const int nv = (count - e0) < LE ? (int)(count - e0) : LE;
+      // own payload in wire format
+      Pack<T, LE> own;
+      if (VE > 1 && nv == LE) {
+        Pack<IO, LE> raw;
+        BE::template ld<(int)sizeof(Pack<IO, LE>)>(&raw, x + e0, false);
+#pragma unroll
+        for (int q = 0; q < LE; ++q) {
+          if constexpr (kRawIO) own.e[q] = raw.e[q];
+          else own.e[q] = EL::down((A)EU::up(raw.e[q]));
+        }
+      } else {
+        for (int q = 0; q < LE; ++q) {
+          IO t0;
+          if (q < nv) BE::template ld<(int)sizeof(IO)>(&t0, x + e0 + q, false);
+          else BE::template ld<(int)sizeof(IO)>(&t0, x + e0, false);
+          if constexpr (kRawIO) own.e[q] = t0;
+          else own.e[q] = EL::down((A)EU::up(t0));
+        }
+      }
+      uint32_t d[2] = {0, 0};
+      memcpy(d, &own, sizeof(own) < 8 ? sizeof(own) : 8);
+      for (int p = 0; p < N; ++p) {
+        if (p == r) continue;
+        be.ll_st(cd.ll[p] + par_off + (size_t)r * region + (size_t)i * 16, d[0], d[1], tag);
+      }
+      A acc[LE] = {};
+      bool first = true;
+      for (int q = 0; q < N; ++q) {  // ascending rank order, identical on every rank
+        Pack<T, LE> in;
+        if (q == r) {
+          in = own;
+        } else {
+          uint32_t g[2];
+          if (!ll_wait(cd.ll[r] + par_off + (size_t)q * region + (size_t)i * 16, tag, g, q)) { g[0] = g[1] = 0; }
+          memcpy(&in, g, sizeof(in) < 8 ? sizeof(in) : 8);
+        }
+#pragma unroll
+        for (int e = 0; e < LE; ++e) acc[e] = first ? EL::up(in.e[e]) : Op::apply(acc[e], EL::up(in.e[e]));
+        first = false;
+      }
+      Pack<IO, LE> out;
+#pragma unroll
+      for (int e = 0; e < LE; ++e) {
+        if constexpr (EL::is_float) {
+          A v = acc[e];
+          if (a.apply_scale) v = (A)(v * (A)a.scale);
+          out.e[e] = EU::down((typename EU::acc)v);
+        } else {
+          out.e[e] = EU::down((typename EU::acc)acc[e]);
+        }
+      }
+      if (VE > 1 && nv == LE) BE::template st<(int)sizeof(Pack<IO, LE>)>(y + e0, &out);
+      else for (int q = 0; q < nv; ++q) BE::template st<(int)sizeof(IO)>(y + e0 + q, &out.e[q]);
+    }
+    be.finish(cd, a.ctas);
+  }
+  FT_DEV bool ll_wait(const char* line, uint32_t tag, uint32_t* data, int src) {
+    if (*abort_flag) return false;
+    uint64_t t0 = 0;
+    unsigned it = 0;
+    while (!be.ll_ld(line, tag, data)) {
+      if (((++it) & 0x3ff) == 0) {
+        if (be.err_ld(cd.err)) { *abort_flag = 1; return false; }
+        if (a.timeout_ns) {
+          uint64_t now = be.now_ns();
+          if (!t0) t0 = now;
+          else if (now - t0 > a.timeout_ns) {
+            be.err_set(cd.err, (unsigned)ERR_TIMEOUT | (0xfeu << 8) | ((unsigned)src << 16) | ((unsigned)r << 24));
+            *abort_flag = 1;
+            return false;
+          }
+        }
+      }
+      be.pause();
+    }
+    return true;
+  }
+
+  // ---- ring ----------------------------------------------------------------------------------------------
+  // Capability parity: FlexTree::ring_allreduce (mpi_mod.hpp:1113-1163): N-1 reduce-scatter steps then N-1
+  // all-gather steps around the ring, here as pulls from the left neighbour gated by one progress
+  // counter per (CTA, neighbour). Progress value for "step s, tile j done" is E + s*mine + j + 1 with
+  // s = 0 for the input, 1..N-1 for RS, N..2N-2 for AG (monotone because loops are step-major).
+  template <int UNR> FT_DEV void ring_step_tile(int t, int blk, bool reduce, bool to_user, bool own_from_user) {
+    const int N = a.plan.nranks, left = (r + N - 1) % N;
+    long long start, n = tile_valid(blk, t, &start);
+    if (n <= 0) return;
+    const long long nvec = (n + VE - 1) / VE;
+    const char* wl = rc.win[left] + woff;
+    char* wr = rc.win[r] + woff;
+    const IO* x = (const IO*)rc.send;
+    IO* y = (IO*)rc.recv;
+    const int nth = be.nthr(), tid = be.tid();
+    for (long long q0 = 0; q0 < nvec; q0 += (long long)nth * UNR) {
+      PackT in[UNR], own[UNR];
+      int nv[UNR];
+#pragma unroll
+      for (int u = 0; u < UNR; ++u) {
+        long long q = q0 + (long long)u * nth + tid;
+        nv[u] = 0;
+        if (q < nvec) {
+          long long rem = n - q * VE;
+          nv[u] = rem < VE ? (int)rem : VE;
+          long long el = start + q * VE;
+          in[u] = ld_win(wl, el * (long long)sizeof(T), true);
+          if (reduce) {
+            if (own_from_user) own[u] = io_to_wire(ld_user(x, el, nv[u]));
+            else own[u] = ld_win(wr, el * (long long)sizeof(T), false);
+          }
+        }
+      }
+#pragma unroll
+      for (int u = 0; u < UNR; ++u) {
+        if (!nv[u]) continue;
+        long long el = start + (q0 + (long long)u * nth + tid) * VE;
+        PackT o = in[u];
+        if (reduce) {
+          // the partial sum arriving from the left is accumulated first, then my contribution
+#pragma unroll
+          for (int i = 0; i < VE; ++i) o.e[i] = EL::down(Op::apply(EL::up(in[u].e[i]), EL::up(own[u].e[i])));
+        }
+        st_win(wr, el * (long long)sizeof(T), o);
+        if (to_user) st_user(y, el, wire_to_io(o), nv[u]);
+      }
+    }
+  }
+  template <int UNR> FT_DEV void ring_copy_tile(int t, int blk, bool in_dir) {
+    // in_dir: user -> window (input block); else window -> user (my fully reduced block)
+    long long start, n = tile_valid(blk, t, &start);
+    if (n <= 0) return;
+    const long long nvec = (n + VE - 1) / VE;
+    char* wr = rc.win[r] + woff;
+    const int nth = be.nthr(), tid = be.tid();
+    for (long long q = tid; q < nvec; q += nth) {
+      long long rem = n - q * VE, el = start + q * VE;
+      int nv = rem < VE ? (int)rem : VE;
+      if (in_dir) st_win(wr, el * (long long)sizeof(T), io_to_wire(ld_user((const IO*)rc.send, el, nv)));
+      else st_user((IO*)rc.recv, el, wire_to_io(ld_win(wr, el * (long long)sizeof(T), false)), nv);
+    }
+  }
+  FT_DEV void ring_signal(uint64_t val) {  // to my right neighbour
+    const int N = a.plan.nranks, right = (r + 1) % N;
+    if (be.tid() == 0) {
+      be.fence();
+      be.flag_st(cd.pad[right] + pad_slot(PH_RS0, cta, r), val);
+    }
+  }
+  FT_DEV void ring_wait(uint64_t val) {  // on my left neighbour
+    const int N = a.plan.nranks, left = (r + N - 1) % N;
+    if (be.tid() == 0) {
+      spin(cd.pad[r] + pad_slot(PH_RS0, cta, left), val, PH_RS0, left);
+      be.fence();
+    }
+    be.sync();
+  }
+  FT_DEV void run_ring() {
+    const int N = a.plan.nranks, G = a.ctas, nt = a.lay.ntiles;
+    const int mine = cta < nt ? (nt - cta + G - 1) / G : 0;
+    constexpr int CU = (VE == 1) ? 1 : 4;
+    const bool staging = a.mode == MODE_STAGING;
+    // step 0: my raw block r must be in my window for the right neighbour
+    for (int j = 0; j < mine; ++j) {
+      if (staging) ring_copy_tile<CU>(cta + j * G, r, true);
+      be.sync();
+      ring_signal(E + (uint64_t)j + 1);
+    }
+    // RS steps 1..N-1: pull block (r - s) from the left (it finished step s-1 on it), add mine
+    for (int s = 1; s <= N - 1; ++s) {
+      const int blk = ((r - s) % N + N) % N;
+      for (int j = 0; j < mine; ++j) {
+        ring_wait(E + (uint64_t)(s - 1) * mine + j + 1);
+        // after the last RS step block (r+1) is complete on this rank
+        ring_step_tile<CU>(cta + j * G, blk, true, s == N - 1, staging);
+        be.sync();
+        ring_signal(E + (uint64_t)s * mine + j + 1);
+      }
+    }
+    // AG steps N..2N-2: pull the completed block (r + 1 - (s - N + 1)) from the left
+    for (int s = N; s <= 2 * N - 2; ++s) {
+      const int blk = ((r - (s - N)) % N + N) % N;
+      for (int j = 0; j < mine; ++j) {
+        ring_wait(E + (uint64_t)(s - 1) * mine + j + 1);
+        ring_step_tile<CU>(cta + j * G, blk, false, true, false);
+        be.sync();
+        ring_signal(E + (uint64_t)s * mine + j + 1);
+      }
+    }
+    if (a.mode == MODE_REGISTERED) {  // exit barrier with both neighbours' readers: the right one reads me
+      const int right = (r + 1) % N, left = (r + N - 1) % N;
+      be.sync();
+      if (be.tid() == 0) {
+        be.fence();
+        be.flag_st(cd.pad[left] + pad_slot(PH_END, cta, r), E + 1);
+        spin(cd.pad[r] + pad_slot(PH_END, cta, right), E + 1, PH_END, right);
+        be.fence();
+      }
+      be.sync();
+    }
+    be.finish(cd, a.ctas);
+  }
+
+  template <int UNR_DUMMY = 0> FT_DEV void rs_dispatch(int k, int t) {
+    const int w = a.plan.width[k];
+    if constexpr (VE == 1) {
+      rs_tile<1, 8>(k, t);
+    } else {
+      if (w == 2) rs_tile<4, 1>(k, t);
+      else if (w == 3) rs_tile<4, 2>(k, t);
+      else if (w <= 5) rs_tile<2, 4>(k, t);
+      else rs_tile<1, 8>(k, t);
+    }
+  }
+
+  // ---- the whole call, for this CTA ---------------------------------------------------------------------
+  FT_DEV void run() {
+    const int G = a.ctas, m = a.plan.nstages, nt = a.lay.ntiles;
+    const int mine = cta < nt ? (nt - cta + G - 1) / G : 0;  // my tiles: t = cta + j*G
+    constexpr int CU = (VE == 1) ? 1 : 4;
+
+    // IN: publish my window to my stage-0 group
+    if (a.mode == MODE_STAGING) {
+      for (int j = 0; j < mine; ++j) {
+        copy_in_tile<CU>(cta + j * G);
+        be.sync();
+        signal_group(PH_IN, 0, E + j + 1);
+      }
+    } else {
+      signal_group(PH_IN, 0, E + mine);  // data was complete before the kernel started
+    }
+
+    // reduce-scatter, stage-major so that a wait is almost always for a long-finished tile
+    for (int k = 0; k < m; ++k) {
+      for (int j = 0; j < mine; ++j) {
+        wait_group(k == 0 ? (int)PH_IN : PH_RS0 + k - 1, k, E + j + 1);
+        rs_dispatch(k, cta + j * G);
+        be.sync();
+        // consumers: RS stage k+1 pulls from its stage-(k+1) group; after the last RS stage the AG of
+        // the same stage pulls
+        signal_group(PH_RS0 + k, k + 1 < m ? k + 1 : k, E + j + 1);
+      }
+    }
+
+    // all-gather, stages unwound in reverse
+    for (int k = m - 1; k >= 0; --k) {
+      for (int j = 0; j < mine; ++j) {
+        wait_group(k == m - 1 ? PH_RS0 + k : PH_AG0 + k + 1, k, E + j + 1);
+        ag_tile<CU>(k, cta + j * G);
+        if (k > 0) {
+          be.sync();
+          signal_group(PH_AG0 + k, k - 1, E + j + 1);
+        }
+      }
+    }
+
+    // registered mode: nobody may leave (and let the user overwrite the buffer) while a peer still reads it
+    if (a.mode == MODE_REGISTERED) {
+      be.sync();
+      for (int k = 0; k < m; ++k) signal_group(PH_END, k, E + 1);
+      for (int k = 0; k < m; ++k) wait_group(PH_END, k, E + 1);
+    }
+    be.finish(cd, a.ctas);
+  }
+};
+
+}  // namespace ft

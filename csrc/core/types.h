@@ -1,0 +1,183 @@
+// Element types, reduction operators and 16-byte packs shared by the CPU model and the CUDA kernels.
+//
+// Capability parity: the (op x dtype) dispatch of handle_reduce and the k-way reducers
+// reduce_sum<T> / reduce_band<T> (allreduce_over_mpi/mpi_mod.hpp:246-660, :825-874). The reference
+// supports SUM over 10 dtypes and BAND over the integer ones and exits on anything else; this
+// version adds MAX / MIN / BOR and fp16 / bf16 / uint32 / uint64, and accumulates 16-bit floats in
+// fp32 inside a stage.
+#pragma once
+#include <stdint.h>
+#include <string.h>
+
+#include "plan.h"
+
+#if defined(__CUDACC__)
+#include <cuda_bf16.h>
+#include <cuda_fp16.h>
+#endif
+
+namespace ft {
+
+// Numeric values are part of the C ABI (include/flextree.h).
+enum DType {
+  DT_UINT8 = 0, DT_INT8 = 1, DT_UINT16 = 2, DT_INT16 = 3, DT_INT32 = 4, DT_INT64 = 5,
+  DT_FLOAT = 6, DT_DOUBLE = 7, DT_BOOL = 8, DT_LONG_LONG = 9,
+  DT_UINT32 = 10, DT_UINT64 = 11, DT_HALF = 12, DT_BFLOAT16 = 13, DT_COUNT = 14
+};
+enum RedOp { OP_SUM = 0, OP_BAND = 1, OP_MAX = 2, OP_MIN = 3, OP_BOR = 4, OP_COUNT = 5 };
+
+inline int dtype_size(int dt) {
+  switch (dt) {
+    case DT_UINT8: case DT_INT8: case DT_BOOL: return 1;
+    case DT_UINT16: case DT_INT16: case DT_HALF: case DT_BFLOAT16: return 2;
+    case DT_INT32: case DT_UINT32: case DT_FLOAT: return 4;
+    case DT_INT64: case DT_UINT64: case DT_DOUBLE: case DT_LONG_LONG: return 8;
+  }
+  return 0;
+}
+inline bool dtype_is_float(int dt) {
+  return dt == DT_FLOAT || dt == DT_DOUBLE || dt == DT_HALF || dt == DT_BFLOAT16;
+}
+inline const char* dtype_name(int dt) {
+  static const char* n[] = {"uint8", "int8", "uint16", "int16", "int32", "int64", "float32",
+                            "float64", "bool", "longlong", "uint32", "uint64", "float16", "bfloat16"};
+  return (dt >= 0 && dt < DT_COUNT) ? n[dt] : "?";
+}
+inline const char* op_name(int op) {
+  static const char* n[] = {"sum", "band", "max", "min", "bor"};
+  return (op >= 0 && op < OP_COUNT) ? n[op] : "?";
+}
+// Is (op, dtype) defined? Bitwise ops need integers (as in the reference, mpi_mod.hpp:851-858).
+inline bool op_supported(int op, int dt) {
+  if (op < 0 || op >= OP_COUNT || dt < 0 || dt >= DT_COUNT) return false;
+  if ((op == OP_BAND || op == OP_BOR) && dtype_is_float(dt)) return false;
+  return true;
+}
+
+// ---- 16-bit float storage types usable from plain C++ -------------------------------------------
+struct bf16_t { uint16_t v; };
+struct f16_t { uint16_t v; };
+struct bool8_t { uint8_t v; };  // MPI_C_BOOL: SUM behaves as logical OR, BAND as logical AND
+
+FT_HD float bits_to_float(uint32_t u) {
+#if defined(__CUDA_ARCH__)
+  return __uint_as_float(u);
+#else
+  float f; memcpy(&f, &u, 4); return f;
+#endif
+}
+FT_HD uint32_t float_to_bits(float f) {
+#if defined(__CUDA_ARCH__)
+  return __float_as_uint(f);
+#else
+  uint32_t u; memcpy(&u, &f, 4); return u;
+#endif
+}
+
+FT_HD float to_float(bf16_t x) { return bits_to_float((uint32_t)x.v << 16); }
+FT_HD bf16_t bf16_from_float(float f) {
+  bf16_t r;
+#if defined(__CUDA_ARCH__)
+  r.v = __bfloat16_as_ushort(__float2bfloat16_rn(f));
+#else
+  uint32_t u = float_to_bits(f);
+  if ((u & 0x7fffffffu) > 0x7f800000u) { r.v = (uint16_t)((u >> 16) | 0x40); return r; }  // quiet NaN
+  u += 0x7fffu + ((u >> 16) & 1u);  // round to nearest even
+  r.v = (uint16_t)(u >> 16);
+#endif
+  return r;
+}
+
+FT_HD float to_float(f16_t x) {
+#if defined(__CUDA_ARCH__)
+  return __half2float(__ushort_as_half(x.v));
+#else
+  uint32_t s = (uint32_t)(x.v & 0x8000u) << 16, e = (x.v >> 10) & 0x1f, m = x.v & 0x3ffu;
+  if (e == 0) {
+    if (m == 0) return bits_to_float(s);
+    int sh = 0;  // subnormal: normalise
+    while (!(m & 0x400u)) { m <<= 1; ++sh; }
+    m &= 0x3ffu;
+    return bits_to_float(s | ((uint32_t)(127 - 15 - sh + 1) << 23) | (m << 13));
+  }
+  if (e == 31) return bits_to_float(s | 0x7f800000u | (m << 13));
+  return bits_to_float(s | ((e + 112) << 23) | (m << 13));
+#endif
+}
+FT_HD f16_t f16_from_float(float f) {
+  f16_t r;
+#if defined(__CUDA_ARCH__)
+  r.v = __half_as_ushort(__float2half_rn(f));
+#else
+  uint32_t u = float_to_bits(f), s = (u >> 16) & 0x8000u, a = u & 0x7fffffffu;
+  if (a > 0x7f800000u) { r.v = (uint16_t)(s | 0x7e00u); return r; }       // NaN
+  if (a >= 0x47800000u) { r.v = (uint16_t)(s | 0x7c00u); return r; }      // overflow -> inf (incl. inf)
+  if (a < 0x33000001u) { r.v = (uint16_t)s; return r; }                   // underflow -> 0
+  int e = (int)(a >> 23) - 127;
+  uint32_t m = (a & 0x7fffffu) | 0x800000u;
+  int shift = e < -14 ? (13 + (-14 - e)) : 13;   // bits dropped from the 24-bit significand
+  uint32_t half_m = m >> shift, rem = m & ((1u << shift) - 1), halfway = 1u << (shift - 1);
+  if (rem > halfway || (rem == halfway && (half_m & 1u))) ++half_m;
+  uint32_t he = e < -14 ? 0 : (uint32_t)(e + 15);
+  // half_m includes the implicit bit for normals; adding handles mantissa carry into the exponent
+  uint32_t out = e < -14 ? half_m : ((he << 10) + (half_m - 0x400u));
+  r.v = (uint16_t)(s | out);
+#endif
+  return r;
+}
+
+// ---- accumulator traits ---------------------------------------------------------------------------
+template <typename T> struct Elem {  // default: integers and fp32/fp64 accumulate in themselves
+  using acc = T;
+  static FT_HD acc up(T x) { return x; }
+  static FT_HD T down(acc a) { return a; }
+  static constexpr bool is_float = false;
+};
+template <> struct Elem<float> {
+  using acc = float;
+  static FT_HD acc up(float x) { return x; }
+  static FT_HD float down(acc a) { return a; }
+  static constexpr bool is_float = true;
+};
+template <> struct Elem<double> {
+  using acc = double;
+  static FT_HD acc up(double x) { return x; }
+  static FT_HD double down(acc a) { return a; }
+  static constexpr bool is_float = true;
+};
+template <> struct Elem<bf16_t> {
+  using acc = float;
+  static FT_HD acc up(bf16_t x) { return to_float(x); }
+  static FT_HD bf16_t down(acc a) { return bf16_from_float(a); }
+  static constexpr bool is_float = true;
+};
+template <> struct Elem<f16_t> {
+  using acc = float;
+  static FT_HD acc up(f16_t x) { return to_float(x); }
+  static FT_HD f16_t down(acc a) { return f16_from_float(a); }
+  static constexpr bool is_float = true;
+};
+template <> struct Elem<bool8_t> {
+  using acc = uint8_t;
+  static FT_HD acc up(bool8_t x) { return x.v ? 1 : 0; }
+  static FT_HD bool8_t down(acc a) { bool8_t r; r.v = a ? 1 : 0; return r; }
+  static constexpr bool is_float = false;
+};
+
+// ---- operators (applied on accumulators) ----------------------------------------------------------
+struct OpSum { template <typename A> static FT_HD A apply(A a, A b) { return (A)(a + b); } };
+struct OpMax { template <typename A> static FT_HD A apply(A a, A b) { return a > b ? a : (b > a ? b : (a == a ? a : b)); } };
+struct OpMin { template <typename A> static FT_HD A apply(A a, A b) { return a < b ? a : (b < a ? b : (a == a ? a : b)); } };
+struct OpBand { template <typename A> static FT_HD A apply(A a, A b) { return (A)(a & b); } };
+struct OpBor { template <typename A> static FT_HD A apply(A a, A b) { return (A)(a | b); } };
+// bool: SUM == OR (any), BAND == AND; on the 0/1 accumulator '+' could overflow to 2, so map it.
+struct OpBoolOr { template <typename A> static FT_HD A apply(A a, A b) { return (A)((a | b) ? 1 : 0); } };
+
+// ---- packs ----------------------------------------------------------------------------------------
+// A Pack is what one thread moves per memory instruction: 16 bytes on the vector path, one element
+// on the scalar (unaligned user buffer) path.
+template <typename T, int VE> struct alignas(sizeof(T) * VE >= 16 ? 16 : sizeof(T) * VE) Pack { T e[VE]; };
+
+template <typename T> struct VecElems { static constexpr int value = 16 / (int)sizeof(T); };
+
+}  // namespace ft

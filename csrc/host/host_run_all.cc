@@ -1,0 +1,19 @@
+#include "../core/comm_dev.h"
+#include "../core/dispatch.h"
+namespace ft {
+bool host_run_g1(int, int, int, bool, const StagedArgs*, int);
+bool host_run_g2(int, int, int, bool, const StagedArgs*, int);
+bool host_run_g4(int, int, int, bool, const StagedArgs*, int);
+bool host_run_g8(int, int, int, bool, const StagedArgs*, int);
+bool host_run_g16(int, int, int, bool, const StagedArgs*, int);
+bool host_run_group(int group, int dtype, int io_dtype, int op, bool vec, const StagedArgs* a, int algo) {
+  switch (group) {
+    case TG_F32: return host_run_g1(dtype, io_dtype, op, vec, a, algo);
+    case TG_F16: return host_run_g2(dtype, io_dtype, op, vec, a, algo);
+    case TG_64: return host_run_g4(dtype, io_dtype, op, vec, a, algo);
+    case TG_I32: return host_run_g8(dtype, io_dtype, op, vec, a, algo);
+    case TG_SMALL: return host_run_g16(dtype, io_dtype, op, vec, a, algo);
+  }
+  return false;
+}
+}  // namespace ft

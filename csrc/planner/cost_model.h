@@ -1,0 +1,83 @@
+// Cost models that rank stage-width factorizations (and, for the GPU model, algorithms).
+//
+// 1. LegacyCost: the reference's hand-calibrated formula, kept as an oracle so that the planner can
+//    reproduce the reference's picks (cost_model/CostModel.h:1-120). Behaviour re-implemented:
+//      latency  = sum over layers of 2*lo (+ 100*(w-9)*co if w > 9)      (CostModel.h:1-20, :92 -
+//                 the reference passes a literal 100 instead of the chunk size; reproduced)
+//      bandwidth= (N-1)/N * chunk * bo                                    (CostModel.h:22-30)
+//      memory   = (N + 1 + 2*sum_{k=1}^{h-1} prod_{j<k} tree[j]) * chunk/N * o   (CostModel.h:32-79)
+//    The reference has undefined behaviour for tree heights 0 and >9 and an uninitialised
+//    accumulator; this version is total (any height) and initialised.
+//
+// 2. LinkModel: an alpha-beta-gamma model of one NVSwitch box, re-fit from measurements taken on the
+//    box (bench/fit_cost_model.py writes the JSON that load_link_model reads). It predicts the time of
+//    every algorithm this library implements and drives FT_ALGO=auto.
+#pragma once
+#include <string>
+#include <vector>
+
+#include "factorize.h"
+
+namespace ft {
+
+struct LegacyTerms {
+  double latency = 0, memory = 0, bandwidth = 0;
+  double total() const { return latency + memory + bandwidth; }
+};
+
+struct LegacyCoeffs {
+  double lo = 0.004;         // per-layer latency (x2)
+  double co = 0.0002;        // incast/control penalty per chunk-unit per width above 9
+  double bo = 0.0068;        // bandwidth + compute
+  double o = 0.0004;         // memory read/write
+  double latency_chunk = 100;  // the reference hard-codes 100 here (CostModel.h:92)
+  int incast_knee = 9;
+};
+
+LegacyTerms legacy_cost(const Widths& tree, int total_nodes, double chunk,
+                        const LegacyCoeffs& c = LegacyCoeffs());
+
+// arg-min over candidates (first minimum wins, like the reference's strict '<').
+// Returns the index into `trees`, or -1 if empty.
+int legacy_choose(const std::vector<Widths>& trees, int total_nodes, double chunk,
+                  double* best_cost = nullptr, const LegacyCoeffs& c = LegacyCoeffs());
+
+// ---------------------------------------------------------------------------------------------
+enum Algo { ALGO_AUTO = 0, ALGO_ONESHOT = 1, ALGO_STAGED = 2, ALGO_NVLS = 3, ALGO_RING = 4 };
+const char* algo_name(int a);
+int algo_from_name(const std::string& s);  // -1 if unknown
+
+struct LinkModel {
+  // latencies, microseconds
+  double alpha_launch_us = 2.2;   // kernel launch + first instruction
+  double alpha_sync_us = 2.0;     // one release->acquire hop across NVLink incl. fence
+  double alpha_ll_us = 1.6;       // one LL (data+flag) hop
+  // bandwidths, GB/s (bytes arriving at one GPU per second)
+  double beta_p2p_GBps = 700.0;   // asymptotic pull bandwidth with >= fanin_knee peers
+  double beta_p2p_1peer_GBps = 600.0;  // pull bandwidth from a single peer
+  int fanin_knee = 3;
+  double beta_nvls_GBps = 800.0;  // multimem ld_reduce/st effective per-GPU payload rate
+  double beta_ll_GBps = 300.0;    // LL payload rate (half of the line is flags)
+  double gamma_hbm_GBps = 6000.0; // local HBM copy/reduce traffic rate
+  double half_bw_bytes = 262144;  // per-stage bytes at which a stage reaches half its peak rate
+  bool has_nvls = false;
+  int max_oneshot_bytes = 1 << 20;
+};
+
+bool load_link_model(const std::string& json_path, LinkModel* m, std::string* err = nullptr);
+std::string dump_link_model(const LinkModel& m);
+
+struct Choice {
+  int algo = ALGO_STAGED;
+  Widths widths;     // for ALGO_STAGED
+  double est_us = 0;
+};
+
+// Predicted time of one algorithm. `registered` = zero-copy path (no copy-in pass).
+double predict_us(const LinkModel& m, int algo, const Widths& widths, int nranks, double bytes,
+                  bool registered);
+
+// Best (algo, widths) for a message. Considers every ordered factorization with width <= max_width.
+Choice choose(const LinkModel& m, int nranks, double bytes, bool registered, int max_width = 32);
+
+}  // namespace ft

@@ -1,0 +1,192 @@
+/* flextree.h - C API of the B200-native generalized allreduce library.
+ *
+ * Capability map to the reference (Youhe-Jiang/AllReduce-Over-MPI; citations are reference paths):
+ *   ft_allreduce            <-> MPI_Allreduce_FT / MPI_Allreduce override  allreduce_over_mpi/mpi_mod.hpp:1167-1221
+ *   FT_IN_PLACE             <-> MPI_IN_PLACE handling                     mpi_mod.hpp:959-962, 1194-1215
+ *   env FT_TOPO, ft_comm_set_widths <-> get_stages                        mpi_mod.hpp:882-929
+ *   ft_dtype_t / ft_op_t    <-> MPI_Datatype / MPI_Op dispatch            mpi_mod.hpp:825-874
+ *   ft_enumerate_widths ... <-> cost_model/GetWidth.h, ChooseWidth.h, CostModel.h, topo_count/factor_count.py
+ * Everything that takes a `stream` is asynchronous and CUDA-graph capturable once the communicator
+ * has been warmed up for that message size (see ft_comm_reserve).
+ */
+#ifndef FLEXTREE_H_
+#define FLEXTREE_H_
+
+#include <stddef.h>
+#include <stdint.h>
+
+#ifdef __cplusplus
+extern "C" {
+#endif
+
+#define FT_VERSION_MAJOR 0
+#define FT_VERSION_MINOR 1
+
+typedef enum {
+  FT_SUCCESS = 0,
+  FT_ERR_INVALID = 1,     /* bad argument (also: widths whose product is not the world size) */
+  FT_ERR_CUDA = 2,        /* a CUDA runtime/driver call failed; see ft_last_error() */
+  FT_ERR_UNSUPPORTED = 3, /* (op, dtype) or algorithm not available */
+  FT_ERR_TIMEOUT = 4,     /* device watchdog fired: a peer never signalled */
+  FT_ERR_NOMEM = 5,
+  FT_ERR_INTERNAL = 6
+} ft_result_t;
+
+/* Numeric values match ft::DType / ft::RedOp (csrc/core/types.h). The first ten are the reference's
+ * list (mpi_mod.hpp:827-837); the rest are additions. */
+typedef enum {
+  FT_UINT8 = 0, FT_INT8 = 1, FT_UINT16 = 2, FT_INT16 = 3, FT_INT32 = 4, FT_INT64 = 5,
+  FT_FLOAT = 6, FT_DOUBLE = 7, FT_BOOL = 8, FT_LONG_LONG = 9,
+  FT_UINT32 = 10, FT_UINT64 = 11, FT_HALF = 12, FT_BFLOAT16 = 13
+} ft_dtype_t;
+
+typedef enum { FT_SUM = 0, FT_BAND = 1, FT_MAX = 2, FT_MIN = 3, FT_BOR = 4 } ft_op_t;
+
+typedef enum { FT_ALGO_AUTO = 0, FT_ALGO_ONESHOT = 1, FT_ALGO_STAGES = 2, FT_ALGO_NVLS = 3, FT_ALGO_RING = 4 } ft_algo_t;
+
+#define FT_IN_PLACE ((const void*)(intptr_t)-1)
+
+const char* ft_last_error(void);      /* thread-local description of the last failure */
+const char* ft_version_string(void);  /* "flextree-b200 x.y (git describe, date)" */
+
+/* ------------------------------------------------------------------------------------------------
+ * Planner (pure CPU, no CUDA needed)
+ * ---------------------------------------------------------------------------------------------- */
+
+/* H(n): number of ordered factorizations of n (topo_count/factor_count.py:1-11). */
+uint64_t ft_count_factorizations(uint64_t n);
+
+/* Ordered factorizations of n, flattened as [len, w0..w(len-1), len, ...] into out[cap]. legacy_flat=1
+ * lists the single-stage tree the way cost_model/GetWidth.h:15-23 does ({1,n} and {n,1}).
+ * Returns the number of ints written, or -(needed) if cap is too small; *n_lists gets the list count. */
+long long ft_enumerate_widths(int n, int legacy_flat, int* out, long long cap, long long* n_lists);
+
+/* Reference chooseWidth(n) listing (cost_model/ChooseWidth.h:8-38) as text lines "2*4", "3*3-1", "7*1+1". */
+long long ft_candidates_text(int n, char* out, long long cap);
+
+int ft_prime_factors(int n, int* out, int cap); /* returns count */
+int ft_is_prime(int n);
+int ft_is_prime_legacy(int n);
+
+/* Reference cost formula (cost_model/CostModel.h). terms[3] = latency, memory, bandwidth (may be NULL). */
+double ft_legacy_cost(const int* widths, int nstages, int total_nodes, double chunk, double* terms);
+/* arg-min over ft_enumerate_widths(n, legacy) - what cost_model/main.cpp prints as the optimum.
+ * Returns the number of stages written to widths_out (<= cap), 0 if there is no candidate. */
+int ft_legacy_choose(int n, double chunk, int* widths_out, int cap, double* cost_out);
+
+/* Block-granular traffic of one rank for a plan, as the reference would send it (one message per
+ * block, mpi_mod.hpp:673-703). */
+int ft_plan_traffic(const int* widths, int nstages, int rank, long long count, long long* messages,
+                    long long* elements);
+/* ASCII dump of the send/recv tables of one rank (print_ops, mpi_mod.hpp:107-144). */
+long long ft_print_ops(const int* widths, int nstages, int rank, int lonely, char* out, long long cap);
+
+/* Link model (alpha-beta-gamma, fitted on the box). json may be NULL -> built-in defaults /
+ * env FT_COSTMODEL. */
+typedef struct ft_link_model ft_link_model_t;
+ft_link_model_t* ft_link_model_create(const char* json_path);
+void ft_link_model_destroy(ft_link_model_t*);
+long long ft_link_model_dump(const ft_link_model_t*, char* out, long long cap);
+int ft_link_model_set(ft_link_model_t*, const char* key, double value);
+double ft_predict_us(const ft_link_model_t*, int algo, const int* widths, int nstages, int nranks,
+                     double bytes, int registered);
+/* Picks algorithm + widths for a message; returns nstages written. */
+int ft_choose(const ft_link_model_t*, int nranks, double bytes, int registered, int* algo_out,
+              int* widths_out, int cap, double* est_us);
+
+/* FT_TOPO semantics of the reference (mpi_mod.hpp:882-929): unset/empty -> {n}; any 1 -> ring ({1});
+ * product != n -> error. text may be NULL to read the environment. Returns nstages or -1. */
+int ft_parse_topo(const char* text, int nranks, int* widths_out, int cap);
+
+/* ------------------------------------------------------------------------------------------------
+ * Communicators
+ * ---------------------------------------------------------------------------------------------- */
+typedef struct ft_comm ft_comm_t;
+
+/* Byte all-gather used once at creation to exchange memory handles: every rank contributes `bytes`
+ * and receives nranks*bytes in rank order. Must be a collective over the same ranks. */
+typedef int (*ft_allgather_fn)(void* ctx, const void* send, void* recv, size_t bytes);
+
+typedef struct {
+  size_t window_bytes;   /* initial staging window per parity (grow-only, like mpi_mod.hpp:932-950); 0 = default */
+  size_t ll_bytes;       /* LL (one-shot) buffer per parity; 0 = default */
+  int use_multicast;     /* -1 auto, 0 never, 1 require */
+  int use_vmm;           /* -1 auto (VMM + POSIX fd, fall back to cudaIpc), 0 cudaIpc only */
+  double timeout_s;      /* device watchdog; <0 = default (env FT_TIMEOUT_S or 20 s); 0 = off */
+} ft_comm_options_t;
+void ft_comm_options_default(ft_comm_options_t*);
+
+/* One process per GPU (what torch.distributed / torchrun gives you). */
+ft_result_t ft_comm_create(ft_comm_t** out, int rank, int nranks, int device, ft_allgather_fn ag,
+                           void* ag_ctx, const ft_comm_options_t* opts);
+/* One process, one rank per listed device (cudaDeviceEnablePeerAccess); comms[i] is rank i. */
+ft_result_t ft_comm_create_local(ft_comm_t** comms, int nranks, const int* devices,
+                                 const ft_comm_options_t* opts);
+/* One process, ONE device, nranks logical ranks served by a single cooperative launch: the kernels'
+ * protocol and arithmetic with every "peer" in local HBM. For tests and the 1-GPU benchmark. */
+ft_result_t ft_comm_create_emulated(ft_comm_t** out, int nranks, int device, const ft_comm_options_t* opts);
+ft_result_t ft_comm_destroy(ft_comm_t*);
+
+int ft_comm_rank(const ft_comm_t*);
+int ft_comm_size(const ft_comm_t*);
+int ft_comm_has_multicast(const ft_comm_t*);
+/* Sticky device error word (0 = healthy): code | phase<<8 | src<<16 | rank<<24. Synchronizes nothing. */
+unsigned ft_comm_error(ft_comm_t*);
+ft_result_t ft_comm_clear_error(ft_comm_t*);
+
+/* Overrides (NULL/0 restores automatic choice). Same meaning as env FT_TOPO / FT_ALGO. */
+ft_result_t ft_comm_set_widths(ft_comm_t*, const int* widths, int nstages);
+ft_result_t ft_comm_set_algo(ft_comm_t*, ft_algo_t algo);
+ft_result_t ft_comm_set_link_model(ft_comm_t*, const ft_link_model_t*);
+/* Launch shape overrides: CTAs per rank, threads per CTA, tile bytes (0 = automatic). */
+ft_result_t ft_comm_set_launch(ft_comm_t*, int ctas, int threads, long long tile_bytes);
+
+/* Collective: make sure a message of `bytes` fits the staging window (allocates + exchanges handles
+ * if it has to grow). Call it before stream capture. */
+ft_result_t ft_comm_reserve(ft_comm_t*, size_t bytes);
+
+/* Symmetric (registered) memory: collective allocation of `bytes` on every rank. Buffers from here
+ * can be all-reduced in place with zero copies. */
+ft_result_t ft_symm_alloc(ft_comm_t*, size_t bytes, void** ptr);
+ft_result_t ft_symm_free(ft_comm_t*, void* ptr);
+
+/* ------------------------------------------------------------------------------------------------
+ * Collectives. `stream` is a cudaStream_t.
+ * ---------------------------------------------------------------------------------------------- */
+ft_result_t ft_allreduce(const void* sendbuf, void* recvbuf, size_t count, ft_dtype_t dtype, ft_op_t op,
+                         ft_comm_t* comm, void* stream);
+
+/* Extended form used by the torch path: fp32 user buffers with a 16-bit wire (wire_dtype), and a
+ * fused `out = cast(sum * scale)` epilogue (the DDP 1/N). wire_dtype == dtype and scale == 1 give
+ * ft_allreduce. */
+ft_result_t ft_allreduce_ex(const void* sendbuf, void* recvbuf, size_t count, ft_dtype_t dtype,
+                            ft_dtype_t wire_dtype, ft_op_t op, double scale, ft_comm_t* comm, void* stream);
+
+/* Emulated communicators: one send/recv pointer per logical rank. */
+ft_result_t ft_allreduce_multi(const void* const* sendbufs, void* const* recvbufs, size_t count,
+                               ft_dtype_t dtype, ft_dtype_t wire_dtype, ft_op_t op, double scale,
+                               ft_comm_t* comm, void* stream);
+
+/* What the last call on this communicator resolved to (for logs, tests and the benchmark). */
+typedef struct {
+  int algo;
+  int nstages;
+  int widths[8];
+  int ctas, threads;
+  long long tile_bytes;
+  int mode;        /* 0 staging, 1 registered */
+  int vectorized;
+  double est_us;
+} ft_call_info_t;
+ft_result_t ft_comm_last_call(const ft_comm_t*, ft_call_info_t*);
+
+#ifdef STANDALONE_TEST
+/* Source-level alias for code written against the reference benchmark (benchmark.cpp:153). */
+#define MPI_Allreduce_FT(send, recv, count, dtype, op, comm) \
+  ((int)ft_allreduce((send), (recv), (count), (dtype), (op), (comm), 0))
+#endif
+
+#ifdef __cplusplus
+}
+#endif
+#endif /* FLEXTREE_H_ */

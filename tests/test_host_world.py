@@ -1,0 +1,296 @@
+"""The algorithm templates of csrc/core/staged_core.h, executed on CPU threads (one per "CTA"),
+checked against an independent numpy model. These are the same templates the CUDA kernels instantiate."""
+import numpy as np
+import pytest
+
+import flextree as ft
+from flextree import HostWorld
+from flextree.ops import constants as K
+
+from refimpl import block_size, from_bf16_bits, round_bf16, staged_allreduce, to_bf16_bits
+
+RNG = np.random.default_rng(1234)
+NP_OPS = {"sum": np.add, "max": np.maximum, "min": np.minimum, "band": np.bitwise_and, "bor": np.bitwise_or}
+
+
+def make_inputs(n, count, dtype):
+    dt = np.dtype(dtype)
+    if dt.kind == "f":
+        return [RNG.standard_normal(count).astype(dt) for _ in range(n)]
+    if dt.kind == "b":
+        return [RNG.integers(0, 2, count).astype(dt) for _ in range(n)]
+    info = np.iinfo(dt)
+    return [RNG.integers(info.min, info.max, count, dtype=dt, endpoint=True) for _ in range(n)]
+
+
+def aligned_empty(count, dtype, misalign=0):
+    raw = np.empty(count * np.dtype(dtype).itemsize + 64, dtype=np.uint8)
+    off = (-raw.ctypes.data) % 16 + misalign
+    return raw[off:off + count * np.dtype(dtype).itemsize].view(dtype)
+
+
+def aligned_copy(a, misalign=0):
+    out = aligned_empty(a.size, a.dtype, misalign)
+    out[:] = a
+    return out
+
+
+WIDTHS = {2: [[2]], 4: [[4], [2, 2]], 6: [[6], [2, 3], [3, 2]], 8: [[8], [2, 4], [4, 2], [2, 2, 2]],
+          12: [[2, 3, 2], [3, 4]], 20: [[20], [4, 5]]}
+
+
+@pytest.mark.parametrize("n", [2, 4, 6, 8, 12])
+@pytest.mark.parametrize("count", [1, 3, 5, 7, 35, 1000, 1001, 4099])
+def test_fp32_sum_bit_exact_all_factorizations(n, count):
+    """fp32 SUM must be bit-identical to the order-aware model (own first, peers ascending), on every
+    rank, for every width vector, in place and out of place, incl. count < N."""
+    inputs = make_inputs(n, count, np.float32)
+    B = block_size(count, n, 4)
+    with_world = HostWorld(n, window_bytes=1 << 16)
+    for widths in WIDTHS[n]:
+        want = staged_allreduce(inputs, widths, block=B)
+        send = [aligned_copy(x) for x in inputs]
+        recv = [aligned_empty(count, np.float32) for _ in range(n)]
+        for r in recv:
+            r[:] = np.nan
+        assert with_world.allreduce(send, recv, widths=widths, ctas=3, tile_bytes=256) == 0
+        for r in range(n):
+            np.testing.assert_array_equal(recv[r], want[r], err_msg=f"{widths} rank {r}")
+            np.testing.assert_array_equal(send[r], inputs[r])  # sendbuf untouched
+        buf = [aligned_copy(x) for x in inputs]  # in place
+        assert with_world.allreduce(buf, None, widths=widths, ctas=2, tile_bytes=512) == 0
+        for r in range(n):
+            np.testing.assert_array_equal(buf[r], want[r])
+    with_world.close()
+
+
+@pytest.mark.parametrize("dtype", [np.uint8, np.int8, np.uint16, np.int16, np.int32, np.uint32, np.int64,
+                                   np.uint64, np.float64, np.bool_])
+@pytest.mark.parametrize("op", ["sum", "max", "min", "band", "bor"])
+def test_dtype_op_matrix(dtype, op):
+    n, count, widths = 6, 1001, [2, 3]
+    dt = np.dtype(dtype)
+    if dt.kind == "f" and op in ("band", "bor"):
+        w = HostWorld(n)
+        x = make_inputs(n, 8, dtype)
+        assert w.allreduce([aligned_copy(a) for a in x], None, op=op, widths=widths) == -7  # unsupported
+        return
+    inputs = make_inputs(n, count, dtype)
+    w = HostWorld(n, window_bytes=1 << 16)
+    buf = [aligned_copy(x) for x in inputs]
+    assert w.allreduce(buf, None, op=op, widths=widths, ctas=2, tile_bytes=128) == 0
+    if dt.kind == "b":
+        stack = np.stack(inputs)
+        want = stack.any(0) if op in ("sum", "max", "bor") else stack.all(0)
+    elif dt.kind == "f":
+        want = staged_allreduce(inputs, widths, op=NP_OPS[op], block=block_size(count, n, dt.itemsize))[0]
+    else:
+        with np.errstate(over="ignore"):
+            want = inputs[0].copy()
+            for x in inputs[1:]:
+                want = NP_OPS[op](want, x)
+    for r in range(n):
+        np.testing.assert_array_equal(buf[r], want, err_msg=f"rank {r}")
+
+
+@pytest.mark.parametrize("misalign", [4, 8, 2])
+def test_unaligned_buffers_take_scalar_path(misalign):
+    n, count = 4, 777
+    dtype = np.float32 if misalign % 4 == 0 else np.int16
+    inputs = make_inputs(n, count, dtype)
+    w = HostWorld(n)
+    send = [aligned_copy(x, misalign) for x in inputs]
+    recv = [aligned_empty(count, dtype, misalign) for _ in range(n)]
+    assert w.allreduce(send, recv, widths=[2, 2], ctas=2, tile_bytes=64) == 0
+    if np.dtype(dtype).kind == "f":
+        want = staged_allreduce(inputs, [2, 2], block=block_size(count, n, 4, vectorized=False))[0]
+    else:
+        with np.errstate(over="ignore"):
+            want = inputs[0] + inputs[1] + inputs[2] + inputs[3]
+    for r in range(n):
+        np.testing.assert_array_equal(recv[r], want)
+
+
+def test_half_and_bf16_wire():
+    n, count, widths = 8, 2049, [2, 4]
+    # fp16 through numpy
+    x16 = [RNG.standard_normal(count).astype(np.float16) for _ in range(n)]
+    w = HostWorld(n, window_bytes=1 << 16)
+    buf = [aligned_copy(x) for x in x16]
+    assert w.allreduce(buf, None, widths=widths, ctas=2, tile_bytes=256) == 0
+    want = staged_allreduce(x16, widths, block=block_size(count, n, 2),
+                            round_fn=lambda a: a.astype(np.float16).astype(np.float32))[0].astype(np.float16)
+    for r in range(n):
+        np.testing.assert_array_equal(buf[r], want)
+    # bf16 carried as uint16 bit patterns
+    xf = [RNG.standard_normal(count).astype(np.float32) for _ in range(n)]
+    xb = [to_bf16_bits(x) for x in xf]
+    buf = [aligned_copy(x) for x in xb]
+    assert w.allreduce(buf, None, widths=widths, ctas=2, tile_bytes=256, dtype_code=K.BFLOAT16) == 0
+    want = staged_allreduce([from_bf16_bits(b) for b in xb], widths, block=block_size(count, n, 2),
+                            round_fn=round_bf16)[0]
+    for r in range(n):
+        np.testing.assert_array_equal(from_bf16_bits(buf[r]), want)
+
+
+def test_fp32_io_bf16_wire_with_scale():
+    """DDP shape: fp32 gradients, bf16 on the wire, fused 1/N scale + cast back to fp32."""
+    n, count, widths = 4, 1234, [4]
+    xf = [RNG.standard_normal(count).astype(np.float32) for _ in range(n)]
+    w = HostWorld(n, window_bytes=1 << 16)
+    buf = [aligned_copy(x) for x in xf]
+    assert w.allreduce(buf, None, widths=widths, ctas=2, tile_bytes=256, dtype_code=K.BFLOAT16,
+                       io_dtype_code=K.FLOAT, scale=1.0 / n) == 0
+    want = staged_allreduce([round_bf16(x) for x in xf], widths, block=block_size(count, n, 2),
+                            round_fn=round_bf16)[0] * np.float32(1.0 / n)
+    for r in range(n):
+        np.testing.assert_array_equal(buf[r], want)
+    exact = np.mean(np.stack(xf).astype(np.float64), 0)
+    assert np.max(np.abs(buf[0] - exact)) < 0.03
+
+
+def test_scale_epilogue_fp32():
+    n, count = 6, 333
+    xf = make_inputs(n, count, np.float32)
+    w = HostWorld(n)
+    buf = [aligned_copy(x) for x in xf]
+    assert w.allreduce(buf, None, widths=[3, 2], scale=0.25) == 0
+    want = staged_allreduce(xf, [3, 2], block=block_size(count, n, 4))[0] * np.float32(0.25)
+    np.testing.assert_array_equal(buf[3], want)
+
+
+@pytest.mark.parametrize("widths", [[8], [2, 4], [2, 2, 2]])
+def test_registered_in_place_zero_copy(widths):
+    n, count = 8, 5000
+    xf = make_inputs(n, count, np.float32)
+    w = HostWorld(n, window_bytes=1 << 16)
+    views = [w.registered(r, count, np.float32) for r in range(n)]
+    for it in range(3):  # back-to-back calls exercise the exit barrier / epoch logic
+        for r in range(n):
+            views[r][:] = xf[r]
+        assert w.allreduce(views, None, widths=widths, ctas=4, tile_bytes=512, mode=K.MODE_REGISTERED) == 0
+        want = staged_allreduce(xf, widths, block=block_size(count, n, 4))[0]
+        for r in range(n):
+            np.testing.assert_array_equal(views[r], want)
+    assert w.epoch(0) == 3 and w.epoch(n - 1) == 3
+
+
+def test_back_to_back_sizes_and_plans_reuse_flags():
+    """Different sizes, tilings, CTA counts and plans in sequence: epochs keep flags monotone and the
+    parity windows never collide."""
+    n = 6
+    w = HostWorld(n, window_bytes=1 << 18)
+    for i, (count, widths, ctas, tile) in enumerate([(10, [6], 1, 64), (40000, [2, 3], 5, 1024), (3, [3, 2], 2, 64),
+                                                     (777, [6], 4, 128), (40000, [3, 2], 3, 4096), (1, [2, 3], 1, 64)]):
+        xf = make_inputs(n, count, np.float32)
+        buf = [aligned_copy(x) for x in xf]
+        assert w.allreduce(buf, None, widths=widths, ctas=ctas, tile_bytes=tile) == 0
+        want = staged_allreduce(xf, widths, block=block_size(count, n, 4))[0]
+        for r in range(n):
+            np.testing.assert_array_equal(buf[r], want, err_msg=f"call {i} rank {r}")
+    assert w.epoch(0) == 6
+
+
+def test_width_20_single_stage():
+    """The reference caps a stage at 20-way reduce (mpi_mod.hpp:245); make sure 20 works (batched peers)."""
+    n, count = 20, 2000
+    xf = make_inputs(n, count, np.float32)
+    w = HostWorld(n, window_bytes=1 << 16)
+    for widths in ([20], [4, 5]):
+        buf = [aligned_copy(x) for x in xf]
+        assert w.allreduce(buf, None, widths=widths, ctas=1, tile_bytes=512) == 0
+        want = staged_allreduce(xf, widths, block=block_size(count, n, 4))[0]
+        for r in range(n):
+            np.testing.assert_array_equal(buf[r], want)
+
+
+@pytest.mark.parametrize("n", [2, 3, 5, 8])
+@pytest.mark.parametrize("count", [1, 6, 1000, 4097])
+def test_ring(n, count):
+    """Ring mode (FT_TOPO containing 1; reference ring_allreduce mpi_mod.hpp:1113-1163)."""
+    xf = make_inputs(n, count, np.float32)
+    w = HostWorld(n, window_bytes=1 << 16)
+    send = [aligned_copy(x) for x in xf]
+    recv = [aligned_empty(count, np.float32) for _ in range(n)]
+    assert w.allreduce(send, recv, algo="ring", ctas=2, tile_bytes=256) == 0
+    exact = np.sum(np.stack(xf).astype(np.float64), 0)
+    for r in range(n):
+        np.testing.assert_allclose(recv[r], exact, rtol=1e-5, atol=1e-5)
+        np.testing.assert_array_equal(recv[r], recv[0])  # all ranks bit-identical
+    ints = make_inputs(n, count, np.int32)
+    buf = [aligned_copy(x) for x in ints]
+    assert w.allreduce(buf, None, algo="ring", ctas=3, tile_bytes=128) == 0
+    with np.errstate(over="ignore"):
+        want = np.sum(np.stack(ints), 0, dtype=np.int32)
+    for r in range(n):
+        np.testing.assert_array_equal(buf[r], want)
+
+
+@pytest.mark.parametrize("n", [2, 4, 8])
+@pytest.mark.parametrize("dtype", [np.float32, np.float16, np.int32, np.uint8, np.float64])
+def test_oneshot_ll(n, dtype):
+    w = HostWorld(n, ll_bytes=1 << 18)
+    for count in (1, 5, 1023):
+        x = make_inputs(n, count, dtype)
+        send = [aligned_copy(a) for a in x]
+        recv = [aligned_empty(count, dtype) for _ in range(n)]
+        assert w.allreduce(send, recv, algo="oneshot", ctas=2) == 0
+        if np.dtype(dtype).kind == "f":
+            acc = x[0].astype(np.float64 if dtype == np.float64 else np.float32)
+            for a in x[1:]:
+                acc = acc + a.astype(acc.dtype)
+            want = acc.astype(dtype)
+        else:
+            with np.errstate(over="ignore"):
+                want = np.sum(np.stack(x), 0, dtype=dtype)
+        for r in range(n):
+            np.testing.assert_array_equal(recv[r], want, err_msg=f"count {count} rank {r}")
+    assert w.allreduce([aligned_copy(a) for a in make_inputs(n, 1 << 16, np.float32)], None, algo="oneshot") == -5
+
+
+@pytest.mark.parametrize("mode", [K.MODE_STAGING, K.MODE_REGISTERED])
+def test_nvls_protocol_with_emulated_switch(mode):
+    n, count = 8, 3001
+    xf = make_inputs(n, count, np.float32)
+    w = HostWorld(n, window_bytes=1 << 16)
+    if mode == K.MODE_REGISTERED:
+        bufs = [w.registered(r, count, np.float32) for r in range(n)]
+        for r in range(n):
+            bufs[r][:] = xf[r]
+    else:
+        bufs = [aligned_copy(x) for x in xf]
+    for _ in range(2):
+        assert w.allreduce(bufs, None, algo="nvls", ctas=3, tile_bytes=256, mode=mode) == 0
+        acc = xf[0].copy()
+        for a in xf[1:]:
+            acc = acc + a
+        for r in range(n):
+            np.testing.assert_array_equal(bufs[r], acc)
+        xf = [acc.copy() for _ in range(n)]
+
+
+def test_watchdog_fires_instead_of_hanging():
+    """Fault injection: one rank never joins the collective. The others must report a timeout."""
+    n = 4
+    w = HostWorld(n)
+    xf = make_inputs(n, 100, np.float32)
+    bufs = [aligned_copy(x) for x in xf]
+    rc = w.allreduce(bufs, None, widths=[2, 2], ctas=1, timeout_s=0.2, skip_rank=2)
+    assert rc > 0 and (rc & 0xFF) == 1  # ERR_TIMEOUT
+    assert any(w.error(r) for r in range(n))
+
+
+def test_conversions_match_numpy():
+    import ctypes as C
+    L = ft._lib.load()
+    vals = np.concatenate([RNG.standard_normal(2000).astype(np.float32) * 10.0 ** RNG.integers(-9, 6, 2000),
+                           np.array([0.0, -0.0, np.inf, -np.inf, 65504.0, 65520.0, 65519.9, 5.96e-8, 2.98e-8,
+                                     2.9802322e-8, 6.1e-5, 6.0975552e-05, 1e-10, 70000.0], dtype=np.float32)])
+    for v in vals:
+        h = L.ft_float_to_f16(C.c_float(v))
+        assert h == int(np.float32(v).astype(np.float16).view(np.uint16)), v
+        assert L.ft_float_to_bf16(C.c_float(v)) == int(to_bf16_bits(np.array([v], np.float32))[0]), v
+    for bits in list(range(0, 65536, 7)) + [0x7c00, 0xfc00, 0x0001, 0x03ff, 0x0400]:
+        f = L.ft_f16_to_float(bits)
+        want = np.array([bits], np.uint16).view(np.float16).astype(np.float32)[0]
+        assert (np.isnan(f) and np.isnan(want)) or f == want, hex(bits)
