@@ -19,7 +19,7 @@ GIT_HASH := $(shell git rev-parse --short HEAD 2>/dev/null || echo unknown)
 VERDEFS := -DFT_GIT_DESCRIBE='"$(GIT_DESCRIBE)"' -DFT_GIT_DATE='"$(GIT_DATE)"' -DFT_GIT_HASH='"$(GIT_HASH)"'
 
 CXXFLAGS := -std=c++17 -O2 -fPIC -Wall -Wextra -Wno-unknown-pragmas -Wno-maybe-uninitialized -Wno-uninitialized -Iinclude $(VERDEFS)
-NVFLAGS := -std=c++17 -O3 $(ARCH) -lineinfo -Xcompiler -fPIC -Xcompiler -Wall -Iinclude $(VERDEFS) --expt-relaxed-constexpr
+NVFLAGS := -ccbin /usr/bin/g++ -std=c++17 -O3 $(ARCH) -lineinfo -Xcompiler -fPIC -Xcompiler -Wall -Iinclude $(VERDEFS) --expt-relaxed-constexpr
 
 PLANNER_SRC := csrc/planner/factorize.cc csrc/planner/cost_model.cc csrc/planner/schedule.cc csrc/planner/c_api.cc
 HOST_SRC := csrc/host/host_world.cc csrc/host/host_run_all.cc $(wildcard csrc/host/host_run_g*.cc)
@@ -50,7 +50,7 @@ $(B)/libflextree_host.so: $(PLANNER_OBJ) $(HOST_OBJ)
 
 $(LIBDIR)/libflextree.so: $(PLANNER_OBJ) $(HOST_OBJ) $(RT_CC_OBJ) $(CUDA_OBJ)
 	@mkdir -p $(LIBDIR)
-	$(NVCC) $(ARCH) -shared -o $@ $^ -lpthread -ldl
+	$(NVCC) -ccbin /usr/bin/g++ $(ARCH) -shared -o $@ $^ -lpthread -ldl
 
 $(B)/ft_plan: csrc/tools/ft_plan.cc $(PLANNER_OBJ)
 	$(CXX) $(CXXFLAGS) -o $@ $^

@@ -6,4 +6,10 @@ from .ops.constants import __all__ as _const_all
 from .utils.hostworld import HostWorld
 from .utils.timer import Timer
 
-__all__ = list(_planner_all) + list(_const_all) + ["HostWorld", "Timer"]
+from .parallel.comm import Communicator, FlexTreeError
+from .parallel.api import init, allreduce, get_communicator, shutdown
+from .parallel.ddp import ddp_comm_hook, FlexTreeHookState
+
+__all__ = list(_planner_all) + list(_const_all) + [
+    "HostWorld", "Timer", "Communicator", "FlexTreeError", "init", "allreduce", "get_communicator", "shutdown",
+    "ddp_comm_hook", "FlexTreeHookState"]

@@ -1,0 +1,242 @@
+"""Communicators over the native runtime (csrc/runtime/comm.cu).
+
+* ``Communicator.from_process_group(pg)``: one process per GPU; torch.distributed is used only to move
+  the memory handles at creation/growth (the ``ft_allgather_fn`` callback) - never for the collective.
+* ``Communicator.emulated(n)``: n logical ranks on ONE GPU served by one cooperative launch (tests,
+  1-GPU benchmark).
+
+The reference's only "API" is MPI_Allreduce(sendbuf, recvbuf, count, datatype, op, comm)
+(allreduce_over_mpi/mpi_mod.hpp:1167-1221); ``allreduce`` below is that call for torch tensors, plus
+the fused scale/cast the DDP path needs.
+"""
+import ctypes as C
+
+import torch
+
+from .. import _lib
+from ..ops import constants as K
+
+_AG_FN = C.CFUNCTYPE(C.c_int, C.c_void_p, C.c_void_p, C.c_void_p, C.c_size_t)
+
+
+class CommOptions(C.Structure):
+    _fields_ = [("window_bytes", C.c_size_t), ("ll_bytes", C.c_size_t), ("use_multicast", C.c_int),
+                ("use_vmm", C.c_int), ("timeout_s", C.c_double)]
+
+
+class CallInfo(C.Structure):
+    _fields_ = [("algo", C.c_int), ("nstages", C.c_int), ("widths", C.c_int * 8), ("ctas", C.c_int),
+                ("threads", C.c_int), ("tile_bytes", C.c_longlong), ("mode", C.c_int), ("vectorized", C.c_int),
+                ("est_us", C.c_double)]
+
+    def as_dict(self):
+        return {"algo": K.ALGO_NAMES.get(self.algo, "?"), "widths": list(self.widths[:self.nstages]),
+                "ctas": self.ctas, "threads": self.threads, "tile_bytes": self.tile_bytes,
+                "mode": "registered" if self.mode else "staging", "vectorized": bool(self.vectorized),
+                "est_us": self.est_us}
+
+
+class FlexTreeError(RuntimeError):
+    pass
+
+
+def _check(L, rc, what):
+    if rc != 0:
+        raise FlexTreeError(f"{what} failed (code {rc}): {L.ft_last_error().decode()}")
+
+
+class _RawCudaBuffer:
+    """Minimal __cuda_array_interface__ holder so torch can wrap symmetric memory without copying."""
+
+    def __init__(self, ptr, nbytes, owner):
+        self.__cuda_array_interface__ = {"shape": (nbytes,), "typestr": "|u1", "data": (ptr, False), "version": 2}
+        self._owner = owner
+
+
+class Communicator:
+    def __init__(self):
+        self._L = _lib.load()
+        if not _lib.has_cuda_lib():
+            raise FlexTreeError("flextree: the CUDA library (allreduce-over-mpi_b200/lib/libflextree.so) is not built")
+        self._h = C.c_void_p()
+        self._cb = None
+        self.emulated_ranks = 0
+        self.device = None
+        self._symm = []
+
+    # ---- construction ---------------------------------------------------------------------------------
+    @staticmethod
+    def _options(window_bytes=0, ll_bytes=0, multicast=-1, vmm=-1, timeout_s=-1.0):
+        o = CommOptions()
+        o.window_bytes, o.ll_bytes, o.use_multicast, o.use_vmm, o.timeout_s = window_bytes, ll_bytes, multicast, vmm, timeout_s
+        return o
+
+    @classmethod
+    def from_process_group(cls, group=None, device=None, **opts):
+        import torch.distributed as dist
+        self = cls()
+        rank, world = dist.get_rank(group), dist.get_world_size(group)
+        if device is None:
+            device = torch.cuda.current_device()
+        self.device = torch.device("cuda", device if isinstance(device, int) else device.index)
+        backend = dist.get_backend(group)
+
+        def _allgather(_ctx, send, recv, nbytes):
+            try:
+                src = (C.c_ubyte * nbytes).from_address(send)
+                t = torch.frombuffer(src, dtype=torch.uint8).clone()
+                if "nccl" in backend:
+                    t = t.to(self.device)
+                out = [torch.empty_like(t) for _ in range(world)]
+                dist.all_gather(out, t, group=group)
+                flat = torch.cat(out).cpu().contiguous()
+                C.memmove(recv, flat.data_ptr(), nbytes * world)
+                return 0
+            except Exception as e:  # never let an exception cross the C boundary
+                import sys
+                print(f"[flextree] bootstrap allgather failed: {e!r}", file=sys.stderr)
+                return 1
+
+        self._cb = _AG_FN(_allgather)
+        o = cls._options(**opts)
+        with torch.cuda.device(self.device):
+            rc = self._L.ft_comm_create(C.byref(self._h), rank, world, self.device.index,
+                                        C.cast(self._cb, C.c_void_p), None, C.cast(C.byref(o), C.c_void_p))
+        _check(self._L, rc, "ft_comm_create")
+        return self
+
+    @classmethod
+    def emulated(cls, nranks, device=0, **opts):
+        self = cls()
+        self.device = torch.device("cuda", device)
+        o = cls._options(**opts)
+        rc = self._L.ft_comm_create_emulated(C.byref(self._h), nranks, device, C.cast(C.byref(o), C.c_void_p))
+        _check(self._L, rc, "ft_comm_create_emulated")
+        self.emulated_ranks = nranks
+        return self
+
+    def close(self):
+        if getattr(self, "_h", None) and self._h.value:
+            self._L.ft_comm_destroy(self._h)
+            self._h = C.c_void_p()
+
+    def __del__(self):
+        try:
+            self.close()
+        except Exception:
+            pass
+
+    # ---- properties -------------------------------------------------------------------------------------
+    @property
+    def rank(self):
+        return self._L.ft_comm_rank(self._h)
+
+    @property
+    def size(self):
+        return self._L.ft_comm_size(self._h)
+
+    @property
+    def has_multicast(self):
+        return bool(self._L.ft_comm_has_multicast(self._h))
+
+    def error(self):
+        """Sticky device error word (0 = healthy). Synchronizes the device."""
+        torch.cuda.synchronize(self.device)
+        return int(self._L.ft_comm_error(self._h))
+
+    def clear_error(self):
+        _check(self._L, self._L.ft_comm_clear_error(self._h), "ft_comm_clear_error")
+
+    def last_call(self):
+        info = CallInfo()
+        self._L.ft_comm_last_call(self._h, C.cast(C.byref(info), C.c_void_p))
+        return info.as_dict()
+
+    # ---- policy -------------------------------------------------------------------------------------------
+    def set_widths(self, widths):
+        if widths is None:
+            _check(self._L, self._L.ft_comm_set_widths(self._h, None, 0), "ft_comm_set_widths")
+        else:
+            a = (C.c_int * len(widths))(*widths)
+            _check(self._L, self._L.ft_comm_set_widths(self._h, a, len(widths)), "ft_comm_set_widths")
+
+    def set_algo(self, algo):
+        code = K.ALGOS[algo] if isinstance(algo, str) else int(algo)
+        _check(self._L, self._L.ft_comm_set_algo(self._h, code), "ft_comm_set_algo")
+
+    def set_launch(self, ctas=0, threads=0, tile_bytes=0):
+        _check(self._L, self._L.ft_comm_set_launch(self._h, ctas, threads, tile_bytes), "ft_comm_set_launch")
+
+    def set_link_model(self, model):
+        _check(self._L, self._L.ft_comm_set_link_model(self._h, model._h if model is not None else None),
+               "ft_comm_set_link_model")
+
+    def reserve(self, nbytes):
+        """Collective: make the staging window large enough for messages of nbytes (do this before
+        capturing a CUDA graph)."""
+        with torch.cuda.device(self.device):
+            _check(self._L, self._L.ft_comm_reserve(self._h, nbytes), "ft_comm_reserve")
+
+    # ---- symmetric tensors ----------------------------------------------------------------------------------
+    def symm_empty(self, shape, dtype=torch.float32):
+        """Collective: a tensor (a list of them for an emulated communicator) living in symmetric
+        memory; all-reducing it in place takes the zero-copy path."""
+        if isinstance(shape, int):
+            shape = (shape,)
+        numel = 1
+        for s in shape:
+            numel *= s
+        nbytes = max(16, numel * torch.empty((), dtype=dtype).element_size())
+        n = max(1, self.emulated_ranks)
+        ptrs = (C.c_void_p * n)()
+        with torch.cuda.device(self.device):
+            _check(self._L, self._L.ft_symm_alloc(self._h, nbytes, ptrs), "ft_symm_alloc")
+        outs = []
+        for p in ptrs:
+            raw = torch.as_tensor(_RawCudaBuffer(p, nbytes, self), device=self.device)
+            outs.append(raw.view(dtype)[:numel].view(*shape))
+        self._symm.append((list(ptrs), outs))
+        return outs if self.emulated_ranks else outs[0]
+
+    # ---- collectives ------------------------------------------------------------------------------------------
+    def _stream(self, stream):
+        s = stream if stream is not None else torch.cuda.current_stream(self.device)
+        return C.c_void_p(s.cuda_stream)
+
+    def allreduce(self, tensor, op="sum", out=None, scale=1.0, wire_dtype=None, stream=None):
+        """In place (``out=None``) or out of place allreduce of a contiguous CUDA tensor.
+
+        ``scale`` is fused into the last stage (``out = cast(sum * scale)``); ``wire_dtype`` (bf16/fp16) moves
+        fp32 tensors in 16 bits."""
+        if self.emulated_ranks:
+            raise FlexTreeError("emulated communicator: use allreduce_multi")
+        out = tensor if out is None else out
+        if not (tensor.is_contiguous() and out.is_contiguous()):
+            raise ValueError("flextree.allreduce needs contiguous tensors")
+        if out.dtype != tensor.dtype or out.numel() != tensor.numel():
+            raise ValueError("out must match the input dtype/size")
+        dt = K.torch_dtype_code(tensor.dtype)
+        wt = dt if wire_dtype is None else K.torch_dtype_code(wire_dtype)
+        opc = K.OPS[op] if isinstance(op, str) else int(op)
+        with torch.cuda.device(self.device):
+            rc = self._L.ft_allreduce_ex(C.c_void_p(tensor.data_ptr()), C.c_void_p(out.data_ptr()), tensor.numel(),
+                                         dt, wt, opc, float(scale), self._h, self._stream(stream))
+        _check(self._L, rc, "ft_allreduce")
+        return out
+
+    def allreduce_multi(self, tensors, op="sum", outs=None, scale=1.0, wire_dtype=None, stream=None):
+        """Emulated communicator: one tensor per logical rank."""
+        n = self.emulated_ranks
+        if not n or len(tensors) != n:
+            raise ValueError("need one tensor per emulated rank")
+        outs = tensors if outs is None else outs
+        dt = K.torch_dtype_code(tensors[0].dtype)
+        wt = dt if wire_dtype is None else K.torch_dtype_code(wire_dtype)
+        opc = K.OPS[op] if isinstance(op, str) else int(op)
+        s = (C.c_void_p * n)(*[t.data_ptr() for t in tensors])
+        r = (C.c_void_p * n)(*[t.data_ptr() for t in outs])
+        with torch.cuda.device(self.device):
+            rc = self._L.ft_allreduce_multi(s, r, tensors[0].numel(), dt, wt, opc, float(scale), self._h,
+                                            self._stream(stream))
+        _check(self._L, rc, "ft_allreduce_multi")
+        return outs

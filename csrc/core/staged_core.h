@@ -31,8 +31,10 @@ namespace ft {
 
 #if defined(__CUDACC__)
 #define FT_DEV __device__ __forceinline__
+#define FT_NOINLINE __device__ __noinline__
 #else
 #define FT_DEV inline
+#define FT_NOINLINE inline
 #endif
 
 template <typename X, typename Y> struct SameType { static constexpr bool value = false; };
@@ -173,31 +175,38 @@ struct StagedCta {
     *start = lo;
     return hi - lo;
   }
+  // Same, as a 32-bit count clamped to [0, tile]: jobs are indexed with 32-bit math (64-bit division
+  // costs ~40 registers per use and made the reduce loops spill).
+  FT_DEV int tile_valid32(int b, int t, long long* start) const {
+    long long n = tile_valid(b, t, start);
+    return n <= 0 ? 0 : (int)n;
+  }
 
   // ---- phase IN: private user buffer -> my window (only the blocks some peer will pull) -------------
   template <int UNR> FT_DEV void copy_in_tile(int t) {
     const Layout& L = a.lay;
     const int N = a.plan.nranks, g1 = a.plan.gap[1];
     const int CV = (int)((L.tile + VE - 1) / VE);
-    const long long total = (long long)N * CV;
+    const int total = N * CV;
     const IO* x = (const IO*)rc.send;
     char* wr = rc.win[r] + woff;
     const int nth = be.nthr(), tid = be.tid();
-    for (long long q0 = 0; q0 < total; q0 += (long long)nth * UNR) {
+    for (int q0 = 0; q0 < total; q0 += nth * UNR) {
       PackIO v[UNR];
       long long el[UNR];
       int nv[UNR];
 #pragma unroll
       for (int u = 0; u < UNR; ++u) {
-        long long q = q0 + (long long)u * nth + tid;
+        const int q = q0 + u * nth + tid;
         nv[u] = 0;
         if (q < total) {
-          int b = (int)(q / CV), vi = (int)(q - (long long)b * CV);
+          const int b = q / CV, vi = q - b * CV;
           if ((b % g1) != (r % g1)) {  // blocks I own after stage 0 are read straight from `send`
-            long long start, n = tile_valid(b, t, &start) - (long long)vi * VE;
+            long long start;
+            const int n = tile_valid32(b, t, &start) - vi * VE;
             if (n > 0) {
-              nv[u] = n < VE ? (int)n : VE;
-              el[u] = start + (long long)vi * VE;
+              nv[u] = n < VE ? n : VE;
+              el[u] = start + vi * VE;
               v[u] = ld_user(x, el[u], nv[u]);
             }
           }
@@ -211,74 +220,96 @@ struct StagedCta {
 
   // ---- reduce-scatter stage k on tile t ---------------------------------------------------------------
   // For every block b == r (mod g_{k+1}): W_r[b] = own[b] (+) peers' W_p[b], peers ascending.
+  // Each thread works on UNR vectors at a time and pulls PB peers per batch, so UNR*PB 16-byte NVLink
+  // loads are in flight per thread before the first add (the pulls are latency-, not issue-bound).
+  FT_DEV const char* rs_peer_ptr(int k, int j) const {  // j-th peer in ascending order, self skipped
+    const int g = a.plan.gap[k], base = stage_base(a.plan, r, k);
+    const int p = base + (j + (base + j * g >= r ? 1 : 0)) * g;
+    return rc.win[p] + woff;
+  }
   template <int UNR, int PB> FT_DEV void rs_tile(int k, int t) {
     const Plan& P = a.plan;
     const Layout& L = a.lay;
-    const int w = P.width[k], g = P.gap[k], gn = P.gap[k + 1], base = stage_base(P, r, k);
+    const int w = P.width[k], gn = P.gap[k + 1];
     const int nb = P.nranks / gn, rmod = r % gn;
     const int CV = (int)((L.tile + VE - 1) / VE);
-    const long long total = (long long)nb * CV;
+    const int total = nb * CV;
     const int npeers = w - 1;
-    const char* pp[PB];
+    const char* pp[PB];  // first batch of peers kept in registers; later batches are looked up
 #pragma unroll
-    for (int j = 0; j < PB; ++j) {
-      int p = base + (j + (base + j * g >= r ? 1 : 0)) * g;  // j-th peer in ascending order, self skipped
-      pp[j] = (j < npeers) ? (rc.win[p] + woff) : nullptr;
-    }
+    for (int j = 0; j < PB; ++j) pp[j] = (j < npeers) ? rs_peer_ptr(k, j) : nullptr;
     char* wr = rc.win[r] + woff;
     const IO* x = (const IO*)rc.send;
     const bool own_from_user = (k == 0) && (a.mode == MODE_STAGING);
     const int nth = be.nthr(), tid = be.tid();
 
-    for (long long q0 = 0; q0 < total; q0 += (long long)nth * UNR) {
-      PackT own[UNR];
+    for (int q0 = 0; q0 < total; q0 += nth * UNR) {
       PackT in[UNR][PB];
-      long long el[UNR];
+      A acc[UNR][VE];
+      long long off[UNR];
       int nv[UNR];
 #pragma unroll
       for (int u = 0; u < UNR; ++u) {
-        long long q = q0 + (long long)u * nth + tid;
+        const int q = q0 + u * nth + tid;
         nv[u] = 0;
         if (q < total) {
-          int bi = (int)(q / CV), vi = (int)(q - (long long)bi * CV);
-          long long b = rmod + (long long)bi * gn;
-          long long start, n = tile_valid(b, t, &start) - (long long)vi * VE;
+          const int bi = q / CV, vi = q - bi * CV;
+          long long start;
+          const int n = tile_valid32(rmod + bi * gn, t, &start) - vi * VE;
           if (n > 0) {
-            nv[u] = n < VE ? (int)n : VE;
-            el[u] = start + (long long)vi * VE;
-            const long long off = el[u] * (long long)sizeof(T);
-            if (own_from_user) own[u] = io_to_wire(ld_user(x, el[u], nv[u]));
-            else own[u] = ld_win(wr, off, false);
+            nv[u] = n < VE ? n : VE;
+            const long long el = start + vi * VE;
+            off[u] = el * (long long)sizeof(T);
+            PackT own;
+            if (own_from_user) own = io_to_wire(ld_user(x, el, nv[u]));
+            else own = ld_win(wr, off[u], false);
 #pragma unroll
             for (int j = 0; j < PB; ++j)
-              if (j < npeers) in[u][j] = ld_win(pp[j], off, true);
+              if (j < npeers) in[u][j] = ld_win(pp[j], off[u], true);
+#pragma unroll
+            for (int i = 0; i < VE; ++i) acc[u][i] = EL::up(own.e[i]);
           }
         }
       }
 #pragma unroll
       for (int u = 0; u < UNR; ++u) {
         if (!nv[u]) continue;
-        A acc[VE];
-#pragma unroll
-        for (int i = 0; i < VE; ++i) acc[i] = EL::up(own[u].e[i]);
 #pragma unroll
         for (int j = 0; j < PB; ++j) {
           if (j < npeers) {
 #pragma unroll
-            for (int i = 0; i < VE; ++i) acc[i] = Op::apply(acc[i], EL::up(in[u][j].e[i]));
+            for (int i = 0; i < VE; ++i) acc[u][i] = Op::apply(acc[u][i], EL::up(in[u][j].e[i]));
           }
         }
-        const long long off = el[u] * (long long)sizeof(T);
-        for (int j = PB; j < npeers; ++j) {  // widths beyond PB+1: one peer at a time
-          int p = base + (j + (base + j * g >= r ? 1 : 0)) * g;
-          PackT xin = ld_win(rc.win[p] + woff, off, true);
+      }
+      // widths beyond PB+1: further batches of PB peers, again all loads of a batch before its adds
+      for (int j0 = PB; j0 < npeers; j0 += PB) {
 #pragma unroll
-          for (int i = 0; i < VE; ++i) acc[i] = Op::apply(acc[i], EL::up(xin.e[i]));
+        for (int u = 0; u < UNR; ++u) {
+          if (!nv[u]) continue;
+#pragma unroll
+          for (int j = 0; j < PB; ++j)
+            if (j0 + j < npeers) in[u][j] = ld_win(rs_peer_ptr(k, j0 + j), off[u], true);
         }
+#pragma unroll
+        for (int u = 0; u < UNR; ++u) {
+          if (!nv[u]) continue;
+#pragma unroll
+          for (int j = 0; j < PB; ++j) {
+            if (j0 + j < npeers) {
+#pragma unroll
+              for (int i = 0; i < VE; ++i) acc[u][i] = Op::apply(acc[u][i], EL::up(in[u][j].e[i]));
+            }
+          }
+        }
+      }
+#pragma unroll
+      for (int u = 0; u < UNR; ++u) {
+        if (!nv[u]) continue;
         PackT o;
 #pragma unroll
-        for (int i = 0; i < VE; ++i) o.e[i] = EL::down(acc[i]);
-        st_win(wr, off, o);
+        for (int i = 0; i < VE; ++i) o.e[i] = EL::down(acc[u][i]);
+        st_win(wr, off[u], o);
       }
     }
   }
@@ -296,32 +327,30 @@ struct StagedCta {
     // In registered mode recv aliases my window: my own blocks are already in place unless the
     // epilogue changes them.
     const bool self_needed = last && !(a.mode == MODE_REGISTERED && kRawIO && !(EL::is_float && a.apply_scale));
-    const long long per_src = (long long)nb * CV;
-    const long long total = per_src * w;
+    const int total = nb * CV * w;
     char* wr = rc.win[r] + woff;
     IO* y = (IO*)rc.recv;
     const int nth = be.nthr(), tid = be.tid();
 
-    for (long long q0 = 0; q0 < total; q0 += (long long)nth * UNR) {
+    for (int q0 = 0; q0 < total; q0 += nth * UNR) {
       PackT v[UNR];
       long long el[UNR];
       int nv[UNR];
 #pragma unroll
       for (int u = 0; u < UNR; ++u) {
-        long long q = q0 + (long long)u * nth + tid;
+        const int q = q0 + u * nth + tid;
         nv[u] = 0;
         if (q < total) {
           // vector index fastest, then source, then block group: neighbouring CV-runs hit different peers
-          int vi = (int)(q % CV);
-          long long rest = q / CV;
-          int s = (int)(rest % w), bi = (int)(rest / w);
-          int p = base + s * g;
+          const int rest = q / CV, vi = q - rest * CV;
+          const int bi = rest / w, s = rest - bi * w;
+          const int p = base + s * g;
           if (p != r || self_needed) {
-            long long b = (p % gn) + (long long)bi * gn;
-            long long start, n = tile_valid(b, t, &start) - (long long)vi * VE;
+            long long start;
+            const int n = tile_valid32((p % gn) + bi * gn, t, &start) - vi * VE;
             if (n > 0) {
-              nv[u] = n < VE ? (int)n : VE;
-              el[u] = start + (long long)vi * VE;
+              nv[u] = n < VE ? n : VE;
+              el[u] = start + vi * VE;
               v[u] = ld_win(rc.win[p] + woff, el[u] * (long long)sizeof(T), p != r);
             }
           }
@@ -342,24 +371,25 @@ struct StagedCta {
     const Layout& L = a.lay;
     const int N = a.plan.nranks;
     const int CV = (int)((L.tile + VE - 1) / VE);
-    const long long total = (long long)N * CV;
+    const int total = N * CV;
     const IO* x = (const IO*)rc.send;
     char* wr = rc.win[r] + woff;
     const int nth = be.nthr(), tid = be.tid();
-    for (long long q0 = 0; q0 < total; q0 += (long long)nth * UNR) {
+    for (int q0 = 0; q0 < total; q0 += nth * UNR) {
       PackIO v[UNR];
       long long el[UNR];
       int nv[UNR];
 #pragma unroll
       for (int u = 0; u < UNR; ++u) {
-        long long q = q0 + (long long)u * nth + tid;
+        const int q = q0 + u * nth + tid;
         nv[u] = 0;
         if (q < total) {
-          int b = (int)(q / CV), vi = (int)(q - (long long)b * CV);
-          long long start, n = tile_valid(b, t, &start) - (long long)vi * VE;
+          const int b = q / CV, vi = q - b * CV;
+          long long start;
+          const int n = tile_valid32(b, t, &start) - vi * VE;
           if (n > 0) {
-            nv[u] = n < VE ? (int)n : VE;
-            el[u] = start + (long long)vi * VE;
+            nv[u] = n < VE ? n : VE;
+            el[u] = start + vi * VE;
             v[u] = ld_user(x, el[u], nv[u]);
           }
         }
@@ -401,25 +431,27 @@ struct StagedCta {
     const Layout& L = a.lay;
     const int N = a.plan.nranks;
     const int CV = (int)((L.tile + VE - 1) / VE);
-    const long long total = (long long)N * CV;
+    const int total = N * CV;
     IO* y = (IO*)rc.recv;
     const char* wr = rc.win[r] + woff;
     const int nth = be.nthr(), tid = be.tid();
-    for (long long q0 = 0; q0 < total; q0 += (long long)nth * UNR) {
+    for (int q0 = 0; q0 < total; q0 += nth * UNR) {
       PackT v[UNR];
       long long el[UNR];
       int nv[UNR];
 #pragma unroll
       for (int u = 0; u < UNR; ++u) {
-        long long q = q0 + (long long)u * nth + tid;
+        const int q = q0 + u * nth + tid;
         nv[u] = 0;
         if (q < total) {
-          int b = (int)(q / CV), vi = (int)(q - (long long)b * CV);
-          long long start, n = tile_valid(b, t, &start) - (long long)vi * VE;
+          const int b = q / CV, vi = q - b * CV;
+          long long start;
+          const int n = tile_valid32(b, t, &start) - vi * VE;
           if (n > 0) {
-            nv[u] = n < VE ? (int)n : VE;
-            el[u] = start + (long long)vi * VE;
-            v[u] = ld_win(wr, el[u] * (long long)sizeof(T), false);
+            nv[u] = n < VE ? n : VE;
+            el[u] = start + vi * VE;
+            // written by the peers' multimem.st: read around L1
+            v[u] = ld_win(wr, el[u] * (long long)sizeof(T), true);
           }
         }
       }
@@ -685,12 +717,16 @@ struct StagedCta {
   template <int UNR_DUMMY = 0> FT_DEV void rs_dispatch(int k, int t) {
     const int w = a.plan.width[k];
     if constexpr (VE == 1) {
-      rs_tile<1, 8>(k, t);
+      rs_tile<1, 4>(k, t);
     } else {
-      if (w == 2) rs_tile<4, 1>(k, t);
-      else if (w == 3) rs_tile<4, 2>(k, t);
-      else if (w <= 5) rs_tile<2, 4>(k, t);
-      else rs_tile<1, 8>(k, t);
+#if defined(FT_PROBE) && FT_PROBE == 1
+      rs_tile<4, 1>(k, t);
+#elif defined(FT_PROBE) && FT_PROBE == 2
+      rs_tile<2, 4>(k, t);
+#else
+      if (w == 2) rs_tile<4, 1>(k, t);   // one peer: more vectors per thread instead
+      else rs_tile<2, 4>(k, t);
+#endif
     }
   }
 

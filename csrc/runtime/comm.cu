@@ -1,0 +1,843 @@
+// Communicator + collective entry points (the C API of include/flextree.h).
+//
+// Capability parity: MPI_Allreduce_FT / MPI_Allreduce (allreduce_over_mpi/mpi_mod.hpp:1167-1221):
+// context sizing (:216-243), N<=1 copy fast path (:1181-1188), grow-only staging buffer (:932-950,
+// :1190), stage vector from FT_TOPO (:882-929, :1191), tree vs ring selection (:1194-1215).
+// Additions: algorithm selection by the fitted link model, zero-copy registered buffers, one-shot and
+// NVLS paths, fused scale/cast, device watchdog, CUDA-graph-safe epochs.
+#include <cuda_runtime.h>
+#include <stdio.h>
+#include <stdlib.h>
+#include <string.h>
+
+#include <memory>
+#include <mutex>
+#include <string>
+#include <vector>
+
+#include "../../include/flextree.h"
+#include "../core/comm_dev.h"
+#include "../core/dispatch.h"
+#include "../core/types.h"
+#include "../kernels/launch.h"
+#include "../planner/cost_model.h"
+#include "../planner/factorize.h"
+#include "symm.h"
+
+namespace ft {
+void set_last_error(const std::string& s);  // planner/c_api.cc
+}
+using namespace ft;
+
+struct ft_link_model { LinkModel m; };
+
+namespace {
+
+enum CommKind { COMM_PROCESS = 0, COMM_LOCAL = 1, COMM_EMULATED = 2 };
+
+int env_int(const char* name, int dflt) {
+  const char* v = getenv(name);
+  return (v && *v) ? atoi(v) : dflt;
+}
+long long env_ll(const char* name, long long dflt) {
+  const char* v = getenv(name);
+  return (v && *v) ? atoll(v) : dflt;
+}
+int log_level() {
+  static int lvl = [] {
+    const char* v = getenv("FT_LOG_LEVEL");
+    if (!v) return 0;
+    if (!strcmp(v, "debug")) return 2;
+    if (!strcmp(v, "info")) return 1;
+    return atoi(v);
+  }();
+  return lvl;
+}
+#define FT_LOG(lvl, ...)                                   \
+  do {                                                     \
+    if (log_level() >= (lvl)) {                            \
+      fprintf(stderr, "[flextree] " __VA_ARGS__);          \
+      fprintf(stderr, "\n");                               \
+    }                                                      \
+  } while (0)
+
+// State shared by the comms of one ft_comm_create_local() group: segments are (re)allocated for the
+// whole group by whichever member asks first.
+struct LocalGroup {
+  std::vector<int> devices;
+  std::vector<struct ft_comm*> members;
+  std::mutex mu;
+};
+
+}  // namespace
+
+struct ft_comm {
+  CommKind kind = COMM_PROCESS;
+  int rank = 0, nranks = 1, device = 0;
+  int nlocal = 1;  // logical ranks served by this object (N for COMM_EMULATED)
+  Bootstrap bs;
+  std::shared_ptr<LocalGroup> group;
+  SymmOptions sopt;
+
+  // per logical rank (size nlocal): views of the symmetric segments
+  std::vector<Segment> pad, ll, win;
+  size_t window_bytes = 0;  // per parity
+  size_t ll_bytes = 0;      // per parity
+  struct UserSeg {
+    std::vector<Segment> seg;  // per logical rank
+    size_t bytes;
+  };
+  std::vector<UserSeg> user;
+  size_t local_alloc_cursor = 0;  // COMM_LOCAL: which user segment the next ft_symm_alloc returns
+
+  CommDev* d_comm = nullptr;       // [nlocal]
+  uint64_t* d_epoch = nullptr;     // [nlocal]
+  unsigned* d_done = nullptr;      // [nlocal]
+  unsigned* d_err = nullptr;       // [nlocal]
+
+  // policy
+  std::vector<int> widths_override;
+  int algo_override = ALGO_AUTO;
+  LinkModel model;
+  int ctas_override = 0, threads_override = 0;
+  long long tile_override = 0;
+  unsigned long long timeout_ns = 20000000000ull;
+  int sm_count = 148;
+  ft_call_info_t last{};
+};
+
+namespace {
+
+bool fail(ft_result_t* out, ft_result_t code, const std::string& msg) {
+  set_last_error(msg);
+  FT_LOG(1, "error: %s", msg.c_str());
+  *out = code;
+  return false;
+}
+#define FT_CHECK_RT(call)                                                                   \
+  do {                                                                                      \
+    cudaError_t _e = (call);                                                                \
+    if (_e != cudaSuccess) {                                                                \
+      set_last_error(std::string(#call) + ": " + cudaGetErrorString(_e));                   \
+      (void)cudaGetLastError();                                                             \
+      return FT_ERR_CUDA;                                                                   \
+    }                                                                                       \
+  } while (0)
+
+void apply_options(ft_comm* c, const ft_comm_options_t* o) {
+  ft_comm_options_t d;
+  ft_comm_options_default(&d);
+  if (o) d = *o;
+  c->window_bytes = d.window_bytes ? d.window_bytes : (size_t)env_ll("FT_WINDOW_BYTES", 64ll << 20);
+  c->ll_bytes = d.ll_bytes ? d.ll_bytes : (size_t)env_ll("FT_LL_BYTES", 4ll << 20);
+  c->window_bytes = (c->window_bytes + 4095) & ~(size_t)4095;
+  c->ll_bytes = (c->ll_bytes + 4095) & ~(size_t)4095;
+  int mc = d.use_multicast;
+  if (getenv("FT_MULTICAST")) mc = atoi(getenv("FT_MULTICAST"));
+  c->sopt.try_multicast = mc != 0;
+  c->sopt.require_multicast = mc == 1;
+  int vmm = d.use_vmm;
+  if (getenv("FT_SYMM")) vmm = strcmp(getenv("FT_SYMM"), "ipc") ? 1 : 0;
+  c->sopt.try_vmm = vmm != 0;
+  double t = d.timeout_s;
+  if (t < 0) t = getenv("FT_TIMEOUT_S") ? atof(getenv("FT_TIMEOUT_S")) : 20.0;
+  c->timeout_ns = (unsigned long long)(t * 1e9);
+  const char* cm = getenv("FT_COSTMODEL");
+  if (cm && *cm) {
+    std::string err;
+    if (!load_link_model(cm, &c->model, &err)) FT_LOG(1, "FT_COSTMODEL: %s", err.c_str());
+  }
+  const char* al = getenv("FT_ALGO");
+  if (al && *al) {
+    int a = algo_from_name(al);
+    if (a >= 0) c->algo_override = a;
+  }
+}
+
+// Device-side CommDev for every logical rank; requires pad/ll segments.
+ft_result_t upload_comm_dev(ft_comm* c) {
+  const int L = c->nlocal;
+  FT_CHECK_RT(cudaSetDevice(c->device));
+  FT_CHECK_RT(cudaMalloc(&c->d_comm, sizeof(CommDev) * (size_t)L));
+  FT_CHECK_RT(cudaMalloc(&c->d_epoch, sizeof(uint64_t) * (size_t)L));
+  FT_CHECK_RT(cudaMalloc(&c->d_done, sizeof(unsigned) * (size_t)L));
+  FT_CHECK_RT(cudaMalloc(&c->d_err, sizeof(unsigned) * (size_t)L));
+  FT_CHECK_RT(cudaMemset(c->d_epoch, 0, sizeof(uint64_t) * (size_t)L));
+  FT_CHECK_RT(cudaMemset(c->d_done, 0, sizeof(unsigned) * (size_t)L));
+  FT_CHECK_RT(cudaMemset(c->d_err, 0, sizeof(unsigned) * (size_t)L));
+  std::vector<CommDev> h((size_t)L);
+  for (int l = 0; l < L; ++l) {
+    CommDev& d = h[(size_t)l];
+    memset(&d, 0, sizeof d);
+    d.rank = c->kind == COMM_EMULATED ? l : c->rank;
+    d.nranks = c->nranks;
+    for (int p = 0; p < c->nranks; ++p) {
+      d.pad[p] = (uint64_t*)c->pad[(size_t)l].base[(size_t)p];
+      d.ll[p] = c->ll[(size_t)l].base[(size_t)p];
+    }
+    d.epoch = c->d_epoch + l;
+    d.done = c->d_done + l;
+    d.err = c->d_err + l;
+    d.ll_bytes = c->ll_bytes;
+  }
+  FT_CHECK_RT(cudaMemcpy(c->d_comm, h.data(), sizeof(CommDev) * (size_t)L, cudaMemcpyHostToDevice));
+  cudaDeviceProp prop;
+  if (cudaGetDeviceProperties(&prop, c->device) == cudaSuccess) c->sm_count = prop.multiProcessorCount;
+  return FT_SUCCESS;
+}
+
+// (Re)allocate one kind of segment for this comm (COMM_PROCESS) or the whole local group / emulation.
+bool make_segments(ft_comm* c, size_t bytes, std::vector<Segment>* out, std::string* err) {
+  if (c->kind == COMM_PROCESS) {
+    out->assign(1, Segment());
+    return segment_create(c->bs, c->device, bytes, c->sopt, &(*out)[0], err);
+  }
+  if (c->kind == COMM_EMULATED) {
+    std::vector<int> devs((size_t)c->nranks, c->device);
+    return segment_create_local(devs, bytes, out, err);
+  }
+  return false;  // COMM_LOCAL handled by the group helpers
+}
+
+void destroy_segments(std::vector<Segment>* v) {
+  for (auto& s : *v) segment_destroy(&s);
+  v->clear();
+}
+
+ft_result_t grow_window(ft_comm* c, size_t need_per_parity) {
+  if (need_per_parity <= c->window_bytes && !c->win.empty()) return FT_SUCCESS;
+  size_t nb = c->window_bytes;
+  while (nb < need_per_parity) nb *= 2;
+  nb = (nb + 4095) & ~(size_t)4095;
+  FT_LOG(1, "rank %d: staging window -> %zu bytes per parity", c->rank, nb);
+  std::string err;
+  if (c->kind == COMM_LOCAL) {
+    std::lock_guard<std::mutex> lk(c->group->mu);
+    bool need = false;
+    for (auto* m : c->group->members) need = need || m->win.empty() || m->window_bytes < need_per_parity;
+    if (!need) return FT_SUCCESS;
+    for (auto* m : c->group->members) {
+      cudaSetDevice(m->device);
+      cudaDeviceSynchronize();
+    }
+    std::vector<Segment> segs;
+    if (!segment_create_local(c->group->devices, 2 * nb, &segs, &err)) {
+      set_last_error(err);
+      return FT_ERR_CUDA;
+    }
+    for (size_t i = 0; i < c->group->members.size(); ++i) {
+      ft_comm* m = c->group->members[i];
+      destroy_segments(&m->win);
+      m->win.assign(1, segs[i]);
+      m->window_bytes = nb;
+    }
+    cudaSetDevice(c->device);
+    return FT_SUCCESS;
+  }
+  FT_CHECK_RT(cudaSetDevice(c->device));
+  FT_CHECK_RT(cudaDeviceSynchronize());
+  if (c->kind == COMM_PROCESS && !c->bs.barrier()) {
+    set_last_error("bootstrap barrier failed");
+    return FT_ERR_INTERNAL;
+  }
+  std::vector<Segment> segs;
+  if (!make_segments(c, 2 * nb, &segs, &err)) {
+    set_last_error(err);
+    return FT_ERR_CUDA;
+  }
+  destroy_segments(&c->win);
+  c->win = segs;
+  c->window_bytes = nb;
+  return FT_SUCCESS;
+}
+
+// Find the user (registered) segment containing [p, p+bytes) for logical rank l.
+int find_user_seg(const ft_comm* c, int l, const void* p, size_t bytes, size_t* off) {
+  for (size_t i = 0; i < c->user.size(); ++i) {
+    const Segment& s = c->user[i].seg[(size_t)l];
+    const char* b = s.base[(size_t)s.self];
+    if ((const char*)p >= b && (const char*)p + bytes <= b + s.bytes) {
+      *off = (size_t)((const char*)p - b);
+      return (int)i;
+    }
+  }
+  return -1;
+}
+
+struct Shape {
+  int ctas, threads;
+  long long tile_bytes;
+};
+
+// Launch shape heuristics (re-tuned from measurements; see docs/TUNING.md). Every rank must derive
+// the same shape from the same arguments.
+Shape pick_shape(const ft_comm* c, int algo, size_t msg_bytes, int nranks, int esize) {
+  Shape s;
+  s.threads = c->threads_override ? c->threads_override : env_int("FT_THREADS", 512);
+  if (s.threads > FT_MAX_THREADS) s.threads = FT_MAX_THREADS;
+  if (s.threads < 32) s.threads = 32;
+  int ctas;
+  if (msg_bytes <= (64u << 10)) ctas = 4;
+  else if (msg_bytes <= (1u << 20)) ctas = 16;
+  else if (msg_bytes <= (16u << 20)) ctas = 32;
+  else ctas = 64;
+  if (algo == ALGO_ONESHOT) {
+    // one LL line (8 payload bytes) per thread
+    long long lines = ((long long)msg_bytes + 7) / 8;
+    ctas = (int)((lines + s.threads - 1) / s.threads);
+    if (ctas > 32) ctas = 32;
+  }
+  ctas = c->ctas_override ? c->ctas_override : env_int("FT_CTAS", ctas);
+  if (ctas < 1) ctas = 1;
+  if (ctas > FT_MAX_CTAS) ctas = FT_MAX_CTAS;
+  if (c->kind == COMM_EMULATED) {
+    // cooperative launch: nranks*ctas CTAs must be co-resident (1 CTA of 512 threads / SM worst case)
+    int per_sm = s.threads <= 256 ? 2 : 1;
+    int cap = c->sm_count * per_sm / nranks;
+    if (cap < 1) cap = 1;
+    if (ctas > cap) ctas = cap;
+  }
+  s.ctas = ctas;
+  long long block_bytes = ((long long)msg_bytes + nranks - 1) / nranks;
+  long long tile = c->tile_override ? c->tile_override : env_ll("FT_TILE_BYTES", 0);
+  if (tile <= 0) {
+    // aim for >= 4 tiles per CTA so that stages pipeline, within [4 KiB, 64 KiB] per block-chunk
+    tile = block_bytes / ((long long)ctas * 4);
+    if (tile > (64 << 10)) tile = 64 << 10;
+    if (tile < (4 << 10)) tile = 4 << 10;
+  }
+  tile = (tile + 15) / 16 * 16;
+  if (tile < esize) tile = esize;
+  s.tile_bytes = tile;
+  return s;
+}
+
+ft_result_t check_device_error(ft_comm* c) {
+  // non-blocking peek is impossible without a sync; callers use ft_comm_error() explicitly
+  (void)c;
+  return FT_SUCCESS;
+}
+
+// The one place a collective is resolved and launched. send/recv: per logical rank.
+ft_result_t do_allreduce(ft_comm* c, const void* const* send, void* const* recv, size_t count, int io_dtype,
+                         int wire_dtype, int op, double scale, cudaStream_t stream) {
+  const int N = c->nranks, L = c->nlocal;
+  if (io_dtype < 0 || io_dtype >= DT_COUNT || wire_dtype < 0 || wire_dtype >= DT_COUNT) {
+    set_last_error("bad dtype");
+    return FT_ERR_INVALID;
+  }
+  if (!op_supported(op, wire_dtype)) {
+    set_last_error(std::string("unsupported op/dtype: ") + op_name(op) + " on " + dtype_name(wire_dtype));
+    return FT_ERR_UNSUPPORTED;
+  }
+  if (io_dtype != wire_dtype && !(io_dtype == DT_FLOAT && (wire_dtype == DT_BFLOAT16 || wire_dtype == DT_HALF))) {
+    set_last_error("only fp32 user buffers with a bf16/fp16 wire are supported as a mixed format");
+    return FT_ERR_UNSUPPORTED;
+  }
+  if (count == 0) return FT_SUCCESS;
+  FT_CHECK_RT(cudaSetDevice(c->device));
+  const int es = dtype_size(wire_dtype), ios = dtype_size(io_dtype);
+  const bool is_float = dtype_is_float(wire_dtype);
+  const bool apply_scale = is_float && scale != 1.0;
+  const size_t msg_bytes = count * (size_t)es;
+
+  std::vector<const void*> s((size_t)L);
+  std::vector<void*> r((size_t)L);
+  bool vec = true, in_place = true;
+  for (int l = 0; l < L; ++l) {
+    r[(size_t)l] = recv[l];
+    s[(size_t)l] = (send[l] == FT_IN_PLACE || send[l] == nullptr) ? recv[l] : send[l];
+    if (!r[(size_t)l]) { set_last_error("null recvbuf"); return FT_ERR_INVALID; }
+    vec = vec && ((uintptr_t)s[(size_t)l] % 16 == 0) && ((uintptr_t)r[(size_t)l] % 16 == 0);
+    in_place = in_place && s[(size_t)l] == r[(size_t)l];
+  }
+
+  // ---- N == 1: copy fast path (mpi_mod.hpp:1181-1188) ---------------------------------------------
+  // (a scaled / casting single-rank call still goes through the one-shot kernel below)
+  if (N == 1 && !apply_scale && io_dtype == wire_dtype) {
+    if (!in_place) FT_CHECK_RT(cudaMemcpyAsync(r[0], s[0], count * (size_t)ios, cudaMemcpyDeviceToDevice, stream));
+    c->last = ft_call_info_t{};
+    c->last.algo = ALGO_STAGED;
+    c->last.nstages = 1;
+    c->last.widths[0] = 1;
+    return FT_SUCCESS;
+  }
+
+  // ---- registered (zero-copy) mode? -------------------------------------------------------------------
+  int mode = MODE_STAGING;
+  int useg = -1;
+  size_t uoff = 0;
+  if (in_place && !apply_scale && io_dtype == wire_dtype && vec && N > 1) {
+    useg = find_user_seg(c, 0, r[0], count * (size_t)ios, &uoff);
+    for (int l = 1; l < L && useg >= 0; ++l) {
+      size_t o2 = 0;
+      if (find_user_seg(c, l, r[(size_t)l], count * (size_t)ios, &o2) != useg || o2 != uoff) useg = -1;
+    }
+    if (useg >= 0 && uoff % 16 == 0 && env_int("FT_REGISTERED", 1)) mode = MODE_REGISTERED;
+  }
+
+  // ---- algorithm + widths --------------------------------------------------------------------------------
+  int algo = c->algo_override;
+  std::vector<int> widths = c->widths_override;
+  if (widths.empty() && getenv("FT_TOPO") && *getenv("FT_TOPO")) {
+    int buf[FT_MAX_STAGES + 8];
+    int k = ft_parse_topo(nullptr, N, buf, FT_MAX_STAGES + 8);
+    if (k < 0) return FT_ERR_INVALID;  // product mismatch: the reference exits (mpi_mod.hpp:914-918)
+    widths.assign(buf, buf + k);
+  }
+  if (!widths.empty() && widths[0] == 1 && N > 1) {  // "any 1 means ring" (mpi_mod.hpp:907-910)
+    algo = ALGO_RING;
+    widths.clear();
+  }
+  // Is a multicast mapping available for the buffer this call would use? (The staging window is
+  // allocated lazily, so before its first use we go by the creation-time probe.)
+  bool has_mc;
+  if (mode == MODE_REGISTERED) has_mc = c->user[(size_t)useg].seg[0].mc_base != nullptr;
+  else if (!c->win.empty()) has_mc = c->win[0].mc_base != nullptr;
+  else has_mc = c->model.has_nvls;
+  double est = 0;
+  if (algo == ALGO_AUTO) {
+    if (!widths.empty()) {
+      algo = ALGO_STAGED;
+    } else {
+      LinkModel m = c->model;
+      m.has_nvls = m.has_nvls && has_mc && nvls_supported(wire_dtype, op) && vec;
+      if (N > 1 && (size_t)((msg_bytes + 7) / 8 * 16) > ((c->ll_bytes / (size_t)N) & ~(size_t)15)) m.max_oneshot_bytes = 0;
+      Choice ch = choose(m, N, (double)msg_bytes, mode == MODE_REGISTERED, FT_MAX_WIDTH);
+      algo = ch.algo;
+      widths = ch.widths;
+      est = ch.est_us;
+    }
+  }
+  if (N == 1) algo = ALGO_ONESHOT;
+  if (algo == ALGO_NVLS && !(nvls_supported(wire_dtype, op) && vec)) {
+    set_last_error("NVLS path supports fp32/bf16/fp16 SUM on 16-byte aligned buffers only");
+    return FT_ERR_UNSUPPORTED;
+  }
+  if (algo == ALGO_STAGED && widths.empty()) widths = {N};
+  if (algo != ALGO_STAGED) widths = {N};
+
+  StagedArgs a;
+  memset(&a, 0, sizeof a);
+  if (!make_plan(widths.data(), (int)widths.size(), &a.plan) || a.plan.nranks != N) {
+    set_last_error("stage widths " + to_string(widths) + " do not multiply to the world size " + std::to_string(N));
+    return FT_ERR_INVALID;
+  }
+  if (algo == ALGO_RING && mode == MODE_REGISTERED && (apply_scale || io_dtype != wire_dtype)) mode = MODE_STAGING;
+
+  Shape sh = pick_shape(c, algo, msg_bytes, N, es);
+  a.lay = make_layout((long long)count, N, es, sh.tile_bytes, vec);
+  // flag values encode the tile ordinal in FT_EPOCH_SHIFT bits (ring: steps * tiles)
+  {
+    long long per_cta = (a.lay.ntiles + sh.ctas - 1) / sh.ctas;
+    long long steps = algo == ALGO_RING ? 2LL * N : 1;
+    while (per_cta * steps >= (1LL << FT_EPOCH_SHIFT) - 2) {
+      sh.tile_bytes *= 2;
+      a.lay = make_layout((long long)count, N, es, sh.tile_bytes, vec);
+      per_cta = (a.lay.ntiles + sh.ctas - 1) / sh.ctas;
+    }
+  }
+  if (sh.ctas > a.lay.ntiles && algo != ALGO_ONESHOT) sh.ctas = a.lay.ntiles;
+
+  // ---- memory --------------------------------------------------------------------------------------------
+  if (algo == ALGO_ONESHOT) {
+    size_t region = (c->ll_bytes / (size_t)N) & ~(size_t)15;
+    size_t lines = (msg_bytes + 7) / 8;
+    if (N > 1 && lines * 16 > region) {
+      set_last_error("message too large for the one-shot (LL) buffer; raise ll_bytes / FT_LL_BYTES");
+      return FT_ERR_INVALID;
+    }
+  } else if (mode == MODE_STAGING) {
+    size_t need = (size_t)a.lay.block * (size_t)N * (size_t)es;
+    cudaStreamCaptureStatus cap = cudaStreamCaptureStatusNone;
+    cudaStreamIsCapturing(stream, &cap);
+    if (need > c->window_bytes || c->win.empty()) {
+      if (cap != cudaStreamCaptureStatusNone) {
+        set_last_error("staging window too small during stream capture: call ft_comm_reserve() first");
+        return FT_ERR_INVALID;
+      }
+      ft_result_t rr = grow_window(c, need);
+      if (rr != FT_SUCCESS) return rr;
+    }
+  }
+  if (algo == ALGO_NVLS) {
+    const char* mc = mode == MODE_REGISTERED ? c->user[(size_t)useg].seg[0].mc_base : c->win[0].mc_base;
+    if (!mc) {
+      if (c->algo_override == ALGO_NVLS) {
+        set_last_error(c->kind == COMM_EMULATED ? "NVLS cannot be emulated on one GPU"
+                                                : "NVLS requested but this communicator has no multicast mapping");
+        return FT_ERR_UNSUPPORTED;
+      }
+      algo = ALGO_STAGED;  // multicast bind failed when the window was created: use the P2P stages
+      c->model.has_nvls = false;
+    }
+  }
+
+  a.nlocal = L;
+  a.ctas = sh.ctas;
+  a.mode = mode;
+  a.apply_scale = apply_scale ? 1 : 0;
+  a.scale = scale;
+  a.timeout_ns = c->timeout_ns;
+  if (mode == MODE_REGISTERED) {
+    a.win_off0 = (long long)uoff;
+    a.win_stride = 0;
+  } else {
+    a.win_off0 = 0;
+    a.win_stride = (long long)c->window_bytes;
+  }
+  for (int l = 0; l < L; ++l) {
+    RankCall& rc = a.rc[l];
+    rc.comm = c->d_comm + l;
+    rc.send = s[(size_t)l];
+    rc.recv = r[(size_t)l];
+    const Segment* seg = nullptr;
+    if (algo != ALGO_ONESHOT) seg = mode == MODE_REGISTERED ? &c->user[(size_t)useg].seg[(size_t)l] : &c->win[(size_t)l];
+    rc.win = seg ? seg->d_table : nullptr;
+    rc.mc = seg ? seg->mc_base : nullptr;
+  }
+
+  LaunchCtx ctx;
+  ctx.args = &a;
+  ctx.algo = algo;
+  ctx.threads = sh.threads;
+  ctx.cooperative = c->kind == COMM_EMULATED && N > 1;
+  ctx.stream = stream;
+  if (!cuda_launch(wire_dtype, io_dtype, op, vec, &ctx) || !ctx.supported) {
+    set_last_error(std::string("no kernel for ") + op_name(op) + "/" + dtype_name(wire_dtype) + "/" + algo_name(algo));
+    return FT_ERR_UNSUPPORTED;
+  }
+  if (ctx.err != cudaSuccess) {
+    set_last_error(std::string("kernel launch: ") + cudaGetErrorString(ctx.err));
+    (void)cudaGetLastError();
+    return FT_ERR_CUDA;
+  }
+  ft_call_info_t& li = c->last;
+  li = ft_call_info_t{};
+  li.algo = algo;
+  li.nstages = a.plan.nstages;
+  for (int k = 0; k < a.plan.nstages && k < 8; ++k) li.widths[k] = a.plan.width[k];
+  li.ctas = sh.ctas;
+  li.threads = sh.threads;
+  li.tile_bytes = a.lay.tile * es;
+  li.mode = mode;
+  li.vectorized = vec;
+  li.est_us = est;
+  FT_LOG(2, "rank %d allreduce count=%zu %s/%s algo=%s widths=%s ctas=%d tile=%lld mode=%d", c->rank, count,
+         dtype_name(wire_dtype), op_name(op), algo_name(algo), to_string(widths).c_str(), sh.ctas, li.tile_bytes, mode);
+  return check_device_error(c);
+}
+
+ft_result_t finish_create(ft_comm* c) {
+  // pads + LL buffers exist now; window is allocated lazily at first use (or ft_comm_reserve)
+  return upload_comm_dev(c);
+}
+
+}  // namespace
+
+extern "C" {
+
+void ft_comm_options_default(ft_comm_options_t* o) {
+  o->window_bytes = 0;
+  o->ll_bytes = 0;
+  o->use_multicast = -1;
+  o->use_vmm = -1;
+  o->timeout_s = -1.0;
+}
+
+ft_result_t ft_comm_create(ft_comm_t** out, int rank, int nranks, int device, ft_allgather_fn ag, void* ag_ctx,
+                           const ft_comm_options_t* opts) {
+  ft_result_t rc = FT_SUCCESS;
+  if (!out || nranks < 1 || nranks > FT_MAX_RANKS || rank < 0 || rank >= nranks || (nranks > 1 && !ag)) {
+    fail(&rc, FT_ERR_INVALID, "ft_comm_create: bad arguments");
+    return rc;
+  }
+  auto* c = new ft_comm;
+  c->kind = COMM_PROCESS;
+  c->rank = rank;
+  c->nranks = nranks;
+  c->device = device;
+  c->nlocal = 1;
+  c->bs.rank = rank;
+  c->bs.nranks = nranks;
+  c->bs.fn = ag;
+  c->bs.ctx = ag_ctx;
+  apply_options(c, opts);
+  std::string err;
+  c->pad.assign(1, Segment());
+  c->ll.assign(1, Segment());
+  SymmOptions nomc = c->sopt;
+  nomc.try_multicast = false;
+  nomc.require_multicast = false;
+  if (!segment_create(c->bs, device, FT_PAD_BYTES, nomc, &c->pad[0], &err) ||
+      !segment_create(c->bs, device, 2 * c->ll_bytes, nomc, &c->ll[0], &err)) {
+    fail(&rc, FT_ERR_CUDA, "ft_comm_create: " + err);
+    delete c;
+    return rc;
+  }
+  rc = finish_create(c);
+  if (rc != FT_SUCCESS) { delete c; return rc; }
+  // probe multicast once so that the model knows whether NVLS exists (window itself is lazy)
+  c->model.has_nvls = c->sopt.try_multicast && device_supports_multicast(device) && c->pad[0].kind == SEG_VMM && nranks > 1;
+  FT_LOG(1, "rank %d/%d on device %d: segments via %s, multicast %s", rank, nranks, device,
+         c->pad[0].kind == SEG_VMM ? "VMM" : "cudaIpc", c->model.has_nvls ? "available" : "off");
+  *out = c;
+  return FT_SUCCESS;
+}
+
+ft_result_t ft_comm_create_local(ft_comm_t** comms, int nranks, const int* devices, const ft_comm_options_t* opts) {
+  ft_result_t rc = FT_SUCCESS;
+  if (!comms || nranks < 1 || nranks > FT_MAX_RANKS || !devices) {
+    fail(&rc, FT_ERR_INVALID, "ft_comm_create_local: bad arguments");
+    return rc;
+  }
+  auto group = std::make_shared<LocalGroup>();
+  group->devices.assign(devices, devices + nranks);
+  std::vector<Segment> pads, lls;
+  std::string err;
+  std::vector<ft_comm*> made;
+  for (int i = 0; i < nranks; ++i) {
+    auto* c = new ft_comm;
+    c->kind = COMM_LOCAL;
+    c->rank = i;
+    c->nranks = nranks;
+    c->device = devices[i];
+    c->nlocal = 1;
+    c->group = group;
+    apply_options(c, opts);
+    made.push_back(c);
+  }
+  group->members = made;
+  if (!segment_create_local(group->devices, FT_PAD_BYTES, &pads, &err) ||
+      !segment_create_local(group->devices, 2 * made[0]->ll_bytes, &lls, &err)) {
+    fail(&rc, FT_ERR_CUDA, "ft_comm_create_local: " + err);
+    for (auto* c : made) delete c;
+    return rc;
+  }
+  for (int i = 0; i < nranks; ++i) {
+    made[(size_t)i]->pad.assign(1, pads[(size_t)i]);
+    made[(size_t)i]->ll.assign(1, lls[(size_t)i]);
+    rc = finish_create(made[(size_t)i]);
+    if (rc != FT_SUCCESS) return rc;
+    made[(size_t)i]->model.has_nvls = false;
+    comms[i] = made[(size_t)i];
+  }
+  return FT_SUCCESS;
+}
+
+ft_result_t ft_comm_create_emulated(ft_comm_t** out, int nranks, int device, const ft_comm_options_t* opts) {
+  ft_result_t rc = FT_SUCCESS;
+  if (!out || nranks < 1 || nranks > FT_MAX_LOCAL) {
+    fail(&rc, FT_ERR_INVALID, "ft_comm_create_emulated: nranks must be in [1, 32]");
+    return rc;
+  }
+  auto* c = new ft_comm;
+  c->kind = COMM_EMULATED;
+  c->rank = 0;
+  c->nranks = nranks;
+  c->device = device;
+  c->nlocal = nranks;
+  apply_options(c, opts);
+  std::string err;
+  if (!make_segments(c, FT_PAD_BYTES, &c->pad, &err) || !make_segments(c, 2 * c->ll_bytes, &c->ll, &err)) {
+    fail(&rc, FT_ERR_CUDA, "ft_comm_create_emulated: " + err);
+    delete c;
+    return rc;
+  }
+  rc = finish_create(c);
+  if (rc != FT_SUCCESS) { delete c; return rc; }
+  c->model.has_nvls = false;
+  *out = c;
+  return FT_SUCCESS;
+}
+
+ft_result_t ft_comm_destroy(ft_comm_t* c) {
+  if (!c) return FT_SUCCESS;
+  cudaSetDevice(c->device);
+  cudaDeviceSynchronize();
+  if (c->kind == COMM_PROCESS) c->bs.barrier();
+  destroy_segments(&c->win);
+  destroy_segments(&c->pad);
+  destroy_segments(&c->ll);
+  for (auto& u : c->user) destroy_segments(&u.seg);
+  if (c->d_comm) cudaFree(c->d_comm);
+  if (c->d_epoch) cudaFree(c->d_epoch);
+  if (c->d_done) cudaFree(c->d_done);
+  if (c->d_err) cudaFree(c->d_err);
+  (void)cudaGetLastError();
+  if (c->group) {
+    std::lock_guard<std::mutex> lk(c->group->mu);
+    for (auto& m : c->group->members)
+      if (m == c) m = nullptr;
+    std::vector<ft_comm*> keep;
+    for (auto* m : c->group->members)
+      if (m) keep.push_back(m);
+    c->group->members = keep;
+  }
+  delete c;
+  return FT_SUCCESS;
+}
+
+int ft_comm_rank(const ft_comm_t* c) { return c->rank; }
+int ft_comm_size(const ft_comm_t* c) { return c->nranks; }
+int ft_comm_has_multicast(const ft_comm_t* c) { return c->model.has_nvls ? 1 : 0; }
+
+unsigned ft_comm_error(ft_comm_t* c) {
+  std::vector<unsigned> h((size_t)c->nlocal, 0);
+  cudaSetDevice(c->device);
+  if (cudaMemcpy(h.data(), c->d_err, sizeof(unsigned) * (size_t)c->nlocal, cudaMemcpyDeviceToHost) != cudaSuccess) {
+    (void)cudaGetLastError();
+    return 0xffffffffu;
+  }
+  for (unsigned e : h)
+    if (e) return e;
+  return 0;
+}
+ft_result_t ft_comm_clear_error(ft_comm_t* c) {
+  FT_CHECK_RT(cudaSetDevice(c->device));
+  FT_CHECK_RT(cudaMemset(c->d_err, 0, sizeof(unsigned) * (size_t)c->nlocal));
+  return FT_SUCCESS;
+}
+
+ft_result_t ft_comm_set_widths(ft_comm_t* c, const int* widths, int nstages) {
+  if (!widths || nstages <= 0) {
+    c->widths_override.clear();
+    return FT_SUCCESS;
+  }
+  std::vector<int> w(widths, widths + nstages);
+  bool ring = false;
+  for (int x : w) ring = ring || x == 1;
+  if (ring && c->nranks > 1) {
+    c->widths_override = {1};
+    return FT_SUCCESS;
+  }
+  Plan p;
+  if (!make_plan(w.data(), nstages, &p) || p.nranks != c->nranks) {
+    set_last_error("invalid widths " + to_string(w) + " for world size " + std::to_string(c->nranks));
+    return FT_ERR_INVALID;
+  }
+  c->widths_override = w;
+  return FT_SUCCESS;
+}
+ft_result_t ft_comm_set_algo(ft_comm_t* c, ft_algo_t algo) {
+  if ((int)algo < 0 || (int)algo > ALGO_RING) return FT_ERR_INVALID;
+  c->algo_override = (int)algo;
+  return FT_SUCCESS;
+}
+ft_result_t ft_comm_set_link_model(ft_comm_t* c, const ft_link_model_t* m) {
+  const bool probed = c->model.has_nvls;  // what the hardware/bootstrap allows
+  c->model = m ? m->m : LinkModel();
+  c->model.has_nvls = probed;
+  return FT_SUCCESS;
+}
+ft_result_t ft_comm_set_launch(ft_comm_t* c, int ctas, int threads, long long tile_bytes) {
+  if (ctas < 0 || ctas > FT_MAX_CTAS || threads < 0 || threads > FT_MAX_THREADS || (threads % 32) || tile_bytes < 0)
+    return FT_ERR_INVALID;
+  c->ctas_override = ctas;
+  c->threads_override = threads;
+  c->tile_override = tile_bytes;
+  return FT_SUCCESS;
+}
+
+ft_result_t ft_comm_reserve(ft_comm_t* c, size_t bytes) {
+  // room for the 16-byte block rounding of the widest split
+  size_t need = bytes + (size_t)c->nranks * 16 + 64;
+  return grow_window(c, need);
+}
+
+ft_result_t ft_symm_alloc(ft_comm_t* c, size_t bytes, void** ptr) {
+  if (!ptr || bytes == 0) return FT_ERR_INVALID;
+  size_t padded = ((bytes + 4095) & ~(size_t)4095) + 4096;  // tail pad: full-vector accesses stay inside
+  std::string err;
+  if (c->kind == COMM_LOCAL) {
+    std::lock_guard<std::mutex> lk(c->group->mu);
+    if (c->local_alloc_cursor == c->user.size()) {  // first member to ask allocates for everybody
+      std::vector<Segment> segs;
+      if (!segment_create_local(c->group->devices, padded, &segs, &err)) {
+        set_last_error(err);
+        return FT_ERR_CUDA;
+      }
+      for (size_t i = 0; i < c->group->members.size(); ++i) {
+        ft_comm::UserSeg u;
+        u.seg.assign(1, segs[i]);
+        u.bytes = bytes;
+        c->group->members[i]->user.push_back(u);
+      }
+    }
+    ft_comm::UserSeg& u = c->user[c->local_alloc_cursor++];
+    if (u.bytes != bytes) {
+      set_last_error("ft_symm_alloc: members of a local group must allocate in the same order and size");
+      return FT_ERR_INVALID;
+    }
+    *ptr = u.seg[0].base[(size_t)u.seg[0].self];
+    cudaSetDevice(c->device);
+    return FT_SUCCESS;
+  }
+  ft_comm::UserSeg u;
+  u.bytes = bytes;
+  if (!make_segments(c, padded, &u.seg, &err)) {
+    set_last_error(err);
+    return FT_ERR_CUDA;
+  }
+  c->user.push_back(u);
+  if (c->kind == COMM_EMULATED) {
+    // ptr[0..nranks): one buffer per logical rank
+    for (int l = 0; l < c->nlocal; ++l) ptr[l] = u.seg[(size_t)l].base[(size_t)l];
+  } else {
+    *ptr = u.seg[0].base[(size_t)c->rank];
+  }
+  return FT_SUCCESS;
+}
+
+ft_result_t ft_symm_free(ft_comm_t* c, void* ptr) {
+  for (size_t i = 0; i < c->user.size(); ++i) {
+    Segment& s = c->user[i].seg[0];
+    if (s.kind != SEG_NONE && s.base[(size_t)s.self] == (char*)ptr) {
+      cudaSetDevice(c->device);
+      cudaDeviceSynchronize();
+      if (c->kind == COMM_PROCESS) c->bs.barrier();
+      destroy_segments(&c->user[i].seg);
+      // keep the slot (indices are stable); mark as dead with an empty segment list per rank
+      c->user[i].seg.assign((size_t)c->nlocal, Segment());
+      for (auto& d : c->user[i].seg) { d.base.assign((size_t)c->nranks, nullptr); d.self = 0; d.bytes = 0; }
+      c->user[i].bytes = 0;
+      return FT_SUCCESS;
+    }
+  }
+  set_last_error("ft_symm_free: pointer was not returned by ft_symm_alloc");
+  return FT_ERR_INVALID;
+}
+
+ft_result_t ft_allreduce(const void* sendbuf, void* recvbuf, size_t count, ft_dtype_t dtype, ft_op_t op, ft_comm_t* comm,
+                         void* stream) {
+  return ft_allreduce_ex(sendbuf, recvbuf, count, dtype, dtype, op, 1.0, comm, stream);
+}
+
+ft_result_t ft_allreduce_ex(const void* sendbuf, void* recvbuf, size_t count, ft_dtype_t dtype, ft_dtype_t wire_dtype,
+                            ft_op_t op, double scale, ft_comm_t* comm, void* stream) {
+  if (!comm) return FT_ERR_INVALID;
+  if (comm->kind == COMM_EMULATED) {
+    set_last_error("emulated communicators take one buffer per logical rank: use ft_allreduce_multi");
+    return FT_ERR_INVALID;
+  }
+  const void* s[1] = {sendbuf};
+  void* r[1] = {recvbuf};
+  return do_allreduce(comm, s, r, count, (int)dtype, (int)wire_dtype, (int)op, scale, (cudaStream_t)stream);
+}
+
+ft_result_t ft_allreduce_multi(const void* const* sendbufs, void* const* recvbufs, size_t count, ft_dtype_t dtype,
+                               ft_dtype_t wire_dtype, ft_op_t op, double scale, ft_comm_t* comm, void* stream) {
+  if (!comm || !recvbufs) return FT_ERR_INVALID;
+  std::vector<const void*> s((size_t)comm->nlocal, FT_IN_PLACE);
+  if (sendbufs)
+    for (int l = 0; l < comm->nlocal; ++l) s[(size_t)l] = sendbufs[l];
+  return do_allreduce(comm, s.data(), recvbufs, count, (int)dtype, (int)wire_dtype, (int)op, scale, (cudaStream_t)stream);
+}
+
+ft_result_t ft_comm_last_call(const ft_comm_t* c, ft_call_info_t* out) {
+  if (!c || !out) return FT_ERR_INVALID;
+  *out = c->last;
+  return FT_SUCCESS;
+}
+
+}  // extern "C"

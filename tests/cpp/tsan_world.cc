@@ -1,0 +1,58 @@
+// ThreadSanitizer driver for the CPU world: runs the kernel algorithm templates with one thread per
+// "CTA" under TSAN to validate the hazard analysis (data accesses are plain, flags are acq/rel).
+// Build+run: make tsan   (see Makefile)
+#include <stdint.h>
+#include <stdio.h>
+#include <stdlib.h>
+#include <string.h>
+
+#include <vector>
+
+extern "C" {
+void* ft_host_world_create(int, size_t, size_t);
+void ft_host_world_destroy(void*);
+void* ft_host_registered(void*, int);
+long long ft_host_allreduce(void*, const void* const*, void* const*, long long, int, int, int, int,
+                            const int*, int, int, long long, int, double, int, unsigned long long, int);
+}
+
+static int run(int n, std::vector<int> widths, int algo, int mode, long long count, int ctas, long long tile) {
+  void* w = ft_host_world_create(n, 1 << 18, 1 << 18);
+  std::vector<std::vector<float>> in(n, std::vector<float>(count + 8)), out(n, std::vector<float>(count + 8));
+  std::vector<const void*> s(n);
+  std::vector<void*> r(n);
+  for (int i = 0; i < n; ++i) {
+    float* base = mode ? (float*)ft_host_registered(w, i) : (float*)(((uintptr_t)in[i].data() + 15) & ~(uintptr_t)15);
+    for (long long j = 0; j < count; ++j) base[j] = (float)(i + 1) * (float)(j % 7);
+    s[i] = base;
+    r[i] = mode ? (void*)base : (void*)(((uintptr_t)out[i].data() + 15) & ~(uintptr_t)15);
+  }
+  int bad = 0;
+  for (int rep = 0; rep < 3; ++rep) {
+    if (mode) for (int i = 0; i < n; ++i) for (long long j = 0; j < count; ++j) ((float*)s[i])[j] = (float)(i + 1) * (float)(j % 7);
+    long long rc = ft_host_allreduce(w, s.data(), r.data(), count, 6, 6, 0, algo, widths.data(), (int)widths.size(),
+                                     ctas, tile, mode, 1.0, 0, 20000000000ull, -1);
+    if (rc) { printf("rc=%lld\n", rc); bad = 1; }
+    float tot = (float)n * (n + 1) / 2;
+    for (int i = 0; i < n; ++i)
+      for (long long j = 0; j < count; ++j)
+        if (((float*)r[i])[j] != tot * (float)(j % 7)) { bad = 1; }
+  }
+  ft_host_world_destroy(w);
+  printf("n=%d stages=%zu algo=%d mode=%d count=%lld: %s\n", n, widths.size(), algo, mode, count, bad ? "FAIL" : "ok");
+  return bad;
+}
+
+int main() {
+  int bad = 0;
+  bad |= run(4, {2, 2}, 2, 0, 5000, 3, 256);
+  bad |= run(6, {2, 3}, 2, 0, 7001, 2, 512);
+  bad |= run(8, {2, 2, 2}, 2, 1, 6000, 2, 256);
+  bad |= run(8, {8}, 2, 1, 6000, 3, 128);
+  bad |= run(4, {4}, 3, 0, 3000, 2, 256);
+  bad |= run(4, {4}, 3, 1, 3000, 2, 256);
+  bad |= run(5, {1}, 4, 0, 3000, 2, 256);
+  bad |= run(5, {1}, 4, 1, 3000, 2, 256);
+  bad |= run(4, {4}, 1, 0, 999, 2, 256);
+  return bad;
+}

@@ -1,0 +1,264 @@
+"""GPU tests on ONE device: N logical ranks served by one cooperative launch of the real sm_100a
+kernels (same device code as the multi-GPU path; every "peer" pointer lands in local HBM).
+Oracle: the independent numpy model in refimpl.py (plain fp32/fp64 PyTorch-free reference)."""
+import os
+
+import numpy as np
+import pytest
+
+os.environ.setdefault("FT_TIMEOUT_S", "5")
+
+torch = pytest.importorskip("torch")
+import flextree as ft  # noqa: E402
+from refimpl import block_size, round_bf16, staged_allreduce  # noqa: E402
+
+pytestmark = pytest.mark.gpu
+
+RNG = np.random.default_rng(7)
+
+
+@pytest.fixture(scope="module")
+def comms():
+    cache = {}
+
+    def get(n):
+        if n not in cache:
+            cache[n] = ft.Communicator.emulated(n, 0, window_bytes=8 << 20)
+        return cache[n]
+
+    yield get
+    for c in cache.values():
+        c.close()
+
+
+def dev(a):
+    return torch.from_numpy(np.ascontiguousarray(a)).cuda()
+
+
+def run(comm, arrays, out_of_place=False, **kw):
+    ts = [dev(a) for a in arrays]
+    outs = [torch.full_like(t, 0) for t in ts] if out_of_place else None
+    res = comm.allreduce_multi(ts, outs=outs, **kw)
+    torch.cuda.synchronize()
+    assert comm.error() == 0, hex(comm.error())
+    return [t.cpu().numpy() for t in res], [t.cpu().numpy() for t in ts]
+
+
+WIDTHS = {2: [[2]], 4: [[4], [2, 2]], 6: [[6], [2, 3], [3, 2]], 8: [[8], [2, 4], [4, 2], [2, 2, 2]]}
+
+
+@pytest.mark.parametrize("n", [2, 4, 6, 8])
+@pytest.mark.parametrize("count", [1, 7, 35, 1001, 65536 + 3])
+def test_fp32_sum_bit_exact(comms, n, count):
+    c = comms(n)
+    c.set_algo("stages")
+    xs = [RNG.standard_normal(count).astype(np.float32) for _ in range(n)]
+    B = block_size(count, n, 4)
+    for widths in WIDTHS[n]:
+        c.set_widths(widths)
+        want = staged_allreduce(xs, widths, block=B)
+        got, src = run(c, xs, out_of_place=True)
+        for r in range(n):
+            np.testing.assert_array_equal(got[r], want[r], err_msg=f"{widths} rank {r}")
+            np.testing.assert_array_equal(src[r], xs[r])
+        got, _ = run(c, xs)
+        for r in range(n):
+            np.testing.assert_array_equal(got[r], want[r])
+        info = c.last_call()
+        assert info["algo"] == "stages" and info["widths"] == widths
+    c.set_widths(None)
+    c.set_algo("auto")
+
+
+@pytest.mark.parametrize("dtype", [np.uint8, np.int8, np.int16, np.int32, np.int64, np.float64, np.bool_])
+@pytest.mark.parametrize("op", ["sum", "max", "min", "band", "bor"])
+def test_dtype_op_matrix(comms, dtype, op):
+    n, count = 6, 4099
+    c = comms(n)
+    dt = np.dtype(dtype)
+    if dt.kind == "f":
+        xs = [RNG.standard_normal(count).astype(dt) for _ in range(n)]
+    elif dt.kind == "b":
+        xs = [RNG.integers(0, 2, count).astype(dt) for _ in range(n)]
+    else:
+        info = np.iinfo(dt)
+        xs = [RNG.integers(info.min, info.max, count, dtype=dt, endpoint=True) for _ in range(n)]
+    c.set_algo("stages")
+    c.set_widths([2, 3])
+    if dt.kind == "f" and op in ("band", "bor"):
+        with pytest.raises(ft.FlexTreeError):
+            run(c, xs, op=op)
+        return
+    got, _ = run(c, xs, op=op)
+    npop = {"sum": np.add, "max": np.maximum, "min": np.minimum, "band": np.bitwise_and, "bor": np.bitwise_or}[op]
+    if dt.kind == "b":
+        st = np.stack(xs)
+        want = st.any(0) if op in ("sum", "max", "bor") else st.all(0)
+    elif dt.kind == "f":
+        want = staged_allreduce(xs, [2, 3], op=npop, block=block_size(count, n, dt.itemsize))[0]
+    else:
+        with np.errstate(over="ignore"):
+            want = xs[0].copy()
+            for x in xs[1:]:
+                want = npop(want, x)
+    for r in range(n):
+        np.testing.assert_array_equal(got[r], want)
+    c.set_widths(None)
+    c.set_algo("auto")
+
+
+def test_bf16_and_fp16(comms):
+    n, count, widths = 8, 40001, [2, 4]
+    c = comms(n)
+    c.set_algo("stages")
+    c.set_widths(widths)
+    xs = [RNG.standard_normal(count).astype(np.float32) for _ in range(n)]
+    for tdt, rnd in ((torch.bfloat16, round_bf16), (torch.float16, lambda a: a.astype(np.float16).astype(np.float32))):
+        ts = [torch.from_numpy(x).cuda().to(tdt) for x in xs]
+        ins = [t.float().cpu().numpy() for t in ts]
+        c.allreduce_multi(ts)
+        torch.cuda.synchronize()
+        assert c.error() == 0
+        want = staged_allreduce(ins, widths, block=block_size(count, n, 2), round_fn=rnd)[0]
+        for r in range(n):
+            np.testing.assert_array_equal(ts[r].float().cpu().numpy(), want)
+    c.set_widths(None)
+    c.set_algo("auto")
+
+
+def test_fp32_grads_bf16_wire_fused_scale(comms):
+    n, count = 4, 123457
+    c = comms(n)
+    c.set_algo("stages")
+    xs = [RNG.standard_normal(count).astype(np.float32) for _ in range(n)]
+    ts = [dev(x) for x in xs]
+    c.allreduce_multi(ts, scale=1.0 / n, wire_dtype=torch.bfloat16)
+    torch.cuda.synchronize()
+    assert c.error() == 0
+    want = staged_allreduce([round_bf16(x) for x in xs], [4], block=block_size(count, n, 2), round_fn=round_bf16)[0]
+    want = want * np.float32(1.0 / n)
+    for r in range(n):
+        np.testing.assert_array_equal(ts[r].cpu().numpy(), want)
+    ref = torch.stack([dev(x) for x in xs]).double().mean(0).float().cpu().numpy()
+    assert np.max(np.abs(ts[0].cpu().numpy() - ref)) < 0.03
+    c.set_algo("auto")
+
+
+@pytest.mark.parametrize("n", [2, 8])
+def test_oneshot_and_ring(comms, n):
+    c = comms(n)
+    for count in (1, 33, 5000):
+        xs = [RNG.standard_normal(count).astype(np.float32) for _ in range(n)]
+        exact = np.sum(np.stack(xs).astype(np.float64), 0)
+        acc = xs[0].copy()
+        for x in xs[1:]:
+            acc = acc + x
+        c.set_algo("oneshot")
+        got, _ = run(c, xs, out_of_place=True)
+        for r in range(n):
+            np.testing.assert_array_equal(got[r], acc)  # ascending-rank order on every rank
+        c.set_algo("ring")
+        got, _ = run(c, xs)
+        for r in range(n):
+            np.testing.assert_allclose(got[r], exact, rtol=1e-5, atol=1e-5)
+            np.testing.assert_array_equal(got[r], got[0])
+    c.set_algo("auto")
+
+
+def test_auto_selection_small_is_oneshot_large_is_stages(comms):
+    c = comms(8)
+    xs = [RNG.standard_normal(256).astype(np.float32) for _ in range(8)]
+    run(c, xs)
+    assert c.last_call()["algo"] == "oneshot"
+    xs = [RNG.standard_normal(1 << 20).astype(np.float32) for _ in range(8)]
+    got, _ = run(c, xs)
+    assert c.last_call()["algo"] == "stages"
+    np.testing.assert_allclose(got[3], np.sum(np.stack(xs).astype(np.float64), 0), rtol=1e-4, atol=1e-4)
+
+
+def test_registered_zero_copy_in_place(comms):
+    n, count = 8, 300000
+    c = comms(n)
+    c.set_algo("stages")
+    bufs = c.symm_empty(count, torch.float32)
+    xs = [RNG.standard_normal(count).astype(np.float32) for _ in range(n)]
+    for widths in ([8], [2, 4]):
+        c.set_widths(widths)
+        for it in range(3):
+            for r in range(n):
+                bufs[r].copy_(dev(xs[r]))
+            c.allreduce_multi(bufs)
+            torch.cuda.synchronize()
+            assert c.error() == 0
+            assert c.last_call()["mode"] == "registered"
+            want = staged_allreduce(xs, widths, block=block_size(count, n, 4))[0]
+            for r in range(n):
+                np.testing.assert_array_equal(bufs[r].cpu().numpy(), want)
+    c.set_widths(None)
+    c.set_algo("auto")
+
+
+def test_unaligned_views_use_scalar_path(comms):
+    n, count = 4, 10001
+    c = comms(n)
+    c.set_algo("stages")
+    xs = [RNG.standard_normal(count).astype(np.float32) for _ in range(n)]
+    base = [torch.zeros(count + 1, device="cuda") for _ in range(n)]
+    views = [b[1:] for b in base]  # 4-byte aligned only
+    for v, x in zip(views, xs):
+        v.copy_(dev(x))
+    c.allreduce_multi(views)
+    torch.cuda.synchronize()
+    assert c.error() == 0 and c.last_call()["vectorized"] is False
+    want = staged_allreduce(xs, [4], block=block_size(count, n, 4, vectorized=False))[0]
+    for r in range(n):
+        np.testing.assert_array_equal(views[r].cpu().numpy(), want)
+    c.set_algo("auto")
+
+
+def test_cuda_graph_capture_and_replay(comms):
+    """Epochs live on the device, so a captured allreduce can be replayed without host resets."""
+    n, count = 4, 50000
+    c = comms(n)
+    c.set_algo("stages")
+    c.reserve(count * 4)
+    ts = [torch.ones(count, device="cuda") * (r + 1) for r in range(n)]
+    outs = [torch.zeros(count, device="cuda") for _ in range(n)]
+    c.allreduce_multi(ts, outs=outs)  # warm-up outside capture
+    torch.cuda.synchronize()
+    g = torch.cuda.CUDAGraph()
+    s = torch.cuda.Stream()
+    with torch.cuda.stream(s):
+        g.capture_begin()
+        c.allreduce_multi(ts, outs=outs, stream=s)
+        g.capture_end()
+    for it in range(20):
+        for r in range(n):
+            ts[r].fill_(float(r + 1 + it))
+        g.replay()
+        torch.cuda.synchronize()
+        want = float(sum(r + 1 + it for r in range(n)))
+        for r in range(n):
+            assert torch.all(outs[r] == want), (it, r)
+    assert c.error() == 0
+    c.set_algo("auto")
+
+
+def test_single_rank_fast_path():
+    c = ft.Communicator.emulated(1, 0)
+    x = torch.arange(1000, device="cuda", dtype=torch.float32)
+    y = torch.zeros_like(x)
+    c.allreduce_multi([x], outs=[y])
+    torch.cuda.synchronize()
+    assert torch.equal(x, y)
+    c.allreduce_multi([x], outs=[y], scale=0.5)
+    torch.cuda.synchronize()
+    assert torch.equal(y, x * 0.5)
+    c.close()
+
+
+def test_native_library_is_loaded():
+    """Guard against a silent fallback: the CUDA .so must be the one mapped into this process."""
+    assert ft._lib.has_cuda_lib()
+    maps = open("/proc/self/maps").read()
+    assert "libflextree.so" in maps
