@@ -1,0 +1,148 @@
+#!/usr/bin/env python
+"""Size sweep: flextree algorithms vs NCCL on the same GPUs (BASELINE.json config #2 and #3).
+
+  python -m torch.distributed.run --nproc-per-node N --master-addr 127.0.0.1 bench/sweep.py \
+      [--min-bytes 1024] [--max-bytes 1073741824] [--dtype fp32|bf16] [--out gpurun_out/sweep.jsonl] [--all-widths]
+
+Each (size, implementation) pair: 5 warm-up calls, then `reps` back-to-back calls between two CUDA
+events (same method as nccl-tests), time = MAX over ranks / reps. flextree runs in place on symmetric
+(registered) buffers and, with --staging, also on private buffers; NCCL runs dist.all_reduce in place.
+busbw = bytes/t * 2(N-1)/N. One JSON object per line.
+"""
+import argparse
+import json
+import os
+import sys
+
+import torch
+import torch.distributed as dist
+
+sys.path.insert(0, os.path.dirname(os.path.dirname(os.path.abspath(__file__))))
+import flextree as ft  # noqa: E402
+
+
+def main():
+    ap = argparse.ArgumentParser()
+    ap.add_argument("--min-bytes", dest="min", type=int, default=1 << 10)
+    ap.add_argument("--max-bytes", dest="max", type=int, default=1 << 30)
+    ap.add_argument("--dtype", default="fp32")
+    ap.add_argument("--out", default="gpurun_out/sweep.jsonl")
+    ap.add_argument("--all-widths", action="store_true")
+    ap.add_argument("--staging", action="store_true")
+    ap.add_argument("--factor", type=int, default=4)
+    ap.add_argument("--tune", action="store_true", help="scan CTAs x tile bytes at --max-bytes instead of sweeping sizes")
+    args = ap.parse_args()
+    rank, world, local = int(os.environ["RANK"]), int(os.environ["WORLD_SIZE"]), int(os.environ["LOCAL_RANK"])
+    torch.cuda.set_device(local)
+    dev = torch.device("cuda", local)
+    dist.init_process_group("nccl", device_id=dev)
+    comm = ft.init()
+    tdt = torch.float32 if args.dtype == "fp32" else torch.bfloat16
+    es = 4 if args.dtype == "fp32" else 2
+    maxcount = args.max // es
+    symm = comm.symm_empty(maxcount, tdt)
+    priv = torch.empty(maxcount, device=dev, dtype=tdt)
+    symm.zero_()
+    priv.zero_()
+    comm.reserve(args.max)
+    fout = open(args.out, "a") if rank == 0 else None
+
+    def timed(fn, nbytes):
+        reps = 50 if nbytes <= (1 << 20) else (20 if nbytes <= (64 << 20) else 8)
+        for _ in range(5):
+            fn()
+        torch.cuda.synchronize()
+        dist.barrier()
+        torch.cuda.synchronize()
+        a, b = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+        a.record()
+        for _ in range(reps):
+            fn()
+        b.record()
+        torch.cuda.synchronize()
+        t = torch.tensor([a.elapsed_time(b) / reps], device=dev, dtype=torch.float64)
+        dist.all_reduce(t, op=dist.ReduceOp.MAX)
+        return t.item() * 1e3  # us
+
+    def emit(rec):
+        if rank == 0:
+            fout.write(json.dumps(rec) + "\n")
+            fout.flush()
+            print(json.dumps(rec), flush=True)
+
+    impls = [("auto", None)]
+    impls += [("oneshot", None), ("stages", [world]), ("ring", None)]
+    if comm.has_multicast:
+        impls.append(("nvls", None))
+    if args.all_widths:
+        impls += [("stages", w) for w in ft.enumerate_widths(world) if w != [world]]
+
+    if args.tune:
+        count = args.max // es
+        nbytes = count * es
+        us = timed(lambda: dist.all_reduce(priv[:count]), nbytes)
+        emit({"impl": "nccl", "n": world, "bytes": nbytes, "us": round(us, 2),
+              "busbw_GBps": round(nbytes / us / 1e3 * 2 * (world - 1) / world, 3)})
+        algos = ["stages"] + (["nvls"] if comm.has_multicast else [])
+        for algo in algos:
+            for threads in (512, 256):
+                for ctas in (32, 64, 128, 148, 256):
+                    for tile in (32 << 10, 128 << 10, 512 << 10, 2 << 20):
+                        try:
+                            comm.set_algo(algo)
+                            comm.set_launch(ctas, threads, tile)
+                            view = symm[:count]
+                            us = timed(lambda: comm.allreduce(view), nbytes)
+                            info = comm.last_call()
+                            emit({"impl": "flextree", "algo": algo, "threads": threads, "ctas": info["ctas"], "tile_bytes": info["tile_bytes"],
+                                  "n": world, "bytes": nbytes, "us": round(us, 2), "err": comm.error(),
+                                  "busbw_GBps": round(nbytes / us / 1e3 * 2 * (world - 1) / world, 3)})
+                        except ft.FlexTreeError as e:
+                            emit({"impl": "flextree", "algo": algo, "ctas": ctas, "tile": tile, "error": str(e)[:200]})
+                        symm.zero_()
+        comm.set_launch(0, 0, 0)
+        args.min = args.max + 1  # skip the size sweep
+
+    size = args.min
+    while size <= args.max:
+        count = size // es
+        nbytes = count * es
+        # NCCL
+        us = timed(lambda: dist.all_reduce(priv[:count]), nbytes)
+        emit({"impl": "nccl", "n": world, "bytes": nbytes, "dtype": args.dtype, "us": round(us, 2),
+              "busbw_GBps": round(nbytes / us / 1e3 * 2 * (world - 1) / world, 3)})
+        priv.zero_()
+        for algo, widths in impls:
+            for buf, mode in ((symm, "registered"),) + (((priv, "staging"),) if args.staging else ()):
+                if algo == "oneshot" and nbytes > (256 << 10):
+                    continue
+                if algo == "ring" and nbytes > (64 << 20):
+                    continue
+                if algo == "nvls" and nbytes < 16 * world:
+                    continue
+                try:
+                    comm.set_algo(algo)
+                    comm.set_widths(widths)
+                    view = buf[:count]
+                    us = timed(lambda: comm.allreduce(view), nbytes)
+                    info = comm.last_call()
+                    err = comm.error()
+                    emit({"impl": "flextree", "algo": info["algo"], "requested": algo, "widths": info["widths"], "mode": info["mode"],
+                          "ctas": info["ctas"], "tile_bytes": info["tile_bytes"], "n": world, "bytes": nbytes,
+                          "dtype": args.dtype, "us": round(us, 2), "est_us": round(info["est_us"], 2),
+                          "busbw_GBps": round(nbytes / us / 1e3 * 2 * (world - 1) / world, 3), "err": err})
+                    if err:
+                        comm.clear_error()
+                except ft.FlexTreeError as e:
+                    emit({"impl": "flextree", "requested": algo, "widths": widths, "bytes": nbytes, "error": str(e)[:200]})
+                buf.zero_()
+        comm.set_algo("auto")
+        comm.set_widths(None)
+        size *= args.factor
+    dist.barrier()
+    ft.shutdown()
+    dist.destroy_process_group()
+
+
+if __name__ == "__main__":
+    main()

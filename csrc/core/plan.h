@@ -22,7 +22,7 @@
 #define FT_MAX_RANKS 64
 #define FT_MAX_WIDTH 32   // reference limit is 20 (mpi_mod.hpp:245); we allow up to 32 per stage
 #define FT_MAX_LOCAL 32   // logical ranks served by one launch (single-GPU emulation mode)
-#define FT_MAX_CTAS 128   // CTAs per rank that own flag slots
+#define FT_MAX_CTAS 256   // CTAs per rank that own flag slots
 
 namespace ft {
 

@@ -477,7 +477,7 @@ struct StagedCta {
     }
     for (int j = 0; j < mine; ++j) {
       wait_group(PH_IN, 0, E + j + 1);
-      nvls_reduce_tile<CU>(cta + j * G);
+      nvls_reduce_tile<(VE == 1) ? 1 : 8>(cta + j * G);
       be.sync();
       signal_group(PH_RS0, 0, E + j + 1);
     }
@@ -734,7 +734,7 @@ struct StagedCta {
   FT_DEV void run() {
     const int G = a.ctas, m = a.plan.nstages, nt = a.lay.ntiles;
     const int mine = cta < nt ? (nt - cta + G - 1) / G : 0;  // my tiles: t = cta + j*G
-    constexpr int CU = (VE == 1) ? 1 : 4;
+    constexpr int CU = (VE == 1) ? 1 : 8;
 
     // IN: publish my window to my stage-0 group
     if (a.mode == MODE_STAGING) {

@@ -1,0 +1,171 @@
+"""Multi-process worker (one rank per GPU), launched by tests/test_multigpu.py through
+torch.distributed.run. Every check compares the flextree kernels against torch.distributed (NCCL) or
+exact fp64 math. Prints MP_WORKER_OK on rank 0 when everything passed."""
+import os
+import sys
+
+import torch
+import torch.distributed as dist
+
+sys.path.insert(0, os.path.dirname(os.path.dirname(os.path.abspath(__file__))))
+os.environ.setdefault("FT_TIMEOUT_S", "10")
+import flextree as ft  # noqa: E402
+
+
+def main():
+    rank, world, local = int(os.environ["RANK"]), int(os.environ["WORLD_SIZE"]), int(os.environ["LOCAL_RANK"])
+    torch.cuda.set_device(local)
+    dev = torch.device("cuda", local)
+    dist.init_process_group("nccl", device_id=dev)
+    comm = ft.init()
+    assert comm.rank == rank and comm.size == world
+    if rank == 0:
+        print(f"[worker] world {world}, multicast={comm.has_multicast}", flush=True)
+    g = torch.Generator(device=dev).manual_seed(100 + rank)
+
+    def check(t, ref, tol, what):
+        torch.cuda.synchronize()
+        e = comm.error()
+        assert e == 0, f"{what}: device error {e:#x}"
+        err = (t.double() - ref.double()).abs().max().item()
+        scale = max(1.0, ref.double().abs().max().item())
+        assert err <= tol * scale, f"{what}: max abs err {err} (scale {scale})"
+
+    def exact_sum(x):
+        y = x.double().clone()
+        dist.all_reduce(y)
+        return y
+
+    # 1. every factorization, several sizes, in place and out of place (staging path)
+    comm.set_algo("stages")
+    for widths in ft.enumerate_widths(world):
+        comm.set_widths(widths)
+        for count in (1, 7, 1000, 65536 + 5, (1 << 22) + 3):
+            x = torch.randn(count, device=dev, generator=g)
+            ref = exact_sum(x)
+            out = torch.zeros_like(x)
+            comm.allreduce(x, out=out)
+            check(out, ref, 1e-5, f"stages {widths} count {count} oop")
+            y = x.clone()
+            comm.allreduce(y)
+            check(y, ref, 1e-5, f"stages {widths} count {count} in place")
+            assert comm.last_call()["widths"] == widths
+            # all ranks must hold bit-identical results
+            chk = y.clone()
+            dist.broadcast(chk, 0)
+            assert torch.equal(chk, y), f"ranks differ for {widths}"
+    comm.set_widths(None)
+
+    # 2. one-shot, ring, (NVLS), auto
+    algos = ["oneshot", "ring", "auto"] + (["nvls"] if comm.has_multicast else [])
+    for algo in algos:
+        comm.set_algo(algo)
+        for count in (3, 2048, 100000):
+            if algo == "nvls" and count < 16:
+                continue
+            x = torch.randn(count, device=dev, generator=g)
+            ref = exact_sum(x)
+            comm.allreduce(x)
+            check(x, ref, 1e-5, f"{algo} count {count}")
+    comm.set_algo("auto")
+
+    # 3. dtypes / ops
+    comm.set_algo("stages")
+    for dt, op, tor in ((torch.int32, "sum", dist.ReduceOp.SUM), (torch.int64, "max", dist.ReduceOp.MAX),
+                        (torch.uint8, "band", None), (torch.float64, "min", dist.ReduceOp.MIN),
+                        (torch.bfloat16, "sum", dist.ReduceOp.SUM), (torch.float16, "max", dist.ReduceOp.MAX)):
+        if dt.is_floating_point:
+            x = torch.randn(33333, device=dev, generator=g).to(dt)
+        else:
+            x = torch.randint(0, 100, (33333,), device=dev, generator=g).to(dt)
+        if tor is None:  # NCCL has no bitwise AND: gather and fold locally
+            parts = [torch.empty_like(x) for _ in range(world)]
+            dist.all_gather(parts, x)
+            ref = parts[0].clone()
+            for q in parts[1:]:
+                ref &= q
+        else:
+            ref = x.clone()
+            dist.all_reduce(ref, op=tor)
+        comm.allreduce(x, op=op)
+        check(x, ref, 2e-2 if dt in (torch.bfloat16, torch.float16) else 0, f"{dt} {op}")
+
+    # 4. fp32 gradients, bf16 wire, fused 1/N (DDP shape)
+    x = torch.randn(250001, device=dev, generator=g)
+    ref = exact_sum(x) / world
+    comm.allreduce(x, scale=1.0 / world, wire_dtype=torch.bfloat16)
+    check(x, ref, 2e-2, "bf16 wire + scale")
+
+    # 5. registered (zero-copy) buffers, repeated, incl. NVLS if present
+    for algo in ["stages"] + (["nvls"] if comm.has_multicast else []):
+        comm.set_algo(algo)
+        buf = comm.symm_empty(1 << 20)
+        for it in range(4):
+            src = torch.randn(1 << 20, device=dev, generator=g)
+            ref = exact_sum(src)
+            buf.copy_(src)
+            comm.allreduce(buf)
+            check(buf, ref, 1e-5, f"registered {algo} iter {it}")
+            assert comm.last_call()["mode"] == "registered"
+    comm.set_algo("auto")
+
+    # 6. CUDA graph capture + replay
+    comm.set_algo("stages")
+    n = 1 << 18
+    comm.reserve(n * 4)
+    x = torch.full((n,), float(rank + 1), device=dev)
+    y = torch.zeros_like(x)
+    comm.allreduce(x, out=y)
+    torch.cuda.synchronize()
+    graph = torch.cuda.CUDAGraph()
+    s = torch.cuda.Stream()
+    with torch.cuda.stream(s):
+        graph.capture_begin()
+        comm.allreduce(x, out=y, stream=s)
+        graph.capture_end()
+    for it in range(10):
+        x.fill_(float(rank + 1 + it))
+        graph.replay()
+        torch.cuda.synchronize()
+        want = float(sum(r + 1 + it for r in range(world)))
+        assert torch.all(y == want), f"graph replay {it}: {y[:4]} vs {want}"
+    assert comm.error() == 0
+    comm.set_algo("auto")
+
+    # 7. DDP comm hook parity with stock NCCL DDP on a small MLP
+    from torch.nn.parallel import DistributedDataParallel as DDP
+    torch.manual_seed(0)
+
+    def make():
+        return torch.nn.Sequential(torch.nn.Linear(256, 512), torch.nn.GELU(), torch.nn.Linear(512, 512),
+                                   torch.nn.GELU(), torch.nn.Linear(512, 10)).to(dev)
+    m_ref, m_ft = make(), make()
+    m_ft.load_state_dict(m_ref.state_dict())
+    d_ref = DDP(m_ref, device_ids=[local], bucket_cap_mb=1)
+    d_ft = DDP(m_ft, device_ids=[local], bucket_cap_mb=1)
+    state = ft.FlexTreeHookState(comm)
+    d_ft.register_comm_hook(state, ft.ddp_comm_hook)
+    o_ref = torch.optim.SGD(d_ref.parameters(), lr=0.05)
+    o_ft = torch.optim.SGD(d_ft.parameters(), lr=0.05)
+    for step in range(5):
+        xb = torch.randn(64, 256, device=dev, generator=g)
+        yb = torch.randint(0, 10, (64,), device=dev, generator=g)
+        for d, o in ((d_ref, o_ref), (d_ft, o_ft)):
+            o.zero_grad()
+            loss = torch.nn.functional.cross_entropy(d(xb), yb)
+            loss.backward()
+            o.step()
+    torch.cuda.synchronize()
+    assert state.calls > 0 and comm.error() == 0
+    for p_ref, p_ft in zip(m_ref.parameters(), m_ft.parameters()):
+        assert torch.allclose(p_ref, p_ft, rtol=1e-4, atol=1e-5), "DDP hook diverged from NCCL DDP"
+
+    dist.barrier()
+    ft.shutdown()
+    if rank == 0:
+        print("MP_WORKER_OK", flush=True)
+    dist.destroy_process_group()
+
+
+if __name__ == "__main__":
+    main()
