@@ -31,6 +31,7 @@ def main():
     ap.add_argument("--staging", action="store_true")
     ap.add_argument("--factor", type=int, default=4)
     ap.add_argument("--tune", action="store_true", help="scan CTAs x tile bytes at --max-bytes instead of sweeping sizes")
+    ap.add_argument("--tune-sizes", default="", help="comma list of message bytes: scan CTAs x tile at each (small grid)")
     args = ap.parse_args()
     rank, world, local = int(os.environ["RANK"]), int(os.environ["WORLD_SIZE"]), int(os.environ["LOCAL_RANK"])
     torch.cuda.set_device(local)
@@ -102,6 +103,40 @@ def main():
                         symm.zero_()
         comm.set_launch(0, 0, 0)
         args.min = args.max + 1  # skip the size sweep
+
+    if args.tune_sizes:
+        for nb in [int(x) for x in args.tune_sizes.split(",")]:
+            count = nb // es
+            nbytes = count * es
+            us = timed(lambda: dist.all_reduce(priv[:count]), nbytes)
+            emit({"impl": "nccl", "n": world, "bytes": nbytes, "us": round(us, 2),
+                  "busbw_GBps": round(nbytes / us / 1e3 * 2 * (world - 1) / world, 3)})
+            algos = ["stages"] + (["nvls"] if comm.has_multicast else [])
+            block = nbytes // world
+            for algo in algos:
+                seen = set()
+                for ctas in (4, 8, 16, 32, 64, 148):
+                    for tile in (4 << 10, 16 << 10, 64 << 10, 256 << 10, 1 << 20, 2 << 20):
+                        if tile > max(4 << 10, block):
+                            continue
+                        try:
+                            comm.set_algo(algo)
+                            comm.set_launch(ctas, 512, tile)
+                            view = symm[:count]
+                            us = timed(lambda: comm.allreduce(view), nbytes)
+                            info = comm.last_call()
+                            key = (info["ctas"], info["tile_bytes"])
+                            if key in seen:
+                                continue
+                            seen.add(key)
+                            emit({"impl": "flextree", "algo": algo, "ctas": info["ctas"], "tile_bytes": info["tile_bytes"],
+                                  "n": world, "bytes": nbytes, "us": round(us, 2), "err": comm.error(),
+                                  "busbw_GBps": round(nbytes / us / 1e3 * 2 * (world - 1) / world, 3)})
+                        except ft.FlexTreeError as e:
+                            emit({"impl": "flextree", "algo": algo, "ctas": ctas, "tile": tile, "bytes": nbytes, "error": str(e)[:200]})
+            comm.set_launch(0, 0, 0)
+            comm.set_algo("auto")
+        args.min = args.max + 1
 
     size = args.min
     while size <= args.max:

@@ -163,8 +163,10 @@ double predict_us(const LinkModel& m, int algo, const Widths& widths, int n, dou
       if (!m.has_nvls) return 1e30;
       double t = m.alpha_launch_us + 3 * m.alpha_sync_us;
       if (!registered) t += S / (m.gamma_hbm_GBps * 1e3) * 4.0 / 8.0;
-      // inbound per GPU: S/N reduced by the switch + (N-1)/N*S multicast from the other owners = S
-      t += xfer_us(S, m.beta_nvls_GBps, m.half_bw_bytes);
+      // per-GPU link traffic (each direction): every rank's copy of all N blocks goes up to the switch once
+      // (S, including the requester's own copy) plus its reduced block broadcast (S/N)  ->  (1 + 1/N) S,
+      // against 2 (N-1)/N S for the P2P stages: NVLS loses at N = 2 and wins from N = 4 up.
+      t += xfer_us(S * (1.0 + 1.0 / N), m.beta_nvls_GBps, m.half_bw_bytes);
       return t;
     }
     case ALGO_RING: {

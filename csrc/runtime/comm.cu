@@ -269,43 +269,50 @@ struct Shape {
   long long tile_bytes;
 };
 
-// Launch shape heuristics (re-tuned from measurements; see docs/TUNING.md). Every rank must derive
-// the same shape from the same arguments.
+// Launch shape heuristics. Measured on 2xB200 (profiles/tune_n2.md): the pull kernels are bound by bytes
+// in flight, so bandwidth grows ~linearly with CTAs up to one per SM, and every tile boundary costs a
+// system fence + a flag hop, so tiles should be as large as the message allows (512 KiB per block-chunk
+// was the sweet spot; 2 MiB starves the grid). Every rank must derive the same shape from the same
+// arguments.
 Shape pick_shape(const ft_comm* c, int algo, size_t msg_bytes, int nranks, int esize) {
   Shape s;
   s.threads = c->threads_override ? c->threads_override : env_int("FT_THREADS", 512);
   if (s.threads > FT_MAX_THREADS) s.threads = FT_MAX_THREADS;
   if (s.threads < 32) s.threads = 32;
+  int max_ctas = c->sm_count;  // one resident CTA per SM at 512 threads x <=128 registers
+  if (max_ctas > FT_MAX_CTAS) max_ctas = FT_MAX_CTAS;
+  if (c->kind == COMM_EMULATED) {
+    // cooperative launch: nranks*ctas CTAs must be co-resident
+    int per_sm = s.threads <= 256 ? 2 : 1;
+    max_ctas = c->sm_count * per_sm / nranks;
+    if (max_ctas < 1) max_ctas = 1;
+  }
+  const long long block_bytes = ((long long)msg_bytes + nranks - 1) / nranks;
+  const long long kMinTile = env_ll("FT_MIN_TILE_BYTES", 16 << 10), kMaxTile = env_ll("FT_MAX_TILE_BYTES", 512 << 10);
   int ctas;
-  if (msg_bytes <= (64u << 10)) ctas = 4;
-  else if (msg_bytes <= (1u << 20)) ctas = 16;
-  else if (msg_bytes <= (16u << 20)) ctas = 32;
-  else ctas = 64;
+  long long tile;
   if (algo == ALGO_ONESHOT) {
-    // one LL line (8 payload bytes) per thread
-    long long lines = ((long long)msg_bytes + 7) / 8;
+    long long lines = ((long long)msg_bytes + 7) / 8;  // one LL line (8 payload bytes) per thread
     ctas = (int)((lines + s.threads - 1) / s.threads);
     if (ctas > 32) ctas = 32;
+    tile = kMinTile;
+  } else {
+    // as many CTAs as there are minimum-size tiles, up to the whole GPU; then one tile per CTA until the
+    // tile would exceed kMaxTile
+    long long want = (block_bytes + kMinTile - 1) / kMinTile;
+    ctas = (int)(want < max_ctas ? want : max_ctas);
+    if (ctas < 1) ctas = 1;
+    tile = (block_bytes + ctas - 1) / ctas;
+    if (tile < kMinTile) tile = kMinTile;
+    if (tile > kMaxTile) tile = kMaxTile;
   }
   ctas = c->ctas_override ? c->ctas_override : env_int("FT_CTAS", ctas);
   if (ctas < 1) ctas = 1;
   if (ctas > FT_MAX_CTAS) ctas = FT_MAX_CTAS;
-  if (c->kind == COMM_EMULATED) {
-    // cooperative launch: nranks*ctas CTAs must be co-resident (1 CTA of 512 threads / SM worst case)
-    int per_sm = s.threads <= 256 ? 2 : 1;
-    int cap = c->sm_count * per_sm / nranks;
-    if (cap < 1) cap = 1;
-    if (ctas > cap) ctas = cap;
-  }
+  if (c->kind == COMM_EMULATED && ctas > max_ctas) ctas = max_ctas;
   s.ctas = ctas;
-  long long block_bytes = ((long long)msg_bytes + nranks - 1) / nranks;
-  long long tile = c->tile_override ? c->tile_override : env_ll("FT_TILE_BYTES", 0);
-  if (tile <= 0) {
-    // aim for >= 4 tiles per CTA so that stages pipeline, within [4 KiB, 64 KiB] per block-chunk
-    tile = block_bytes / ((long long)ctas * 4);
-    if (tile > (64 << 10)) tile = 64 << 10;
-    if (tile < (4 << 10)) tile = 4 << 10;
-  }
+  long long t2 = c->tile_override ? c->tile_override : env_ll("FT_TILE_BYTES", 0);
+  if (t2 > 0) tile = t2;
   tile = (tile + 15) / 16 * 16;
   if (tile < esize) tile = esize;
   s.tile_bytes = tile;
