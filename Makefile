@@ -56,7 +56,7 @@ $(B)/ft_plan: csrc/tools/ft_plan.cc $(PLANNER_OBJ)
 	$(CXX) $(CXXFLAGS) -o $@ $^
 
 $(B)/ft_bench: csrc/tools/ft_bench.cu $(LIBDIR)/libflextree.so
-	$(NVCC) $(NVFLAGS) -o $@ $< -L$(LIBDIR) -lflextree -Xlinker -rpath -Xlinker '$$ORIGIN/../$(LIBDIR)'
+	$(NVCC) $(NVFLAGS) -o $@ $< -L$(LIBDIR) -lflextree -ldl -Xlinker -rpath -Xlinker '$$ORIGIN/../$(LIBDIR)'
 
 $(B)/nccl_bench: csrc/tools/nccl_bench.cu
 	$(NVCC) $(NVFLAGS) -o $@ $< -lnccl

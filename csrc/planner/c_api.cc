@@ -116,6 +116,7 @@ int ft_link_model_set(ft_link_model_t* m, const char* key, double v) {
   std::string k = key;
 #define FT_KEY(name, cast) if (k == #name) { m->m.name = (cast)v; return FT_SUCCESS; }
   FT_KEY(alpha_launch_us, double) FT_KEY(alpha_sync_us, double) FT_KEY(alpha_ll_us, double)
+  FT_KEY(alpha_peer_us, double) FT_KEY(alpha_nvls_us, double) FT_KEY(beta_ll_self_GBps, double)
   FT_KEY(beta_p2p_GBps, double) FT_KEY(beta_p2p_1peer_GBps, double) FT_KEY(fanin_knee, int)
   FT_KEY(beta_nvls_GBps, double) FT_KEY(beta_ll_GBps, double) FT_KEY(gamma_hbm_GBps, double)
   FT_KEY(half_bw_bytes, double) FT_KEY(has_nvls, bool) FT_KEY(max_oneshot_bytes, int)

@@ -95,6 +95,7 @@ bool load_link_model(const std::string& path, LinkModel* m, std::string* err) {
     pos = v;
 #define FT_KEY(name, cast) if (key == #name) { m->name = (cast)val; ++found; continue; }
     FT_KEY(alpha_launch_us, double) FT_KEY(alpha_sync_us, double) FT_KEY(alpha_ll_us, double)
+    FT_KEY(alpha_peer_us, double) FT_KEY(alpha_nvls_us, double) FT_KEY(beta_ll_self_GBps, double)
     FT_KEY(beta_p2p_GBps, double) FT_KEY(beta_p2p_1peer_GBps, double) FT_KEY(fanin_knee, int)
     FT_KEY(beta_nvls_GBps, double) FT_KEY(beta_ll_GBps, double) FT_KEY(gamma_hbm_GBps, double)
     FT_KEY(half_bw_bytes, double) FT_KEY(has_nvls, bool) FT_KEY(max_oneshot_bytes, int)
@@ -105,16 +106,15 @@ bool load_link_model(const std::string& path, LinkModel* m, std::string* err) {
 }
 
 std::string dump_link_model(const LinkModel& m) {
-  char buf[1024];
+  char buf[2048];
   std::snprintf(buf, sizeof buf,
-                "{\"alpha_launch_us\": %.4g, \"alpha_sync_us\": %.4g, \"alpha_ll_us\": %.4g, "
-                "\"beta_p2p_GBps\": %.5g, \"beta_p2p_1peer_GBps\": %.5g, \"fanin_knee\": %d, "
-                "\"beta_nvls_GBps\": %.5g, \"beta_ll_GBps\": %.5g, \"gamma_hbm_GBps\": %.5g, "
+                "{\"alpha_launch_us\": %.4g, \"alpha_sync_us\": %.4g, \"alpha_peer_us\": %.4g, \"alpha_ll_us\": %.4g, "
+                "\"alpha_nvls_us\": %.4g, \"beta_p2p_GBps\": %.5g, \"beta_p2p_1peer_GBps\": %.5g, \"fanin_knee\": %d, "
+                "\"beta_nvls_GBps\": %.5g, \"beta_ll_GBps\": %.5g, \"beta_ll_self_GBps\": %.5g, \"gamma_hbm_GBps\": %.5g, "
                 "\"half_bw_bytes\": %.6g, \"has_nvls\": %s, \"max_oneshot_bytes\": %d}",
-                m.alpha_launch_us, m.alpha_sync_us, m.alpha_ll_us, m.beta_p2p_GBps,
-                m.beta_p2p_1peer_GBps, m.fanin_knee, m.beta_nvls_GBps, m.beta_ll_GBps,
-                m.gamma_hbm_GBps, m.half_bw_bytes, m.has_nvls ? "true" : "false",
-                m.max_oneshot_bytes);
+                m.alpha_launch_us, m.alpha_sync_us, m.alpha_peer_us, m.alpha_ll_us, m.alpha_nvls_us, m.beta_p2p_GBps,
+                m.beta_p2p_1peer_GBps, m.fanin_knee, m.beta_nvls_GBps, m.beta_ll_GBps, m.beta_ll_self_GBps,
+                m.gamma_hbm_GBps, m.half_bw_bytes, m.has_nvls ? "true" : "false", m.max_oneshot_bytes);
   return buf;
 }
 
@@ -138,40 +138,41 @@ double predict_us(const LinkModel& m, int algo, const Widths& widths, int n, dou
                   bool registered) {
   if (n <= 1) return m.alpha_launch_us + S / (m.gamma_hbm_GBps * 1e3);
   const double N = n;
+  auto hop = [&](int w) { return m.alpha_sync_us + m.alpha_peer_us * (w - 1); };
   switch (algo) {
     case ALGO_ONESHOT: {
-      // every rank pushes its whole message to N-1 peers as LL lines, then reduces locally
-      return m.alpha_launch_us + m.alpha_ll_us + (N - 1) * S / (m.beta_ll_GBps * 1e3) +
-             (N + 1) * 2 * S / (m.gamma_hbm_GBps * 1e3);
+      // every rank pushes its whole message to N-1 peers as LL lines, then polls and reduces them
+      return m.alpha_launch_us + m.alpha_ll_us + S / (m.beta_ll_self_GBps * 1e3) +
+             (N - 1) * S / (m.beta_ll_GBps * 1e3);
     }
     case ALGO_STAGED: {
       double t = m.alpha_launch_us;
       if (!registered) t += S / (m.gamma_hbm_GBps * 1e3) * 2.0 / 8.0;  // copy-in mostly overlapped
-      t += m.alpha_sync_us;  // input-ready hop
+      t += hop(widths.empty() ? n : widths[0]);  // input-ready hop
       double g = 1;
       for (int w : widths) {
         double gn = g * w;
         double stage_bytes = (w - 1) / gn * S;  // inbound per rank, same for RS and AG
         double b = beta_fanin(m, w - 1);
-        t += 2.0 * (m.alpha_sync_us + xfer_us(stage_bytes, b, m.half_bw_bytes));
+        t += 2.0 * (hop(w) + xfer_us(stage_bytes, b, m.half_bw_bytes));
         g = gn;
       }
-      if (registered) t += m.alpha_sync_us;  // exit barrier
+      if (registered) t += hop(widths.empty() ? n : widths[0]);  // exit barrier
       return t;
     }
     case ALGO_NVLS: {
       if (!m.has_nvls) return 1e30;
-      double t = m.alpha_launch_us + 3 * m.alpha_sync_us;
+      double t = m.alpha_launch_us + m.alpha_nvls_us;
       if (!registered) t += S / (m.gamma_hbm_GBps * 1e3) * 4.0 / 8.0;
       // per-GPU link traffic (each direction): every rank's copy of all N blocks goes up to the switch once
       // (S, including the requester's own copy) plus its reduced block broadcast (S/N)  ->  (1 + 1/N) S,
       // against 2 (N-1)/N S for the P2P stages: NVLS loses at N = 2 and wins from N = 4 up.
-      t += xfer_us(S * (1.0 + 1.0 / N), m.beta_nvls_GBps, m.half_bw_bytes);
+      t += S * (1.0 + 1.0 / N) / (m.beta_nvls_GBps * 1e3);
       return t;
     }
     case ALGO_RING: {
-      double step = m.alpha_sync_us + xfer_us(S / N, beta_fanin(m, 1), m.half_bw_bytes / 4);
-      return m.alpha_launch_us + m.alpha_sync_us + 2 * (N - 1) * step;
+      double step = hop(2) + xfer_us(S / N, beta_fanin(m, 1), m.half_bw_bytes / 4);
+      return m.alpha_launch_us + hop(2) + 2 * (N - 1) * step;
     }
   }
   return 1e30;
@@ -201,7 +202,9 @@ Choice choose(const LinkModel& m, int n, double S, bool registered, int max_widt
     if (ok) consider(ALGO_STAGED, w);
   }
   consider(ALGO_NVLS, {n});
-  consider(ALGO_RING, {1});
+  // The ring is kept for parity with the reference (FT_TOPO containing a 1) and as the fallback for world
+  // sizes with no usable factorization; on an NVSwitch fabric it never beats the direct exchanges, so it
+  // is not an automatic candidate.
   if (best.est_us >= 1e30) {  // e.g. prime n above max_width: fall back to ring
     best.algo = ALGO_RING;
     best.widths = {1};

@@ -129,7 +129,7 @@ void apply_options(ft_comm* c, const ft_comm_options_t* o) {
   ft_comm_options_default(&d);
   if (o) d = *o;
   c->window_bytes = d.window_bytes ? d.window_bytes : (size_t)env_ll("FT_WINDOW_BYTES", 64ll << 20);
-  c->ll_bytes = d.ll_bytes ? d.ll_bytes : (size_t)env_ll("FT_LL_BYTES", 4ll << 20);
+  c->ll_bytes = d.ll_bytes ? d.ll_bytes : (size_t)env_ll("FT_LL_BYTES", 8ll << 20);
   c->window_bytes = (c->window_bytes + 4095) & ~(size_t)4095;
   c->ll_bytes = (c->ll_bytes + 4095) & ~(size_t)4095;
   int mc = d.use_multicast;
@@ -274,7 +274,7 @@ struct Shape {
 // system fence + a flag hop, so tiles should be as large as the message allows (512 KiB per block-chunk
 // was the sweet spot; 2 MiB starves the grid). Every rank must derive the same shape from the same
 // arguments.
-Shape pick_shape(const ft_comm* c, int algo, size_t msg_bytes, int nranks, int esize) {
+Shape pick_shape(const ft_comm* c, int algo, int mode, size_t msg_bytes, int nranks, int esize) {
   Shape s;
   s.threads = c->threads_override ? c->threads_override : env_int("FT_THREADS", 512);
   if (s.threads > FT_MAX_THREADS) s.threads = FT_MAX_THREADS;
@@ -288,7 +288,10 @@ Shape pick_shape(const ft_comm* c, int algo, size_t msg_bytes, int nranks, int e
     if (max_ctas < 1) max_ctas = 1;
   }
   const long long block_bytes = ((long long)msg_bytes + nranks - 1) / nranks;
-  const long long kMinTile = env_ll("FT_MIN_TILE_BYTES", 16 << 10), kMaxTile = env_ll("FT_MAX_TILE_BYTES", 512 << 10);
+  // P2P tiles: a tile's work is ~nranks * tile bytes of loads; 512 KiB was best at N=2 and 64-128 KiB at N=8
+  const long long kMinTile = env_ll("FT_MIN_TILE_BYTES", 16 << 10);
+  long long kMaxTile = env_ll("FT_MAX_TILE_BYTES", (1 << 20) / (nranks < 2 ? 2 : nranks));
+  if (kMaxTile < kMinTile) kMaxTile = kMinTile;
   int ctas;
   long long tile;
   if (algo == ALGO_ONESHOT) {
@@ -296,9 +299,22 @@ Shape pick_shape(const ft_comm* c, int algo, size_t msg_bytes, int nranks, int e
     ctas = (int)((lines + s.threads - 1) / s.threads);
     if (ctas > 32) ctas = 32;
     tile = kMinTile;
+  } else if (algo == ALGO_NVLS) {
+    // multimem.ld_reduce/st saturate the switch path from very few SMs (8 CTAs reach 796 GB/s busbw at
+    // 256 MiB on 8 GPUs) and every tile boundary costs two system fences with multicast stores in
+    // flight: few CTAs, one big tile each (profiles/tune_n8.md).
+    // Private (staging) buffers add a local copy-in and copy-out pass that needs many more SMs.
+    const int nvls_max = mode == MODE_REGISTERED ? 8 : 64;
+    long long want = block_bytes / (64 << 10);
+    ctas = (int)(want < 2 ? 2 : (want > nvls_max ? nvls_max : want));
+    if (ctas > max_ctas) ctas = max_ctas;
+    tile = (block_bytes + ctas - 1) / ctas;
+    const long long kNvlsMaxTile = env_ll("FT_NVLS_MAX_TILE_BYTES", mode == MODE_REGISTERED ? (2 << 20) : (512 << 10));
+    if (tile > kNvlsMaxTile) tile = kNvlsMaxTile;
+    if (tile < 4096) tile = 4096;
   } else {
-    // as many CTAs as there are minimum-size tiles, up to the whole GPU; then one tile per CTA until the
-    // tile would exceed kMaxTile
+    // P2P pull kernels: as many CTAs as there are minimum-size tiles, up to the whole GPU; then one tile per
+    // CTA until the tile would exceed kMaxTile
     long long want = (block_bytes + kMinTile - 1) / kMinTile;
     ctas = (int)(want < max_ctas ? want : max_ctas);
     if (ctas < 1) ctas = 1;
@@ -432,7 +448,7 @@ ft_result_t do_allreduce(ft_comm* c, const void* const* send, void* const* recv,
   }
   if (algo == ALGO_RING && mode == MODE_REGISTERED && (apply_scale || io_dtype != wire_dtype)) mode = MODE_STAGING;
 
-  Shape sh = pick_shape(c, algo, msg_bytes, N, es);
+  Shape sh = pick_shape(c, algo, mode, msg_bytes, N, es);
   a.lay = make_layout((long long)count, N, es, sh.tile_bytes, vec);
   // flag values encode the tile ordinal in FT_EPOCH_SHIFT bits (ring: steps * tiles)
   {

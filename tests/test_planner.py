@@ -171,12 +171,21 @@ def test_link_model_choice_is_sane():
     algo, widths, est = m.choose(8, 1024)
     assert algo == ft.ALGO_ONESHOT
     algo, widths, est = m.choose(8, 256 << 20)
-    assert algo == ft.ALGO_STAGES and widths == [8]
-    m.set(has_nvls=1, beta_nvls_GBps=1200)
+    assert algo == ft.ALGO_STAGES and eval("*".join(map(str, widths))) == 8
+    algo, widths, est = m.choose(2, 256 << 20)
+    assert algo == ft.ALGO_STAGES and widths == [2]
+    m.set(has_nvls=1)
     algo, widths, est = m.choose(8, 256 << 20)
     assert algo == ft.ALGO_NVLS
-    # per-stage sync makes deep trees lose on a uniform fabric
-    assert m.predict_us(ft.ALGO_STAGES, [2, 2, 2], 8, 1 << 20) > m.predict_us(ft.ALGO_STAGES, [8], 8, 1 << 20)
+    # the switch moves (1 + 1/N) S per link direction, the P2P stages 2 (N-1)/N S: no NVLS win at N = 2
+    assert m.choose(2, 256 << 20)[0] == ft.ALGO_STAGES
+    # more stages = more flag hops: deep trees lose at small sizes on a uniform fabric
+    assert m.predict_us(ft.ALGO_STAGES, [2, 2, 2], 8, 1 << 16) > m.predict_us(ft.ALGO_STAGES, [8], 8, 1 << 16)
+    # fitted constants reproduce the 8xB200 measurements of round 1 within 15 %
+    for nbytes, us in ((1 << 20, 26.2), (4 << 20, 37.9), (16 << 20, 62.7), (64 << 20, 166.9), (256 << 20, 590.3)):
+        assert abs(m.predict_us(ft.ALGO_NVLS, [8], 8, nbytes, True) - us) / us < 0.15
+    for nbytes, us in ((1 << 10, 12.1), (64 << 10, 12.2), (256 << 10, 18.2)):
+        assert abs(m.predict_us(ft.ALGO_ONESHOT, [8], 8, nbytes, True) - us) / us < 0.15
     # 7 ranks (prime) still get an answer
     algo, widths, _ = m.choose(7, 1 << 24)
     assert widths in ([7], [1])
