@@ -120,3 +120,4 @@ def _declare(L):
     sig("ft_allreduce_ex", i32, [vp, vp, C.c_size_t, i32, i32, i32, dbl, vp, vp])
     sig("ft_allreduce_multi", i32, [C.POINTER(vp), C.POINTER(vp), C.c_size_t, i32, i32, i32, dbl, vp, vp])
     sig("ft_comm_last_call", i32, [vp, vp])
+    sig("ft_allreduce_emulated_noalloc", i32, [C.POINTER(vp), C.POINTER(vp), i32, C.c_size_t, i32, i32, vp])

@@ -180,6 +180,38 @@ typedef struct {
 } ft_call_info_t;
 ft_result_t ft_comm_last_call(const ft_comm_t*, ft_call_info_t*);
 
+/* Allreduce across `nranks` buffers that all live on the CURRENT device (the single-GPU "emulated ranks"
+ * form of ft_allreduce_multi, one-shot algorithm), for callers that are not allowed to allocate.
+ * No counterpart in the reference (which has neither a GPU path nor an allocation-free mode).
+ *
+ * Who needs this: code that runs where a device allocation is off limits - a plugin or callback invoked
+ * from inside another framework's execution loop (the host framework owns all device memory and forbids
+ * cudaMalloc/cudaFree there, or treats their implicit device-wide synchronisation as a bug), a service
+ * that has handed the whole GPU to a pool allocator at start-up, or a latency-critical loop that must not
+ * risk an out-of-memory failure mid-run. Such callers cannot create an ft_comm (its creation allocates
+ * the scratch buffers), so this entry point keeps ALL of its scratch - receive buffers, per-rank control
+ * blocks, epoch/completion/error words - in one static __device__ array inside the library
+ * (about 4 MiB, resident on every GPU that loads the library, until the process exits). The call itself
+ * performs no cudaMalloc, cudaFree, host heap allocation or any other allocating routine.
+ *
+ * Limits (rejected with FT_ERR_INVALID and a message in ft_last_error()):
+ *   nranks <= FT_NOALLOC_MAX_RANKS (8), count * sizeof(dtype) <= FT_NOALLOC_MAX_BYTES (16384) per rank.
+ * sendbufs[i] / recvbufs[i]: device pointers of logical rank i (sendbufs == NULL or an entry equal to
+ * FT_IN_PLACE means in place). Every recvbuf receives the same reduced vector, bit-identical to what
+ * ft_allreduce_multi produces with the one-shot algorithm.
+ *
+ * Set-up: the FIRST call on each device (with that device current) looks up the device address of the
+ * scratch array and writes the control blocks into it with a synchronous copy. Make that first call
+ * before any stream capture is started on the device.
+ * Sharing: every call on a device uses the same array, and the array keeps the previous call's contents.
+ * The call clears what has to start from zero (completion counters, error words) in stream order before
+ * the kernel; everything else is protected by per-call tags. Two calls whose kernels overlap on the GPU
+ * (different streams, or different host threads without ordering) race on the array: serialise them. */
+#define FT_NOALLOC_MAX_RANKS 8
+#define FT_NOALLOC_MAX_BYTES 16384
+ft_result_t ft_allreduce_emulated_noalloc(const void* const* sendbufs, void* const* recvbufs, int nranks,
+                                          size_t count, ft_dtype_t dtype, ft_op_t op, void* stream);
+
 #ifdef STANDALONE_TEST
 /* Source-level alias for code written against the reference benchmark (benchmark.cpp:153). */
 #define MPI_Allreduce_FT(send, recv, count, dtype, op, comm) \
