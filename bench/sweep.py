@@ -30,6 +30,7 @@ def main():
     ap.add_argument("--all-widths", action="store_true")
     ap.add_argument("--staging", action="store_true")
     ap.add_argument("--factor", type=int, default=4)
+    ap.add_argument("--tma", type=int, default=-1, help="1/0 force TMA-staged P2P tiles on/off")
     ap.add_argument("--tune", action="store_true", help="scan CTAs x tile bytes at --max-bytes instead of sweeping sizes")
     ap.add_argument("--tune-sizes", default="", help="comma list of message bytes: scan CTAs x tile at each (small grid)")
     args = ap.parse_args()
@@ -38,6 +39,8 @@ def main():
     dev = torch.device("cuda", local)
     dist.init_process_group("nccl", device_id=dev)
     comm = ft.init()
+    if args.tma >= 0:
+        comm.set_tma(bool(args.tma))
     tdt = torch.float32 if args.dtype == "fp32" else torch.bfloat16
     es = 4 if args.dtype == "fp32" else 2
     maxcount = args.max // es

@@ -73,6 +73,8 @@ struct StagedArgs {
   long long win_off0;    // window byte offset inside the segment ...
   long long win_stride;  // ... plus (epoch & 1) * win_stride (0 in registered mode)
   unsigned long long timeout_ns;  // 0 = spin forever
+  int use_tma;  // CUDA back end: stage peer chunks through shared memory with cp.async.bulk (TMA)
+  int reserved_;
   RankCall rc[FT_MAX_LOCAL];
 };
 

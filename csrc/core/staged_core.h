@@ -58,6 +58,8 @@ struct StagedCta {
   uint64_t E;        // flag base of this call
   long long woff;    // byte offset of the window inside the segment
   int* abort_flag;
+  bool use_tma_;     // CUDA only: TMA-staged tiles (see kernels/tma_tiles.cuh)
+  uint32_t pipe_it;  // chunks pushed through the shared-memory ring so far (same value in every thread)
 
   FT_DEV StagedCta(BE& be_, const StagedArgs& a_, const RankCall& rc_, int cta_)
       : be(be_), a(a_), rc(rc_), cd(*rc_.comm), r(rc_.comm->rank), cta(cta_) {
@@ -65,6 +67,9 @@ struct StagedCta {
     E = epoch_base(epoch);
     woff = a.win_off0 + (long long)(epoch & 1) * a.win_stride;
     abort_flag = be.abort_ptr();
+    // bulk copies need 16-byte multiples: the ragged last vector of an odd-sized message stays on the LDG path
+    use_tma_ = BE::kTma && a.use_tma && VE > 1 && (a.lay.count % VE == 0);  // host guarantees this for the TMA kernel
+    pipe_it = 0;
   }
 
   // ---- flags --------------------------------------------------------------------------------------
@@ -731,7 +736,9 @@ struct StagedCta {
   }
 
   // ---- the whole call, for this CTA ---------------------------------------------------------------------
-  FT_DEV void run() {
+  // TMA = true is the kernel whose tiles are staged through shared memory by cp.async.bulk (CUDA only; the
+  // host selects it only for 16-byte-multiple messages on the vector path).
+  template <bool TMA = false> FT_DEV void run() {
     const int G = a.ctas, m = a.plan.nstages, nt = a.lay.ntiles;
     const int mine = cta < nt ? (nt - cta + G - 1) / G : 0;  // my tiles: t = cta + j*G
     constexpr int CU = (VE == 1) ? 1 : 8;
@@ -751,7 +758,8 @@ struct StagedCta {
     for (int k = 0; k < m; ++k) {
       for (int j = 0; j < mine; ++j) {
         wait_group(k == 0 ? (int)PH_IN : PH_RS0 + k - 1, k, E + j + 1);
-        rs_dispatch(k, cta + j * G);
+        if constexpr (TMA) be.template rs_tile_tma<T, IO, Op, VE>(*this, k, cta + j * G);
+        else rs_dispatch(k, cta + j * G);
         be.sync();
         // consumers: RS stage k+1 pulls from its stage-(k+1) group; after the last RS stage the AG of
         // the same stage pulls
@@ -763,7 +771,8 @@ struct StagedCta {
     for (int k = m - 1; k >= 0; --k) {
       for (int j = 0; j < mine; ++j) {
         wait_group(k == m - 1 ? PH_RS0 + k : PH_AG0 + k + 1, k, E + j + 1);
-        ag_tile<CU>(k, cta + j * G);
+        if constexpr (TMA) be.template ag_tile_tma<T, IO, Op, VE>(*this, k, cta + j * G);
+        else ag_tile<CU>(k, cta + j * G);
         if (k > 0) {
           be.sync();
           signal_group(PH_AG0 + k, k - 1, E + j + 1);

@@ -13,6 +13,9 @@
 namespace ft {
 
 struct CpuBE {
+  static constexpr bool kTma = false;  // the TMA-staged tiles exist only on the GPU
+  template <typename T, typename IO, class Op, int VE, class Cta> void rs_tile_tma(Cta&, int, int) {}
+  template <typename T, typename IO, class Op, int VE, class Cta> void ag_tile_tma(Cta&, int, int) {}
   int abort_ = 0;
   int tid() const { return 0; }
   int nthr() const { return 1; }

@@ -14,12 +14,19 @@
 
 #include "../core/comm_dev.h"
 #include "../core/types.h"
+#include "tma_tiles.cuh"
 
 namespace ft {
 
 struct CudaBE {
+  static constexpr bool kTma = true;
   int* abort_;
-  __device__ __forceinline__ explicit CudaBE(int* abort_smem) : abort_(abort_smem) {}
+  TmaRing ring_;
+  __device__ __forceinline__ CudaBE(int* abort_smem, const TmaRing& ring) : abort_(abort_smem), ring_(ring) {}
+  template <typename T, typename IO, class Op, int VE, class Cta>
+  __device__ __forceinline__ void rs_tile_tma(Cta& c, int k, int t) { rs_tile_tma_impl<T, IO, Op, VE>(c, ring_, k, t); }
+  template <typename T, typename IO, class Op, int VE, class Cta>
+  __device__ __forceinline__ void ag_tile_tma(Cta& c, int k, int t) { ag_tile_tma_impl<T, IO, Op, VE>(c, ring_, k, t); }
   __device__ __forceinline__ int tid() const { return (int)threadIdx.x; }
   __device__ __forceinline__ int nthr() const { return (int)blockDim.x; }
   __device__ __forceinline__ void sync() { __syncthreads(); }

@@ -16,14 +16,21 @@ namespace ft {
 
 template <typename T, typename IO, class Op, int VE, int ALGO>
 __global__ void __launch_bounds__(FT_MAX_THREADS, 1) ft_allreduce_kernel(const __grid_constant__ StagedArgs a) {
+  extern __shared__ __align__(128) unsigned char ft_dyn_smem[];
   __shared__ int s_abort;
   if (threadIdx.x == 0) s_abort = 0;
   __syncthreads();
   const int lr = (int)blockIdx.x / a.ctas;
   const int cta = (int)blockIdx.x - lr * a.ctas;
-  CudaBE be(&s_abort);
+  TmaRing ring;
+  ring.ring = (char*)ft_dyn_smem;
+  ring.full = (uint64_t*)(ft_dyn_smem + kTmaRingBytes);
+  ring.empty = ring.full + kTmaStages;
+  if constexpr (ALGO == ALGO_STAGED_TMA) tma_ring_init(ring, ((int)blockDim.x >> 5) - 1);
+  CudaBE be(&s_abort, ring);
   StagedCta<CudaBE, T, IO, Op, VE> k(be, a, a.rc[lr], cta);
-  if constexpr (ALGO == ALGO_STAGED) k.run();
+  if constexpr (ALGO == ALGO_STAGED) k.template run<false>();
+  else if constexpr (ALGO == ALGO_STAGED_TMA) k.template run<true>();
   else if constexpr (ALGO == ALGO_NVLS) k.run_nvls();
   else if constexpr (ALGO == ALGO_ONESHOT) k.run_oneshot();
   else k.run_ring();
@@ -35,17 +42,33 @@ struct CudaLaunch {
   static cudaError_t go(const LaunchCtx* c) {
     auto kern = ft_allreduce_kernel<T, IO, Op, VE, ALGO>;
     dim3 grid((unsigned)(c->args->nlocal * c->args->ctas)), block((unsigned)c->threads);
+    size_t smem = 0;
+    if (ALGO == ALGO_STAGED_TMA) {
+      smem = kTmaSmemBytes;
+      static bool attr_set[64] = {};  // per instantiation, per device
+      int dev = 0;
+      cudaGetDevice(&dev);
+      if (dev >= 0 && dev < 64 && !attr_set[dev]) {
+        cudaError_t e = cudaFuncSetAttribute((const void*)kern, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem);
+        if (e != cudaSuccess) return e;
+        attr_set[dev] = true;
+      }
+    }
     if (c->cooperative) {
       void* params[] = {(void*)c->args};
-      return cudaLaunchCooperativeKernel((const void*)kern, grid, block, params, 0, c->stream);
+      return cudaLaunchCooperativeKernel((const void*)kern, grid, block, params, smem, c->stream);
     }
-    kern<<<grid, block, 0, c->stream>>>(*c->args);
+    kern<<<grid, block, smem, c->stream>>>(*c->args);
     return cudaGetLastError();
   }
   static void run(LaunchCtx* c) {
     c->supported = true;
     switch (c->algo) {
       case ALGO_STAGED: c->err = go<ALGO_STAGED>(c); break;
+      case ALGO_STAGED_TMA:
+        if constexpr (VE > 1) c->err = go<ALGO_STAGED_TMA>(c);
+        else c->supported = false;
+        break;
       case ALGO_ONESHOT: c->err = go<ALGO_ONESHOT>(c); break;
       case ALGO_RING: c->err = go<ALGO_RING>(c); break;
       case ALGO_NVLS:

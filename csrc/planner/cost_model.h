@@ -44,6 +44,8 @@ int legacy_choose(const std::vector<Widths>& trees, int total_nodes, double chun
 
 // ---------------------------------------------------------------------------------------------
 enum Algo { ALGO_AUTO = 0, ALGO_ONESHOT = 1, ALGO_STAGED = 2, ALGO_NVLS = 3, ALGO_RING = 4 };
+// internal kernel selector (not a user-visible algorithm): the P2P stages with TMA-staged tiles
+enum { ALGO_STAGED_TMA = 5 };
 const char* algo_name(int a);
 int algo_from_name(const std::string& s);  // -1 if unknown
 

@@ -100,6 +100,7 @@ struct ft_comm {
   int algo_override = ALGO_AUTO;
   LinkModel model;
   int ctas_override = 0, threads_override = 0;
+  int tma_override = -1;  // -1: env FT_TMA / default
   long long tile_override = 0;
   unsigned long long timeout_ns = 20000000000ull;
   int sm_count = 148;
@@ -520,9 +521,15 @@ ft_result_t do_allreduce(ft_comm* c, const void* const* send, void* const* recv,
     rc.mc = seg ? seg->mc_base : nullptr;
   }
 
+  // TMA-staged tiles: vector path, whole 16-byte vectors only, and a block size that keeps every bulk copy
+  // 16-byte aligned (it always is: blocks are padded to 16 bytes).
+  const bool tma = algo == ALGO_STAGED && vec && (count % (size_t)(16 / es) == 0) && sh.threads >= 64 &&
+                   (c->tma_override >= 0 ? c->tma_override : env_int("FT_TMA", 0)) != 0;
+  a.use_tma = tma ? 1 : 0;
+
   LaunchCtx ctx;
   ctx.args = &a;
-  ctx.algo = algo;
+  ctx.algo = tma ? (int)ALGO_STAGED_TMA : algo;
   ctx.threads = sh.threads;
   ctx.cooperative = c->kind == COMM_EMULATED && N > 1;
   ctx.stream = stream;
@@ -670,6 +677,10 @@ ft_result_t ft_comm_create_emulated(ft_comm_t** out, int nranks, int device, con
   rc = finish_create(c);
   if (rc != FT_SUCCESS) { delete c; return rc; }
   c->model.has_nvls = false;
+  // every "link" is local HBM here: no fan-in effect, cheap hops -> the flat plan wins
+  c->model.beta_p2p_GBps = c->model.beta_p2p_1peer_GBps = 600.0;
+  c->model.alpha_sync_us = 1.5;
+  c->model.alpha_peer_us = 0.2;
   *out = c;
   return FT_SUCCESS;
 }
@@ -759,6 +770,11 @@ ft_result_t ft_comm_set_launch(ft_comm_t* c, int ctas, int threads, long long ti
   c->ctas_override = ctas;
   c->threads_override = threads;
   c->tile_override = tile_bytes;
+  return FT_SUCCESS;
+}
+
+ft_result_t ft_comm_set_tma(ft_comm_t* c, int on) {
+  c->tma_override = on < 0 ? -1 : (on ? 1 : 0);
   return FT_SUCCESS;
 }
 

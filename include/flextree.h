@@ -141,6 +141,10 @@ ft_result_t ft_comm_set_link_model(ft_comm_t*, const ft_link_model_t*);
 /* Launch shape overrides: CTAs per rank, threads per CTA, tile bytes (0 = automatic). */
 ft_result_t ft_comm_set_launch(ft_comm_t*, int ctas, int threads, long long tile_bytes);
 
+/* P2P stage kernels: 1 = stage peer chunks through shared memory with TMA bulk copies (cp.async.bulk +
+ * mbarrier ring), 0 = register-staged 16-byte loads, -1 = default (env FT_TMA). */
+ft_result_t ft_comm_set_tma(ft_comm_t*, int on);
+
 /* Collective: make sure a message of `bytes` fits the staging window (allocates + exchanges handles
  * if it has to grow). Call it before stream capture. */
 ft_result_t ft_comm_reserve(ft_comm_t*, size_t bytes);

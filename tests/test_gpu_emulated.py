@@ -244,6 +244,56 @@ def test_cuda_graph_capture_and_replay(comms):
     c.set_algo("auto")
 
 
+@pytest.mark.parametrize("n,widths", [(2, [2]), (4, [2, 2]), (8, [8]), (8, [2, 4]), (6, [3, 2])])
+def test_tma_staged_tiles_match_register_path(comms, n, widths):
+    """The TMA variant (cp.async.bulk ring + mbarriers) must give the same bits as the LDG variant."""
+    c = comms(n)
+    c.set_algo("stages")
+    c.set_widths(widths)
+    for count, dt in ((4096, np.float32), (1 << 20, np.float32), (300000, np.float32), (65536 + 8, np.int32)):
+        if np.dtype(dt).kind == "f":
+            xs = [RNG.standard_normal(count).astype(dt) for _ in range(n)]
+        else:
+            xs = [RNG.integers(-10**6, 10**6, count, dtype=dt) for _ in range(n)]
+        c.set_tma(False)
+        ref, _ = run(c, xs, out_of_place=True)
+        c.set_tma(True)
+        got, src = run(c, xs, out_of_place=True)
+        got2, _ = run(c, xs)
+        for r in range(n):
+            np.testing.assert_array_equal(got[r], ref[r], err_msg=f"{widths} count {count} rank {r}")
+            np.testing.assert_array_equal(got2[r], ref[r])
+            np.testing.assert_array_equal(src[r], xs[r])
+    # bf16 wire + fused scale on fp32 buffers, and registered buffers, through the TMA kernel
+    xs = [RNG.standard_normal(40000).astype(np.float32) for _ in range(n)]
+    c.set_tma(False)
+    ts = [dev(x) for x in xs]
+    c.allreduce_multi(ts, scale=0.5, wire_dtype=torch.bfloat16)
+    c.set_tma(True)
+    ts2 = [dev(x) for x in xs]
+    c.allreduce_multi(ts2, scale=0.5, wire_dtype=torch.bfloat16)
+    torch.cuda.synchronize()
+    assert c.error() == 0
+    for a_, b_ in zip(ts, ts2):
+        assert torch.equal(a_, b_)
+    bufs = c.symm_empty(100000, torch.float32)
+    for it in range(2):
+        for r in range(n):
+            bufs[r].copy_(dev(xs[r][:100000] if xs[r].size >= 100000 else np.resize(xs[r], 100000)))
+        expect = [b.clone() for b in bufs]
+        c.set_tma(False)
+        c.allreduce_multi(expect)
+        c.set_tma(True)
+        c.allreduce_multi(bufs)
+        torch.cuda.synchronize()
+        assert c.error() == 0 and c.last_call()["mode"] == "registered"
+        for a_, b_ in zip(expect, bufs):
+            assert torch.equal(a_, b_)
+    c.set_tma(None)
+    c.set_widths(None)
+    c.set_algo("auto")
+
+
 def test_single_rank_fast_path():
     c = ft.Communicator.emulated(1, 0)
     x = torch.arange(1000, device="cuda", dtype=torch.float32)
