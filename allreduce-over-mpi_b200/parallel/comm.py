@@ -167,6 +167,10 @@ class Communicator:
     def set_launch(self, ctas=0, threads=0, tile_bytes=0):
         _check(self._L, self._L.ft_comm_set_launch(self._h, ctas, threads, tile_bytes), "ft_comm_set_launch")
 
+    def set_max_ctas(self, n):
+        """Cap the SMs a collective may occupy (0 = whole GPU)."""
+        _check(self._L, self._L.ft_comm_set_max_ctas(self._h, int(n)), "ft_comm_set_max_ctas")
+
     def set_tma(self, on):
         """P2P stages: True = TMA-staged tiles (cp.async.bulk ring), False = register-staged loads, None = default."""
         _check(self._L, self._L.ft_comm_set_tma(self._h, -1 if on is None else int(bool(on))), "ft_comm_set_tma")

@@ -13,8 +13,10 @@ import torch
 
 
 class FlexTreeHookState:
-    def __init__(self, comm, wire_dtype=None, average=True, side_stream=True):
+    def __init__(self, comm, wire_dtype=None, average=True, side_stream=True, max_ctas=32):
         self.comm = comm
+        if max_ctas:
+            comm.set_max_ctas(max_ctas)  # the collective overlaps backward: do not take the whole GPU
         self.wire_dtype = wire_dtype
         self.average = average
         self.stream = torch.cuda.Stream(device=comm.device) if side_stream else None

@@ -113,7 +113,7 @@ struct StagedCta {
       int p = base + j * g;
       if (p == r) continue;
       spin(cd.pad[r] + pad_slot(phase, cta, p), val, phase, p);
-      be.fence();
+      be.acquire(cd.pad[r] + pad_slot(phase, cta, p));
     }
     be.sync();
   }
@@ -669,7 +669,7 @@ struct StagedCta {
     const int N = a.plan.nranks, left = (r + N - 1) % N;
     if (be.tid() == 0) {
       spin(cd.pad[r] + pad_slot(PH_RS0, cta, left), val, PH_RS0, left);
-      be.fence();
+      be.acquire(cd.pad[r] + pad_slot(PH_RS0, cta, left));
     }
     be.sync();
   }
@@ -712,7 +712,7 @@ struct StagedCta {
         be.fence();
         be.flag_st(cd.pad[left] + pad_slot(PH_END, cta, r), E + 1);
         spin(cd.pad[r] + pad_slot(PH_END, cta, right), E + 1, PH_END, right);
-        be.fence();
+        be.acquire(cd.pad[r] + pad_slot(PH_END, cta, right));
       }
       be.sync();
     }

@@ -25,6 +25,7 @@ struct CpuBE {
   uint64_t flag_ld(const uint64_t* p) { return __atomic_load_n(p, __ATOMIC_ACQUIRE); }
   void flag_st(uint64_t* p, uint64_t v) { __atomic_store_n(p, v, __ATOMIC_RELEASE); }
   void fence() { __atomic_thread_fence(__ATOMIC_SEQ_CST); }
+  void acquire(const uint64_t* p) { (void)__atomic_load_n(p, __ATOMIC_ACQUIRE); }
   uint64_t load_epoch(const uint64_t* p) { return __atomic_load_n(p, __ATOMIC_ACQUIRE); }
   unsigned err_ld(const unsigned* p) { return __atomic_load_n(p, __ATOMIC_RELAXED); }
   void err_set(unsigned* p, unsigned v) {

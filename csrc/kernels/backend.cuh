@@ -101,6 +101,14 @@ struct CudaBE {
     asm volatile("st.relaxed.sys.global.u64 [%0], %1;" ::"l"(p), "l"(v) : "memory");
   }
   __device__ __forceinline__ void fence() { asm volatile("fence.acq_rel.sys;" ::: "memory"); }
+  // Acquire side of a flag hop: after the relaxed spin has seen the value, one ld.acquire.sys of the same
+  // word orders everything after it (LDG.STRONG.SYS + CCTL.IVALL, no MEMBAR.SYS - measurably cheaper than a
+  // full fence on every hop).
+  __device__ __forceinline__ void acquire(const uint64_t* p) {
+    uint64_t v;
+    asm volatile("ld.acquire.sys.global.u64 %0, [%1];" : "=l"(v) : "l"(p) : "memory");
+    (void)v;
+  }
   __device__ __forceinline__ uint64_t load_epoch(const uint64_t* p) {
     uint64_t v;
     asm volatile("ld.relaxed.gpu.global.u64 %0, [%1];" : "=l"(v) : "l"(p) : "memory");

@@ -162,7 +162,8 @@ double predict_us(const LinkModel& m, int algo, const Widths& widths, int n, dou
     }
     case ALGO_NVLS: {
       if (!m.has_nvls) return 1e30;
-      double t = m.alpha_launch_us + m.alpha_nvls_us;
+      // three all-to-all flag hops (input ready, reduced, exit) + a constant for the multicast stores in flight
+      double t = m.alpha_launch_us + 3.0 * hop(n) + m.alpha_nvls_us;
       if (!registered) t += S / (m.gamma_hbm_GBps * 1e3) * 4.0 / 8.0;
       // per-GPU link traffic (each direction): every rank's copy of all N blocks goes up to the switch once
       // (S, including the requester's own copy) plus its reduced block broadcast (S/N)  ->  (1 + 1/N) S,

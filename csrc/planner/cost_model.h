@@ -56,7 +56,7 @@ struct LinkModel {
   double alpha_sync_us = 2.8;     // one release->acquire flag hop between two GPUs (incl. fence.sys)
   double alpha_peer_us = 0.45;    // extra per additional peer signalled/polled in the same hop
   double alpha_ll_us = 4.0;       // one LL (data+flag) hop
-  double alpha_nvls_us = 18.0;    // the three hops of the NVLS path (multimem stores in flight)
+  double alpha_nvls_us = 0.0;     // extra fixed cost of the NVLS path on top of its three flag hops
   // bandwidths, GB/s
   double beta_p2p_GBps = 420.0;        // pull bandwidth with >= fanin_knee concurrent peers (LDG path)
   double beta_p2p_1peer_GBps = 500.0;  // pull bandwidth from a single peer

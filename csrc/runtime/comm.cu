@@ -101,6 +101,7 @@ struct ft_comm {
   LinkModel model;
   int ctas_override = 0, threads_override = 0;
   int tma_override = -1;  // -1: env FT_TMA / default
+  int max_ctas = 0;       // 0: whole GPU; >0: cap (leave SMs to overlapping compute, e.g. DDP backward)
   long long tile_override = 0;
   unsigned long long timeout_ns = 20000000000ull;
   int sm_count = 148;
@@ -275,12 +276,14 @@ struct Shape {
 // system fence + a flag hop, so tiles should be as large as the message allows (512 KiB per block-chunk
 // was the sweet spot; 2 MiB starves the grid). Every rank must derive the same shape from the same
 // arguments.
-Shape pick_shape(const ft_comm* c, int algo, int mode, size_t msg_bytes, int nranks, int esize) {
+Shape pick_shape(const ft_comm* c, int algo, int mode, bool tma, size_t msg_bytes, int nranks, int esize) {
   Shape s;
   s.threads = c->threads_override ? c->threads_override : env_int("FT_THREADS", 512);
   if (s.threads > FT_MAX_THREADS) s.threads = FT_MAX_THREADS;
   if (s.threads < 32) s.threads = 32;
   int max_ctas = c->sm_count;  // one resident CTA per SM at 512 threads x <=128 registers
+  const int cap = c->max_ctas > 0 ? c->max_ctas : env_int("FT_MAX_CTAS", 0);
+  if (cap > 0 && cap < max_ctas) max_ctas = cap;
   if (max_ctas > FT_MAX_CTAS) max_ctas = FT_MAX_CTAS;
   if (c->kind == COMM_EMULATED) {
     // cooperative launch: nranks*ctas CTAs must be co-resident
@@ -290,8 +293,10 @@ Shape pick_shape(const ft_comm* c, int algo, int mode, size_t msg_bytes, int nra
   }
   const long long block_bytes = ((long long)msg_bytes + nranks - 1) / nranks;
   // P2P tiles: a tile's work is ~nranks * tile bytes of loads; 512 KiB was best at N=2 and 64-128 KiB at N=8
-  const long long kMinTile = env_ll("FT_MIN_TILE_BYTES", 16 << 10);
-  long long kMaxTile = env_ll("FT_MAX_TILE_BYTES", (1 << 20) / (nranks < 2 ? 2 : nranks));
+  // With TMA-staged tiles the ring drains at every tile boundary, so tiles should be large (measured at
+  // N=2: 1-2 MiB best at 256 MiB, 64 KiB x 32 CTAs best at 4 MiB).
+  const long long kMinTile = env_ll("FT_MIN_TILE_BYTES", tma ? (64 << 10) : (16 << 10));
+  long long kMaxTile = env_ll("FT_MAX_TILE_BYTES", (tma ? (4 << 20) : (1 << 20)) / (nranks < 2 ? 2 : nranks));
   if (kMaxTile < kMinTile) kMaxTile = kMinTile;
   int ctas;
   long long tile;
@@ -440,6 +445,11 @@ ft_result_t do_allreduce(ft_comm* c, const void* const* send, void* const* recv,
   }
   if (algo == ALGO_STAGED && widths.empty()) widths = {N};
   if (algo != ALGO_STAGED) widths = {N};
+  if (est == 0) {  // forced algorithm / widths: still report what the model expects (validation tables)
+    LinkModel m = c->model;
+    m.has_nvls = true;
+    est = predict_us(m, algo, widths, N, (double)msg_bytes, mode == MODE_REGISTERED);
+  }
 
   StagedArgs a;
   memset(&a, 0, sizeof a);
@@ -449,7 +459,12 @@ ft_result_t do_allreduce(ft_comm* c, const void* const* send, void* const* recv,
   }
   if (algo == ALGO_RING && mode == MODE_REGISTERED && (apply_scale || io_dtype != wire_dtype)) mode = MODE_STAGING;
 
-  Shape sh = pick_shape(c, algo, mode, msg_bytes, N, es);
+  // TMA-staged tiles: vector path and whole 16-byte vectors only (blocks are padded to 16 bytes, so every
+  // bulk copy is aligned).
+  const bool tma = algo == ALGO_STAGED && vec && (count % (size_t)(16 / es) == 0) &&
+                   (c->threads_override == 0 || c->threads_override >= 64) &&
+                   (c->tma_override >= 0 ? c->tma_override : env_int("FT_TMA", 1)) != 0;
+  Shape sh = pick_shape(c, algo, mode, tma, msg_bytes, N, es);
   a.lay = make_layout((long long)count, N, es, sh.tile_bytes, vec);
   // flag values encode the tile ordinal in FT_EPOCH_SHIFT bits (ring: steps * tiles)
   {
@@ -521,10 +536,6 @@ ft_result_t do_allreduce(ft_comm* c, const void* const* send, void* const* recv,
     rc.mc = seg ? seg->mc_base : nullptr;
   }
 
-  // TMA-staged tiles: vector path, whole 16-byte vectors only, and a block size that keeps every bulk copy
-  // 16-byte aligned (it always is: blocks are padded to 16 bytes).
-  const bool tma = algo == ALGO_STAGED && vec && (count % (size_t)(16 / es) == 0) && sh.threads >= 64 &&
-                   (c->tma_override >= 0 ? c->tma_override : env_int("FT_TMA", 0)) != 0;
   a.use_tma = tma ? 1 : 0;
 
   LaunchCtx ctx;
@@ -770,6 +781,12 @@ ft_result_t ft_comm_set_launch(ft_comm_t* c, int ctas, int threads, long long ti
   c->ctas_override = ctas;
   c->threads_override = threads;
   c->tile_override = tile_bytes;
+  return FT_SUCCESS;
+}
+
+ft_result_t ft_comm_set_max_ctas(ft_comm_t* c, int max_ctas) {
+  if (max_ctas < 0) return FT_ERR_INVALID;
+  c->max_ctas = max_ctas;
   return FT_SUCCESS;
 }
 

@@ -141,6 +141,11 @@ ft_result_t ft_comm_set_link_model(ft_comm_t*, const ft_link_model_t*);
 /* Launch shape overrides: CTAs per rank, threads per CTA, tile bytes (0 = automatic). */
 ft_result_t ft_comm_set_launch(ft_comm_t*, int ctas, int threads, long long tile_bytes);
 
+/* Upper bound on the CTAs (= SMs) a collective may occupy; 0 = no bound. Use it when the collective
+ * overlaps compute (DDP backward): NVLS needs 8 CTAs anyway, the TMA P2P stages reach most of their
+ * bandwidth from ~32. Same as env FT_MAX_CTAS. */
+ft_result_t ft_comm_set_max_ctas(ft_comm_t*, int max_ctas);
+
 /* P2P stage kernels: 1 = stage peer chunks through shared memory with TMA bulk copies (cp.async.bulk +
  * mbarrier ring), 0 = register-staged 16-byte loads, -1 = default (env FT_TMA). */
 ft_result_t ft_comm_set_tma(ft_comm_t*, int on);
