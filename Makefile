@@ -31,7 +31,7 @@ HOST_OBJ := $(HOST_SRC:%.cc=$(B)/%.o)
 CUDA_OBJ := $(CUDA_SRC:%.cu=$(B)/%.cu.o)
 RT_CC_OBJ := $(RT_CC_SRC:%.cc=$(B)/%.o)
 
-.PHONY: all host cuda tools clean
+.PHONY: all host cuda tools clean tsan fdtest memcheck racecheck
 all: host cuda tools
 host: $(B)/libflextree_host.so
 cuda: $(LIBDIR)/libflextree.so
@@ -60,6 +60,22 @@ $(B)/ft_bench: csrc/tools/ft_bench.cu $(LIBDIR)/libflextree.so
 
 $(B)/nccl_bench: csrc/tools/nccl_bench.cu
 	$(NVCC) $(NVFLAGS) -o $@ $< -lnccl
+
+# ThreadSanitizer run of the algorithm templates on the CPU world (the reference has no
+# sanitizer targets at all) and the SCM_RIGHTS fd-channel test.
+tsan:
+	$(CXX) -std=c++17 -O1 -g -fsanitize=thread -Wno-unknown-pragmas -Iinclude -DFT_ONLY_F32 -o $(B)/tsan_world \
+	  tests/cpp/tsan_world.cc csrc/host/host_world.cc csrc/host/host_run_all.cc csrc/host/host_run_g1.cc \
+	  csrc/planner/factorize.cc csrc/planner/cost_model.cc -lpthread
+	$(B)/tsan_world
+fdtest:
+	$(CXX) -std=c++17 -O1 -o $(B)/fd_channel_test tests/cpp/fd_channel_test.cc
+	$(B)/fd_channel_test 8
+# compute-sanitizer on the single-GPU emulation (one tool per invocation, see B200_PROFILING.md)
+memcheck:
+	compute-sanitizer --tool memcheck python bench/ncu_target.py
+racecheck:
+	compute-sanitizer --tool racecheck python bench/ncu_target.py
 
 clean:
 	rm -rf $(B) $(LIBDIR)/*.so

@@ -44,7 +44,7 @@ class HostWorld:
 
     def allreduce(self, send, recv=None, op="sum", algo="stages", widths=None, ctas=2, tile_bytes=4096,
                   mode=K.MODE_STAGING, scale=None, dtype_code=None, io_dtype_code=None,
-                  timeout_s=20.0, skip_rank=-1):
+                  timeout_s=20.0, skip_rank=-1, lonely=0):
         """send/recv: lists of numpy arrays (one per rank). recv=None -> in place."""
         n = self.n
         recv = send if recv is None else recv
@@ -56,11 +56,11 @@ class HostWorld:
         vp = C.c_void_p * n
         s = vp(*[a.ctypes.data for a in send])
         r = vp(*[a.ctypes.data for a in recv])
-        widths = list(widths) if widths is not None else [n]
+        widths = list(widths) if widths is not None else [n - lonely]
         w = (C.c_int * len(widths))(*widths)
         rc = self._L.ft_host_allreduce(
             self._h, s, r, count, dtype_code, io_dtype_code, K.OPS[op] if isinstance(op, str) else op,
             K.ALGOS[algo] if isinstance(algo, str) else algo, w, len(widths), ctas, tile_bytes, mode,
             1.0 if scale is None else float(scale), 0 if scale is None else 1,
-            int(timeout_s * 1e9), skip_rank)
+            int(timeout_s * 1e9), skip_rank, lonely)
         return rc

@@ -20,7 +20,8 @@ enum Phase {
   PH_RS0 = 1,
   PH_AG0 = 1 + FT_MAX_STAGES,
   PH_END = 1 + 2 * FT_MAX_STAGES,     // "I have finished reading everybody's window" (registered mode)
-  PH_COUNT = 2 + 2 * FT_MAX_STAGES
+  PH_LONELY = 2 + 2 * FT_MAX_STAGES,  // tree rank -> lonely ranks: "my block of this tile is final"
+  PH_COUNT = 3 + 2 * FT_MAX_STAGES
 };
 
 FT_HD size_t pad_slot(int phase, int cta, int src) {
@@ -74,7 +75,7 @@ struct StagedArgs {
   long long win_stride;  // ... plus (epoch & 1) * win_stride (0 in registered mode)
   unsigned long long timeout_ns;  // 0 = spin forever
   int use_tma;  // CUDA back end: stage peer chunks through shared memory with cp.async.bulk (TMA)
-  int reserved_;
+  int lonely;   // ranks plan.nranks .. plan.nranks+lonely-1 are outside the tree (N = tree + lonely)
   RankCall rc[FT_MAX_LOCAL];
 };
 

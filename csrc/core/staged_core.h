@@ -735,6 +735,100 @@ struct StagedCta {
     }
   }
 
+  // ---- lonely ranks (world size = tree ranks + L, the reference's "+1" trees) ------------------------------
+  // Capability parity: the lonely ops of Send_Ops/Recv_Ops (mpi_mod.hpp:172-178, :208-211) and the lonely
+  // branches of tree_allreduce (:981-987, :1019-1026, :1041-1099), which the reference ships as stubs
+  // ("must be modified before use"). Here: a lonely rank publishes its whole vector in its window; tree
+  // rank r folds block r of every lonely rank into its fully reduced block right after the last
+  // reduce-scatter stage (lonely ranks in ascending order, after all tree contributions); the lonely
+  // ranks then gather block b straight from tree rank b.
+  template <int UNR> FT_DEV void lonely_fold_tile(int t) {
+    const int Tn = a.plan.nranks, L = a.lonely;
+    long long start;
+    const int n = tile_valid32(r, t, &start);
+    if (n <= 0) return;
+    const int nvec = (n + VE - 1) / VE;
+    char* wr = rc.win[r] + woff;
+    const int nth = be.nthr(), tid = be.tid();
+    for (int q = tid; q < nvec; q += nth) {
+      const long long off = (start + (long long)q * VE) * (long long)sizeof(T);
+      PackT own = ld_win(wr, off, false);
+      A acc[VE];
+#pragma unroll
+      for (int i = 0; i < VE; ++i) acc[i] = EL::up(own.e[i]);
+      for (int l = 0; l < L; ++l) {
+        PackT in = ld_win(rc.win[Tn + l] + woff, off, true);
+#pragma unroll
+        for (int i = 0; i < VE; ++i) acc[i] = Op::apply(acc[i], EL::up(in.e[i]));
+      }
+      PackT o;
+#pragma unroll
+      for (int i = 0; i < VE; ++i) o.e[i] = EL::down(acc[i]);
+      st_win(wr, off, o);
+    }
+  }
+  // a lonely rank's gather: block b of tile t comes from tree rank b
+  template <int UNR> FT_DEV void lonely_out_tile(int t) {
+    const Layout& L_ = a.lay;
+    const int Tn = a.plan.nranks;
+    const int CV = (int)((L_.tile + VE - 1) / VE);
+    const int total = Tn * CV;
+    IO* y = (IO*)rc.recv;
+    const int nth = be.nthr(), tid = be.tid();
+    for (int q0 = 0; q0 < total; q0 += nth * UNR) {
+      PackT v[UNR];
+      long long el[UNR];
+      int nv[UNR];
+#pragma unroll
+      for (int u = 0; u < UNR; ++u) {
+        const int q = q0 + u * nth + tid;
+        nv[u] = 0;
+        if (q < total) {
+          const int b = q / CV, vi = q - b * CV;
+          long long start;
+          const int n = tile_valid32(b, t, &start) - vi * VE;
+          if (n > 0) {
+            nv[u] = n < VE ? n : VE;
+            el[u] = start + vi * VE;
+            v[u] = ld_win(rc.win[b] + woff, el[u] * (long long)sizeof(T), true);
+          }
+        }
+      }
+#pragma unroll
+      for (int u = 0; u < UNR; ++u)
+        if (nv[u]) st_user(y, el[u], wire_to_io(v[u]), nv[u]);
+    }
+  }
+  // flags between the tree and the lonely ranks (any-to-any inside the two sets)
+  FT_DEV void signal_ranks(int phase, int first, int count, uint64_t val) {
+    for (int j = be.tid(); j < count; j += be.nthr()) {
+      be.fence();
+      be.flag_st(cd.pad[first + j] + pad_slot(phase, cta, r), val);
+    }
+  }
+  FT_DEV void wait_ranks(int phase, int first, int count, uint64_t val) {
+    for (int j = be.tid(); j < count; j += be.nthr()) {
+      spin(cd.pad[r] + pad_slot(phase, cta, first + j), val, phase, first + j);
+      be.acquire(cd.pad[r] + pad_slot(phase, cta, first + j));
+    }
+    be.sync();
+  }
+  FT_DEV void run_lonely_rank() {
+    const int G = a.ctas, nt = a.lay.ntiles, Tn = a.plan.nranks;
+    const int mine = cta < nt ? (nt - cta + G - 1) / G : 0;
+    constexpr int CU = (VE == 1) ? 1 : 8;
+    for (int j = 0; j < mine; ++j) {
+      copy_in_all_tile<CU>(cta + j * G);
+      be.sync();
+      signal_ranks(PH_IN, 0, Tn, E + j + 1);
+    }
+    for (int j = 0; j < mine; ++j) {
+      wait_ranks(PH_LONELY, 0, Tn, E + j + 1);
+      lonely_out_tile<CU>(cta + j * G);
+    }
+    be.finish(cd, a.ctas);
+  }
+
   // ---- the whole call, for this CTA ---------------------------------------------------------------------
   // TMA = true is the kernel whose tiles are staged through shared memory by cp.async.bulk (CUDA only; the
   // host selects it only for 16-byte-multiple messages on the vector path).
@@ -742,6 +836,10 @@ struct StagedCta {
     const int G = a.ctas, m = a.plan.nstages, nt = a.lay.ntiles;
     const int mine = cta < nt ? (nt - cta + G - 1) / G : 0;  // my tiles: t = cta + j*G
     constexpr int CU = (VE == 1) ? 1 : 8;
+    if (a.lonely > 0 && r >= a.plan.nranks) {  // I am outside the tree
+      run_lonely_rank();
+      return;
+    }
 
     // IN: publish my window to my stage-0 group
     if (a.mode == MODE_STAGING) {
@@ -761,6 +859,12 @@ struct StagedCta {
         if constexpr (TMA) be.template rs_tile_tma<T, IO, Op, VE>(*this, k, cta + j * G);
         else rs_dispatch(k, cta + j * G);
         be.sync();
+        if (a.lonely > 0 && k == m - 1) {  // my block is reduced over the tree: add the lonely ranks' copies
+          wait_ranks(PH_IN, a.plan.nranks, a.lonely, E + j + 1);
+          lonely_fold_tile<1>(cta + j * G);
+          be.sync();
+          signal_ranks(PH_LONELY, a.plan.nranks, a.lonely, E + j + 1);
+        }
         // consumers: RS stage k+1 pulls from its stage-(k+1) group; after the last RS stage the AG of
         // the same stage pulls
         signal_group(PH_RS0 + k, k + 1 < m ? k + 1 : k, E + j + 1);

@@ -97,7 +97,7 @@ unsigned long long ft_host_epoch(void* h, int rank) { return ((HostWorld*)h)->ep
 long long ft_host_allreduce(void* h, const void* const* send, void* const* recv, long long count,
                             int dtype, int io_dtype, int op, int algo, const int* widths, int nstages,
                             int ctas, long long tile_bytes, int mode, double scale, int apply_scale,
-                            unsigned long long timeout_ns, int skip_rank) {
+                            unsigned long long timeout_ns, int skip_rank, int lonely) {
   auto* w = (HostWorld*)h;
   StagedArgs a;
   memset(&a, 0, sizeof a);
@@ -107,14 +107,16 @@ long long ft_host_allreduce(void* h, const void* const* send, void* const* recv,
   } else {
     if (!make_plan(widths, nstages, &a.plan)) return -1;
   }
-  if (a.plan.nranks != w->n) return -2;
+  if (lonely < 0 || a.plan.nranks + lonely != w->n) return -2;
+  if (lonely > 0 && (algo != ALGO_STAGED || mode != MODE_STAGING)) return -8;
+  a.lonely = lonely;
   const int es = dtype_size(dtype), ios = dtype_size(io_dtype);
   if (!es || !ios) return -3;
   bool vec = true;
   for (int r = 0; r < w->n; ++r)
     vec = vec && ((uintptr_t)send[r] % 16 == 0) && ((uintptr_t)recv[r] % 16 == 0);
-  a.lay = make_layout(count, w->n, es, tile_bytes, vec);
-  if ((size_t)(a.lay.block * w->n * es) > w->win_bytes) return -4;
+  a.lay = make_layout(count, a.plan.nranks, es, tile_bytes, vec);
+  if ((size_t)(a.lay.block * a.plan.nranks * es) > w->win_bytes) return -4;
   if (algo == ALGO_ONESHOT) {
     size_t region = (w->ll_bytes / w->n) & ~(size_t)15;
     size_t lines = (size_t)((count * es + 7) / 8);

@@ -97,6 +97,7 @@ struct ft_comm {
 
   // policy
   std::vector<int> widths_override;
+  int lonely_override = 0;  // ranks outside the tree when widths_override multiplies to less than the world size
   int algo_override = ALGO_AUTO;
   LinkModel model;
   int ctas_override = 0, threads_override = 0;
@@ -408,11 +409,21 @@ ft_result_t do_allreduce(ft_comm* c, const void* const* send, void* const* recv,
   // ---- algorithm + widths --------------------------------------------------------------------------------
   int algo = c->algo_override;
   std::vector<int> widths = c->widths_override;
+  int lonely = widths.empty() ? 0 : c->lonely_override;
   if (widths.empty() && getenv("FT_TOPO") && *getenv("FT_TOPO")) {
+    // "2,3+1": a tree of 6 plus one lonely rank (extension; the reference's parser has no lonely syntax)
+    std::string topo = getenv("FT_TOPO");
+    size_t plus = topo.find('+');
+    int extra = 0;
+    if (plus != std::string::npos) {
+      extra = atoi(topo.c_str() + plus + 1);
+      topo = topo.substr(0, plus);
+    }
     int buf[FT_MAX_STAGES + 8];
-    int k = ft_parse_topo(nullptr, N, buf, FT_MAX_STAGES + 8);
-    if (k < 0) return FT_ERR_INVALID;  // product mismatch: the reference exits (mpi_mod.hpp:914-918)
+    int k = ft_parse_topo(topo.c_str(), N - extra, buf, FT_MAX_STAGES + 8);
+    if (k < 0 || extra < 0) return FT_ERR_INVALID;  // product mismatch: the reference exits (mpi_mod.hpp:914-918)
     widths.assign(buf, buf + k);
+    lonely = (k == 1 && buf[0] == 1) ? 0 : extra;
   }
   if (!widths.empty() && widths[0] == 1 && N > 1) {  // "any 1 means ring" (mpi_mod.hpp:907-910)
     algo = ALGO_RING;
@@ -444,7 +455,7 @@ ft_result_t do_allreduce(ft_comm* c, const void* const* send, void* const* recv,
     return FT_ERR_UNSUPPORTED;
   }
   if (algo == ALGO_STAGED && widths.empty()) widths = {N};
-  if (algo != ALGO_STAGED) widths = {N};
+  if (algo != ALGO_STAGED) { widths = {N}; lonely = 0; }
   if (est == 0) {  // forced algorithm / widths: still report what the model expects (validation tables)
     LinkModel m = c->model;
     m.has_nvls = true;
@@ -453,7 +464,11 @@ ft_result_t do_allreduce(ft_comm* c, const void* const* send, void* const* recv,
 
   StagedArgs a;
   memset(&a, 0, sizeof a);
-  if (!make_plan(widths.data(), (int)widths.size(), &a.plan) || a.plan.nranks != N) {
+  if (lonely > 0) {  // lonely trees run on the staged kernel with private windows
+    algo = ALGO_STAGED;
+    mode = MODE_STAGING;
+  }
+  if (!make_plan(widths.data(), (int)widths.size(), &a.plan) || a.plan.nranks + lonely != N) {
     set_last_error("stage widths " + to_string(widths) + " do not multiply to the world size " + std::to_string(N));
     return FT_ERR_INVALID;
   }
@@ -461,18 +476,20 @@ ft_result_t do_allreduce(ft_comm* c, const void* const* send, void* const* recv,
 
   // TMA-staged tiles: vector path and whole 16-byte vectors only (blocks are padded to 16 bytes, so every
   // bulk copy is aligned).
-  const bool tma = algo == ALGO_STAGED && vec && (count % (size_t)(16 / es) == 0) &&
+  const bool tma = algo == ALGO_STAGED && lonely == 0 && vec && (count % (size_t)(16 / es) == 0) &&
                    (c->threads_override == 0 || c->threads_override >= 64) &&
                    (c->tma_override >= 0 ? c->tma_override : env_int("FT_TMA", 1)) != 0;
-  Shape sh = pick_shape(c, algo, mode, tma, msg_bytes, N, es);
-  a.lay = make_layout((long long)count, N, es, sh.tile_bytes, vec);
+  const int T = N - lonely;  // ranks in the tree = number of blocks
+  Shape sh = pick_shape(c, algo, mode, tma, msg_bytes, T, es);
+  a.lay = make_layout((long long)count, T, es, sh.tile_bytes, vec);
+  a.lonely = lonely;
   // flag values encode the tile ordinal in FT_EPOCH_SHIFT bits (ring: steps * tiles)
   {
     long long per_cta = (a.lay.ntiles + sh.ctas - 1) / sh.ctas;
     long long steps = algo == ALGO_RING ? 2LL * N : 1;
     while (per_cta * steps >= (1LL << FT_EPOCH_SHIFT) - 2) {
       sh.tile_bytes *= 2;
-      a.lay = make_layout((long long)count, N, es, sh.tile_bytes, vec);
+      a.lay = make_layout((long long)count, T, es, sh.tile_bytes, vec);
       per_cta = (a.lay.ntiles + sh.ctas - 1) / sh.ctas;
     }
   }
@@ -487,7 +504,7 @@ ft_result_t do_allreduce(ft_comm* c, const void* const* send, void* const* recv,
       return FT_ERR_INVALID;
     }
   } else if (mode == MODE_STAGING) {
-    size_t need = (size_t)a.lay.block * (size_t)N * (size_t)es;
+    size_t need = (size_t)a.lay.block * (size_t)T * (size_t)es;
     cudaStreamCaptureStatus cap = cudaStreamCaptureStatusNone;
     cudaStreamIsCapturing(stream, &cap);
     if (need > c->window_bytes || c->win.empty()) {
@@ -747,6 +764,7 @@ ft_result_t ft_comm_clear_error(ft_comm_t* c) {
 ft_result_t ft_comm_set_widths(ft_comm_t* c, const int* widths, int nstages) {
   if (!widths || nstages <= 0) {
     c->widths_override.clear();
+    c->lonely_override = 0;
     return FT_SUCCESS;
   }
   std::vector<int> w(widths, widths + nstages);
@@ -754,14 +772,18 @@ ft_result_t ft_comm_set_widths(ft_comm_t* c, const int* widths, int nstages) {
   for (int x : w) ring = ring || x == 1;
   if (ring && c->nranks > 1) {
     c->widths_override = {1};
+    c->lonely_override = 0;
     return FT_SUCCESS;
   }
   Plan p;
-  if (!make_plan(w.data(), nstages, &p) || p.nranks != c->nranks) {
+  if (!make_plan(w.data(), nstages, &p) || p.nranks > c->nranks) {
     set_last_error("invalid widths " + to_string(w) + " for world size " + std::to_string(c->nranks));
     return FT_ERR_INVALID;
   }
+  // A tree smaller than the world leaves N - T "lonely" ranks (the reference's "+k" trees,
+  // cost_model/ChooseWidth.h:16-31): they feed their vector to the tree and gather the result from it.
   c->widths_override = w;
+  c->lonely_override = c->nranks - p.nranks;
   return FT_SUCCESS;
 }
 ft_result_t ft_comm_set_algo(ft_comm_t* c, ft_algo_t algo) {

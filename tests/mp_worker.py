@@ -56,6 +56,18 @@ def main():
             assert torch.equal(chk, y), f"ranks differ for {widths}"
     comm.set_widths(None)
 
+    # 1b. lonely ranks: a tree smaller than the world (the reference's "+k" trees)
+    if world >= 3:
+        tree = {3: [2], 4: [3], 5: [2, 2], 6: [5], 7: [2, 3], 8: [2, 3]}.get(world, [world - 1])
+        comm.set_widths(tree)
+        for count in (5, 100000):
+            x = torch.randn(count, device=dev, generator=g)
+            ref = exact_sum(x)
+            out = torch.zeros_like(x)
+            comm.allreduce(x, out=out)
+            check(out, ref, 1e-5, f"lonely tree {tree} count {count}")
+        comm.set_widths(None)
+
     # 2. one-shot, ring, (NVLS), auto
     algos = ["oneshot", "ring", "auto"] + (["nvls"] if comm.has_multicast else [])
     for algo in algos:

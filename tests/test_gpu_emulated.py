@@ -294,6 +294,29 @@ def test_tma_staged_tiles_match_register_path(comms, n, widths):
     c.set_algo("auto")
 
 
+@pytest.mark.parametrize("n,widths", [(7, [2, 3]), (5, [2, 2]), (8, [3, 2])])
+def test_lonely_ranks(n, widths):
+    """A tree smaller than the world: the remaining ranks are "lonely" (reference "+k" trees)."""
+    c = ft.Communicator.emulated(n, 0, window_bytes=4 << 20)
+    c.set_algo("stages")
+    c.set_widths(widths)
+    T = int(np.prod(widths))
+    for count in (3, 1001, 200000):
+        xs = [RNG.standard_normal(count).astype(np.float32) for _ in range(n)]
+        got, src = run(c, xs, out_of_place=True)
+        want = staged_allreduce(xs[:T], widths, block=block_size(count, T, 4))[0]
+        for x in xs[T:]:
+            want = want + x
+        for r in range(n):
+            np.testing.assert_array_equal(got[r], want, err_msg=f"count {count} rank {r}")
+            np.testing.assert_array_equal(src[r], xs[r])
+    ints = [RNG.integers(-1000, 1000, 5000, dtype=np.int32) for _ in range(n)]
+    got, _ = run(c, ints, op="max")
+    for r in range(n):
+        np.testing.assert_array_equal(got[r], np.max(np.stack(ints), 0))
+    c.close()
+
+
 def test_single_rank_fast_path():
     c = ft.Communicator.emulated(1, 0)
     x = torch.arange(1000, device="cuda", dtype=torch.float32)

@@ -269,6 +269,34 @@ def test_nvls_protocol_with_emulated_switch(mode):
         xf = [acc.copy() for _ in range(n)]
 
 
+@pytest.mark.parametrize("n,widths,lonely", [(7, [2, 3], 1), (5, [2, 2], 1), (8, [2, 3], 2), (3, [2], 1), (9, [2, 2, 2], 1)])
+def test_lonely_ranks(n, widths, lonely):
+    """World size = tree + lonely ranks (the reference's "+k" trees, stubbed out there: mpi_mod.hpp:981-1099)."""
+    w = HostWorld(n, window_bytes=1 << 16)
+    for count in (1, 5, 1000, 4099):
+        ints = make_inputs(n, count, np.int32)
+        send = [aligned_copy(x) for x in ints]
+        recv = [aligned_empty(count, np.int32) for _ in range(n)]
+        assert w.allreduce(send, recv, widths=widths, lonely=lonely, ctas=2, tile_bytes=256) == 0
+        with np.errstate(over="ignore"):
+            want = np.sum(np.stack(ints), 0, dtype=np.int32)
+        for r in range(n):
+            np.testing.assert_array_equal(recv[r], want, err_msg=f"count {count} rank {r}")
+            np.testing.assert_array_equal(send[r], ints[r])
+        xf = make_inputs(n, count, np.float32)
+        buf = [aligned_copy(x) for x in xf]
+        assert w.allreduce(buf, None, widths=widths, lonely=lonely, ctas=3, tile_bytes=128) == 0
+        # tree part in the staged order, then the lonely ranks in ascending order
+        T = n - lonely
+        tree = staged_allreduce(xf[:T], widths, block=block_size(count, T, 4))[0]
+        for x in xf[T:]:
+            tree = tree + x
+        for r in range(n):
+            np.testing.assert_array_equal(buf[r], tree, err_msg=f"fp32 count {count} rank {r}")
+    assert w.allreduce([aligned_copy(x) for x in make_inputs(n, 8, np.float32)], None, widths=widths, lonely=lonely,
+                       mode=K.MODE_REGISTERED) == -8   # lonely trees use private windows only
+
+
 def test_watchdog_fires_instead_of_hanging():
     """Fault injection: one rank never joins the collective. The others must report a timeout."""
     n = 4
