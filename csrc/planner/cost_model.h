@@ -52,20 +52,20 @@ int algo_from_name(const std::string& s);  // -1 if unknown
 struct LinkModel {
   // Defaults are the round-1 fit on 8xB200 / 2xB200 (profiles/link_model_b200.json, docs/TUNING.md).
   // latencies, microseconds
-  double alpha_launch_us = 8.0;   // launch + first instruction + exit, back-to-back calls
-  double alpha_sync_us = 2.8;     // one release->acquire flag hop between two GPUs (incl. fence.sys)
-  double alpha_peer_us = 0.45;    // extra per additional peer signalled/polled in the same hop
-  double alpha_ll_us = 4.0;       // one LL (data+flag) hop
-  double alpha_nvls_us = 0.0;     // extra fixed cost of the NVLS path on top of its three flag hops
+  double alpha_launch_us = 8.35;  // launch + first instruction + exit, back-to-back calls
+  double alpha_sync_us = 1.16;    // one release->acquire flag hop between two GPUs
+  double alpha_peer_us = 0.087;   // extra per additional peer signalled/polled in the same hop
+  double alpha_ll_us = 3.63;      // one LL (data+flag) hop
+  double alpha_nvls_us = 5.3;     // extra fixed cost of the NVLS path on top of its three flag hops
   // bandwidths, GB/s
-  double beta_p2p_GBps = 420.0;        // pull bandwidth with >= fanin_knee concurrent peers (LDG path)
-  double beta_p2p_1peer_GBps = 500.0;  // pull bandwidth from a single peer
+  double beta_p2p_GBps = 616.0;        // TMA-staged pull bandwidth with >= fanin_knee concurrent peers
+  double beta_p2p_1peer_GBps = 615.0;  // ... from a single peer
   int fanin_knee = 7;
-  double beta_nvls_GBps = 536.0;  // link rate of multimem ld_reduce/st: bytes = (1 + 1/N) * S
-  double beta_ll_GBps = 384.0;    // LL: rate at which the N-1 peer copies are pushed/polled ...
-  double beta_ll_self_GBps = 179.0;  // ... plus a per-message term independent of N
+  double beta_nvls_GBps = 539.0;  // link rate of multimem ld_reduce/st: bytes = (1 + 1/N) * S
+  double beta_ll_GBps = 167.0;    // LL: rate at which the N-1 peer copies are pushed/polled ...
+  double beta_ll_self_GBps = 2000.0;  // ... plus a per-message term independent of N (negligible in the fit)
   double gamma_hbm_GBps = 6000.0; // local HBM copy/reduce traffic rate
-  double half_bw_bytes = 262144;  // per-stage bytes at which a P2P stage reaches half its peak rate
+  double half_bw_bytes = 4.0e6;   // per-stage bytes at which a P2P stage reaches half its peak rate
   bool has_nvls = false;
   int max_oneshot_bytes = 4 << 20;  // further limited by the LL buffer of the communicator
 };
