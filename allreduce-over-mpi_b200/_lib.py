@@ -115,6 +115,8 @@ def _declare(L):
     sig("ft_comm_set_launch", i32, [vp, i32, i32, i64])
     sig("ft_comm_set_tma", i32, [vp, i32])
     sig("ft_comm_set_max_ctas", i32, [vp, i32])
+    sig("ft_comm_trace_enable", i32, [vp, i32])
+    sig("ft_comm_trace_read", i32, [vp, i32, C.POINTER(C.c_ulonglong), i32])
     sig("ft_comm_reserve", i32, [vp, C.c_size_t])
     sig("ft_symm_alloc", i32, [vp, C.c_size_t, C.POINTER(vp)])
     sig("ft_symm_free", i32, [vp, vp])

@@ -167,6 +167,22 @@ class Communicator:
     def set_launch(self, ctas=0, threads=0, tile_bytes=0):
         _check(self._L, self._L.ft_comm_set_launch(self._h, ctas, threads, tile_bytes), "ft_comm_set_launch")
 
+    def trace_enable(self, on=True):
+        """Record device timestamps at the phase boundaries of the staged kernel (SHOW_TIME parity)."""
+        _check(self._L, self._L.ft_comm_trace_enable(self._h, int(bool(on))), "ft_comm_trace_enable")
+
+    def trace(self, local_rank=0):
+        """[(label, microseconds since kernel start)] for the last traced staged call."""
+        torch.cuda.synchronize(self.device)
+        buf = (C.c_ulonglong * 32)()
+        n = self._L.ft_comm_trace_read(self._h, local_rank, buf, 32)
+        if n <= 0:
+            return []
+        m = (n - 3) // 2
+        labels = ["start", "window published"] + [f"reduce-scatter stage {k} done" for k in range(m)] + \
+                 [f"all-gather stage {m - 1 - i} done" for i in range(m)] + ["exit"]
+        return [(labels[i] if i < len(labels) else f"slot {i}", (buf[i] - buf[0]) / 1e3) for i in range(n)]
+
     def set_max_ctas(self, n):
         """Cap the SMs a collective may occupy (0 = whole GPU)."""
         _check(self._L, self._L.ft_comm_set_max_ctas(self._h, int(n)), "ft_comm_set_max_ctas")

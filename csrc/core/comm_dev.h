@@ -47,7 +47,13 @@ struct CommDev {
   unsigned* done;               // local: CTAs of the current kernel that have finished
   unsigned* err;                // local: sticky error word
   size_t ll_bytes;              // capacity of one parity half of an LL buffer
+  uint64_t* trace;              // local, optional: FT_TRACE_SLOTS phase timestamps of CTA 0 (ns), null = off
 };
+
+// Phase-boundary timestamps (parity with the reference's SHOW_TIME logging, mpi_mod.hpp:33-38 and the
+// TIME_LOG_IF sites in tree_allreduce): slot 0 = start, 1 = window published, 2+k = RS stage k done,
+// 2+m+i = i-th AG stage done (stage m-1-i), last used slot = exit. Slot FT_TRACE_SLOTS-1 holds the count.
+static const int FT_TRACE_SLOTS = 24;
 
 enum Mode {
   MODE_STAGING = 0,     // user buffers are private: copy-in to the symmetric window, parity double-buffer

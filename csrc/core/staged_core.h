@@ -59,6 +59,7 @@ struct StagedCta {
   long long woff;    // byte offset of the window inside the segment
   int* abort_flag;
   bool use_tma_;     // CUDA only: TMA-staged tiles (see kernels/tma_tiles.cuh)
+  bool scale_out_;   // wire_to_io applies the scale (one-shot only: the other paths scale when a block becomes final)
   uint32_t pipe_it;  // chunks pushed through the shared-memory ring so far (same value in every thread)
 
   FT_DEV StagedCta(BE& be_, const StagedArgs& a_, const RankCall& rc_, int cta_)
@@ -70,6 +71,15 @@ struct StagedCta {
     // bulk copies need 16-byte multiples: the ragged last vector of an odd-sized message stays on the LDG path
     use_tma_ = BE::kTma && a.use_tma && VE > 1 && (a.lay.count % VE == 0);  // host guarantees this for the TMA kernel
     pipe_it = 0;
+    scale_out_ = false;
+  }
+
+  // ---- phase timestamps (opt-in) -----------------------------------------------------------------
+  FT_DEV void trace(int slot) {
+    if (cd.trace && cta == 0 && be.tid() == 0 && slot < FT_TRACE_SLOTS - 1) {
+      cd.trace[slot] = be.now_ns();
+      cd.trace[FT_TRACE_SLOTS - 1] = (uint64_t)(slot + 1);
+    }
   }
 
   // ---- flags --------------------------------------------------------------------------------------
@@ -163,7 +173,7 @@ struct StagedCta {
     for (int i = 0; i < VE; ++i) {
       if constexpr (EL::is_float) {
         A v = EL::up(x.e[i]);
-        if (a.apply_scale) v = (A)(v * (A)a.scale);
+        if (scale_out_) v = (A)(v * (A)a.scale);
         o.e[i] = EU::down((typename EU::acc)v);
       } else {
         if constexpr (kRawIO) o.e[i] = x.e[i];
@@ -171,6 +181,18 @@ struct StagedCta {
       }
     }
     return o;
+  }
+
+  // The fused 1/N (or any) scale is applied exactly once per element, at the moment its block becomes final
+  // (last reduce-scatter stage / lonely fold / NVLS reduce / last ring reduce step), in the accumulator
+  // precision and before the rounding to the wire type. Later phases only copy.
+  FT_DEV void scale_acc(A* acc) const {
+    if constexpr (EL::is_float) {
+      if (a.apply_scale) {
+#pragma unroll
+        for (int i = 0; i < VE; ++i) acc[i] = (A)(acc[i] * (A)a.scale);
+      }
+    }
   }
 
   // Valid element count of block b inside tile t, relative to the tile start (may be <= 0).
@@ -246,6 +268,7 @@ struct StagedCta {
     char* wr = rc.win[r] + woff;
     const IO* x = (const IO*)rc.send;
     const bool own_from_user = (k == 0) && (a.mode == MODE_STAGING);
+    const bool final_stage = (k == P.nstages - 1) && a.lonely == 0;  // my blocks become final here
     const int nth = be.nthr(), tid = be.tid();
 
     for (int q0 = 0; q0 < total; q0 += nth * UNR) {
@@ -311,6 +334,7 @@ struct StagedCta {
 #pragma unroll
       for (int u = 0; u < UNR; ++u) {
         if (!nv[u]) continue;
+        if (final_stage) scale_acc(acc[u]);
         PackT o;
 #pragma unroll
         for (int i = 0; i < VE; ++i) o.e[i] = EL::down(acc[u][i]);
@@ -331,7 +355,7 @@ struct StagedCta {
     const bool last = (k == 0);
     // In registered mode recv aliases my window: my own blocks are already in place unless the
     // epilogue changes them.
-    const bool self_needed = last && !(a.mode == MODE_REGISTERED && kRawIO && !(EL::is_float && a.apply_scale));
+    const bool self_needed = last && !(a.mode == MODE_REGISTERED && kRawIO);
     const int total = nb * CV * w;
     char* wr = rc.win[r] + woff;
     IO* y = (IO*)rc.recv;
@@ -422,6 +446,20 @@ struct StagedCta {
         ok[u] = q < nvec;
         if (ok[u]) v[u] = be.template mc_ld_reduce<T, Op, VE>(rc, woff + (start + q * VE) * (long long)sizeof(T), a.plan.nranks);
       }
+      if constexpr (EL::is_float) {
+        if (a.apply_scale) {  // the switch returned the final sum: scale it once, before the broadcast
+#pragma unroll
+          for (int u = 0; u < UNR; ++u) {
+            if (!ok[u]) continue;
+            A acc[VE];
+#pragma unroll
+            for (int i = 0; i < VE; ++i) acc[i] = EL::up(v[u].e[i]);
+            scale_acc(acc);
+#pragma unroll
+            for (int i = 0; i < VE; ++i) v[u].e[i] = EL::down(acc[i]);
+          }
+        }
+      }
 #pragma unroll
       for (int u = 0; u < UNR; ++u) {
         long long q = q0 + (long long)u * nth + tid;
@@ -486,7 +524,7 @@ struct StagedCta {
       be.sync();
       signal_group(PH_RS0, 0, E + j + 1);
     }
-    const bool need_out = !(a.mode == MODE_REGISTERED && kRawIO && !(EL::is_float && a.apply_scale));
+    const bool need_out = !(a.mode == MODE_REGISTERED && kRawIO);
     for (int j = 0; j < mine; ++j) {
       wait_group(PH_RS0, 0, E + j + 1);
       if (need_out) out_tile<CU>(cta + j * G);
@@ -506,6 +544,7 @@ struct StagedCta {
   // (No counterpart in the reference, which has no latency-optimised path.)
   static constexpr int LE = 8 / (int)sizeof(T) > 0 ? 8 / (int)sizeof(T) : 1;  // elements per line
   FT_DEV void run_oneshot() {
+    scale_out_ = true;
     const int N = a.plan.nranks, G = a.ctas;
     const long long count = a.lay.count;
     const long long nlines = (count + LE - 1) / LE;
@@ -636,8 +675,12 @@ struct StagedCta {
         PackT o = in[u];
         if (reduce) {
           // the partial sum arriving from the left is accumulated first, then my contribution
+          A acc[VE];
 #pragma unroll
-          for (int i = 0; i < VE; ++i) o.e[i] = EL::down(Op::apply(EL::up(in[u].e[i]), EL::up(own[u].e[i])));
+          for (int i = 0; i < VE; ++i) acc[i] = Op::apply(EL::up(in[u].e[i]), EL::up(own[u].e[i]));
+          if (to_user) scale_acc(acc);  // last reduce step: the block is final
+#pragma unroll
+          for (int i = 0; i < VE; ++i) o.e[i] = EL::down(acc[i]);
         }
         st_win(wr, el * (long long)sizeof(T), o);
         if (to_user) st_user(y, el, wire_to_io(o), nv[u]);
@@ -761,6 +804,7 @@ struct StagedCta {
 #pragma unroll
         for (int i = 0; i < VE; ++i) acc[i] = Op::apply(acc[i], EL::up(in.e[i]));
       }
+      scale_acc(acc);
       PackT o;
 #pragma unroll
       for (int i = 0; i < VE; ++i) o.e[i] = EL::down(acc[i]);
@@ -841,6 +885,7 @@ struct StagedCta {
       return;
     }
 
+    trace(0);
     // IN: publish my window to my stage-0 group
     if (a.mode == MODE_STAGING) {
       for (int j = 0; j < mine; ++j) {
@@ -851,6 +896,7 @@ struct StagedCta {
     } else {
       signal_group(PH_IN, 0, E + mine);  // data was complete before the kernel started
     }
+    trace(1);
 
     // reduce-scatter, stage-major so that a wait is almost always for a long-finished tile
     for (int k = 0; k < m; ++k) {
@@ -869,6 +915,7 @@ struct StagedCta {
         // the same stage pulls
         signal_group(PH_RS0 + k, k + 1 < m ? k + 1 : k, E + j + 1);
       }
+      trace(2 + k);
     }
 
     // all-gather, stages unwound in reverse
@@ -882,6 +929,7 @@ struct StagedCta {
           signal_group(PH_AG0 + k, k - 1, E + j + 1);
         }
       }
+      trace(2 + m + (m - 1 - k));
     }
 
     // registered mode: nobody may leave (and let the user overwrite the buffer) while a peer still reads it
@@ -890,6 +938,7 @@ struct StagedCta {
       for (int k = 0; k < m; ++k) signal_group(PH_END, k, E + 1);
       for (int k = 0; k < m; ++k) wait_group(PH_END, k, E + 1);
     }
+    trace(2 + 2 * m);
     be.finish(cd, a.ctas);
   }
 };

@@ -69,6 +69,7 @@ void* ft_host_world_create(int nranks, size_t window_bytes, size_t ll_bytes) {
     c.done = &w->done[r];
     c.err = &w->err[r];
     c.ll_bytes = w->ll_bytes;
+    c.trace = nullptr;
   }
   return w;
 }

@@ -82,6 +82,7 @@ __device__ __forceinline__ void rs_tile_tma_impl(Cta& c, const TmaRing& R, int k
   const Plan& P = c.a.plan;
   const int w = P.width[k], gn = P.gap[k + 1], nb = P.nranks / gn, rmod = c.r % gn, npeers = w - 1;
   const bool from_user = (k == 0) && (c.a.mode == MODE_STAGING);
+  const bool final_stage = (k == P.nstages - 1) && c.a.lonely == 0;
   // my own contribution can ride the ring too when it already sits in memory in wire format
   const bool own_raw = !from_user || Cta::kRawIO;
   const int nsrc = npeers + (own_raw ? 1 : 0);
@@ -141,6 +142,7 @@ __device__ __forceinline__ void rs_tile_tma_impl(Cta& c, const TmaRing& R, int k
 #pragma unroll
             for (int i = 0; i < VE; ++i) acc[i] = Op::apply(acc[i], EL::up(in.e[i]));
           }
+          if (final_stage) c.scale_acc(acc);
           PackT out;
 #pragma unroll
           for (int i = 0; i < VE; ++i) out.e[i] = EL::down(acc[i]);
@@ -165,7 +167,7 @@ __device__ __forceinline__ void ag_tile_tma_impl(Cta& c, const TmaRing& R, int k
   const int w = P.width[k], g = P.gap[k], gn = P.gap[k + 1], base = stage_base(P, c.r, k), nb = P.nranks / gn;
   const bool last = (k == 0);
   const int my_digit = (c.r - base) / g;
-  const bool self_needed = last && !(c.a.mode == MODE_REGISTERED && Cta::kRawIO && !(EL::is_float && c.a.apply_scale));
+  const bool self_needed = last && !(c.a.mode == MODE_REGISTERED && Cta::kRawIO);
   const int CH = kTmaMaxChunk;
   char* wr = c.rc.win[c.r] + c.woff;
   IO* y = (IO*)c.rc.recv;

@@ -94,6 +94,7 @@ struct ft_comm {
   uint64_t* d_epoch = nullptr;     // [nlocal]
   unsigned* d_done = nullptr;      // [nlocal]
   unsigned* d_err = nullptr;       // [nlocal]
+  uint64_t* d_trace = nullptr;     // [nlocal][FT_TRACE_SLOTS], allocated by ft_comm_trace_enable
 
   // policy
   std::vector<int> widths_override;
@@ -397,7 +398,7 @@ ft_result_t do_allreduce(ft_comm* c, const void* const* send, void* const* recv,
   int mode = MODE_STAGING;
   int useg = -1;
   size_t uoff = 0;
-  if (in_place && !apply_scale && io_dtype == wire_dtype && vec && N > 1) {
+  if (in_place && io_dtype == wire_dtype && vec && N > 1) {
     useg = find_user_seg(c, 0, r[0], count * (size_t)ios, &uoff);
     for (int l = 1; l < L && useg >= 0; ++l) {
       size_t o2 = 0;
@@ -472,7 +473,6 @@ ft_result_t do_allreduce(ft_comm* c, const void* const* send, void* const* recv,
     set_last_error("stage widths " + to_string(widths) + " do not multiply to the world size " + std::to_string(N));
     return FT_ERR_INVALID;
   }
-  if (algo == ALGO_RING && mode == MODE_REGISTERED && (apply_scale || io_dtype != wire_dtype)) mode = MODE_STAGING;
 
   // TMA-staged tiles: vector path and whole 16-byte vectors only (blocks are padded to 16 bytes, so every
   // bulk copy is aligned).
@@ -726,6 +726,7 @@ ft_result_t ft_comm_destroy(ft_comm_t* c) {
   if (c->d_epoch) cudaFree(c->d_epoch);
   if (c->d_done) cudaFree(c->d_done);
   if (c->d_err) cudaFree(c->d_err);
+  if (c->d_trace) cudaFree(c->d_trace);
   (void)cudaGetLastError();
   if (c->group) {
     std::lock_guard<std::mutex> lk(c->group->mu);
@@ -804,6 +805,36 @@ ft_result_t ft_comm_set_launch(ft_comm_t* c, int ctas, int threads, long long ti
   c->threads_override = threads;
   c->tile_override = tile_bytes;
   return FT_SUCCESS;
+}
+
+// Phase timing (SHOW_TIME parity): device timestamps of CTA 0 at every phase boundary of the staged kernel.
+ft_result_t ft_comm_trace_enable(ft_comm_t* c, int on) {
+  FT_CHECK_RT(cudaSetDevice(c->device));
+  FT_CHECK_RT(cudaDeviceSynchronize());
+  const size_t bytes = sizeof(uint64_t) * FT_TRACE_SLOTS * (size_t)c->nlocal;
+  if (on && !c->d_trace) {
+    FT_CHECK_RT(cudaMalloc(&c->d_trace, bytes));
+    FT_CHECK_RT(cudaMemset(c->d_trace, 0, bytes));
+  }
+  std::vector<CommDev> h((size_t)c->nlocal);
+  FT_CHECK_RT(cudaMemcpy(h.data(), c->d_comm, sizeof(CommDev) * (size_t)c->nlocal, cudaMemcpyDeviceToHost));
+  for (int l = 0; l < c->nlocal; ++l) h[(size_t)l].trace = on ? c->d_trace + (size_t)l * FT_TRACE_SLOTS : nullptr;
+  FT_CHECK_RT(cudaMemcpy(c->d_comm, h.data(), sizeof(CommDev) * (size_t)c->nlocal, cudaMemcpyHostToDevice));
+  return FT_SUCCESS;
+}
+// ns[slot] for local rank `local` of the last traced call; returns the number of valid slots (0 if off).
+int ft_comm_trace_read(ft_comm_t* c, int local, unsigned long long* ns, int cap) {
+  if (!c->d_trace || local < 0 || local >= c->nlocal) return 0;
+  uint64_t h[FT_TRACE_SLOTS];
+  cudaSetDevice(c->device);
+  if (cudaMemcpy(h, c->d_trace + (size_t)local * FT_TRACE_SLOTS, sizeof h, cudaMemcpyDeviceToHost) != cudaSuccess) {
+    (void)cudaGetLastError();
+    return 0;
+  }
+  int n = (int)h[FT_TRACE_SLOTS - 1];
+  if (n > FT_TRACE_SLOTS - 1) n = FT_TRACE_SLOTS - 1;
+  for (int i = 0; i < n && i < cap; ++i) ns[i] = h[i];
+  return n;
 }
 
 ft_result_t ft_comm_set_max_ctas(ft_comm_t* c, int max_ctas) {

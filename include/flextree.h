@@ -141,6 +141,12 @@ ft_result_t ft_comm_set_link_model(ft_comm_t*, const ft_link_model_t*);
 /* Launch shape overrides: CTAs per rank, threads per CTA, tile bytes (0 = automatic). */
 ft_result_t ft_comm_set_launch(ft_comm_t*, int ctas, int threads, long long tile_bytes);
 
+/* Phase timing (the reference's SHOW_TIME switch, mpi_mod.hpp:33-38): when enabled, CTA 0 of the staged
+ * kernel records %globaltimer at every phase boundary: start, window published, each reduce-scatter
+ * stage, each all-gather stage, exit. ft_comm_trace_read returns the slots of the last call (ns). */
+ft_result_t ft_comm_trace_enable(ft_comm_t*, int on);
+int ft_comm_trace_read(ft_comm_t*, int local_rank, unsigned long long* ns, int cap);
+
 /* Upper bound on the CTAs (= SMs) a collective may occupy; 0 = no bound. Use it when the collective
  * overlaps compute (DDP backward): NVLS needs 8 CTAs anyway, the TMA P2P stages reach most of their
  * bandwidth from ~32. Same as env FT_MAX_CTAS. */

@@ -121,6 +121,10 @@ def main():
             comm.allreduce(buf)
             check(buf, ref, 1e-5, f"registered {algo} iter {it}")
             assert comm.last_call()["mode"] == "registered"
+        buf.copy_(src)
+        comm.allreduce(buf, scale=1.0 / world)  # fused average on a zero-copy buffer
+        check(buf, ref / world, 1e-5, f"registered {algo} + scale")
+        assert comm.last_call()["mode"] == "registered"
     comm.set_algo("auto")
 
     # 6. CUDA graph capture + replay

@@ -9,7 +9,7 @@ def block_size(count, n, esize, vectorized=True):
     return -(-b // vec) * vec
 
 
-def staged_allreduce(inputs, widths, op=np.add, block=None, round_fn=None):
+def staged_allreduce(inputs, widths, op=np.add, block=None, round_fn=None, final_scale=None):
     """inputs: list of N 1-D arrays (same dtype/len). Summation order inside a stage: own value first,
     then the group peers in ascending rank order. round_fn rounds stage results to the wire dtype."""
     n = len(inputs)
@@ -42,6 +42,8 @@ def staged_allreduce(inputs, widths, op=np.add, block=None, round_fn=None):
                 for pr in peers:
                     if pr != r:
                         acc = op(acc, W[pr][blk(b)])
+                if final_scale is not None and k == len(widths) - 1:
+                    acc = acc * acc.dtype.type(final_scale)  # scaled once, when the block becomes final
                 if round_fn is not None:
                     acc = round_fn(acc)
                 new[r][blk(b)] = acc

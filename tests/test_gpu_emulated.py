@@ -135,8 +135,8 @@ def test_fp32_grads_bf16_wire_fused_scale(comms):
     c.allreduce_multi(ts, scale=1.0 / n, wire_dtype=torch.bfloat16)
     torch.cuda.synchronize()
     assert c.error() == 0
-    want = staged_allreduce([round_bf16(x) for x in xs], [4], block=block_size(count, n, 2), round_fn=round_bf16)[0]
-    want = want * np.float32(1.0 / n)
+    want = staged_allreduce([round_bf16(x) for x in xs], [4], block=block_size(count, n, 2), round_fn=round_bf16,
+                            final_scale=1.0 / n)[0]
     for r in range(n):
         np.testing.assert_array_equal(ts[r].cpu().numpy(), want)
     ref = torch.stack([dev(x) for x in xs]).double().mean(0).float().cpu().numpy()
@@ -315,6 +315,24 @@ def test_lonely_ranks(n, widths):
     for r in range(n):
         np.testing.assert_array_equal(got[r], np.max(np.stack(ints), 0))
     c.close()
+
+
+def test_phase_trace(comms):
+    c = comms(8)
+    c.set_algo("stages")
+    c.set_widths([2, 4])
+    c.trace_enable(True)
+    xs = [RNG.standard_normal(1 << 18).astype(np.float32) for _ in range(8)]
+    run(c, xs)
+    tr = c.trace(3)
+    labels = [l for l, _ in tr]
+    assert labels == ["start", "window published", "reduce-scatter stage 0 done", "reduce-scatter stage 1 done",
+                      "all-gather stage 1 done", "all-gather stage 0 done", "exit"]
+    times = [t for _, t in tr]
+    assert times == sorted(times) and times[-1] > 0
+    c.trace_enable(False)
+    c.set_widths(None)
+    c.set_algo("auto")
 
 
 def test_single_rank_fast_path():

@@ -142,7 +142,7 @@ def test_fp32_io_bf16_wire_with_scale():
     assert w.allreduce(buf, None, widths=widths, ctas=2, tile_bytes=256, dtype_code=K.BFLOAT16,
                        io_dtype_code=K.FLOAT, scale=1.0 / n) == 0
     want = staged_allreduce([round_bf16(x) for x in xf], widths, block=block_size(count, n, 2),
-                            round_fn=round_bf16)[0] * np.float32(1.0 / n)
+                            round_fn=round_bf16, final_scale=1.0 / n)[0]
     for r in range(n):
         np.testing.assert_array_equal(buf[r], want)
     exact = np.mean(np.stack(xf).astype(np.float64), 0)
@@ -155,7 +155,7 @@ def test_scale_epilogue_fp32():
     w = HostWorld(n)
     buf = [aligned_copy(x) for x in xf]
     assert w.allreduce(buf, None, widths=[3, 2], scale=0.25) == 0
-    want = staged_allreduce(xf, [3, 2], block=block_size(count, n, 4))[0] * np.float32(0.25)
+    want = staged_allreduce(xf, [3, 2], block=block_size(count, n, 4), final_scale=0.25)[0]
     np.testing.assert_array_equal(buf[3], want)
 
 
@@ -173,6 +173,23 @@ def test_registered_in_place_zero_copy(widths):
         for r in range(n):
             np.testing.assert_array_equal(views[r], want)
     assert w.epoch(0) == 3 and w.epoch(n - 1) == 3
+
+
+@pytest.mark.parametrize("algo,widths", [("stages", [2, 2]), ("stages", [4]), ("nvls", None), ("ring", None)])
+def test_registered_in_place_with_fused_scale(algo, widths):
+    """The scale is applied when a block becomes final, so zero-copy (registered) buffers can use it too."""
+    n, count = 4, 3000
+    xf = make_inputs(n, count, np.float32)
+    w = HostWorld(n, window_bytes=1 << 16)
+    views = [w.registered(r, count, np.float32) for r in range(n)]
+    for r in range(n):
+        views[r][:] = xf[r]
+    assert w.allreduce(views, None, algo=algo, widths=widths, ctas=3, tile_bytes=256, mode=K.MODE_REGISTERED,
+                       scale=0.25) == 0
+    exact = np.sum(np.stack(xf).astype(np.float64), 0) * 0.25
+    for r in range(n):
+        np.testing.assert_allclose(views[r], exact, rtol=1e-5, atol=1e-6)
+        np.testing.assert_array_equal(views[r], views[0])
 
 
 def test_back_to_back_sizes_and_plans_reuse_flags():
