@@ -98,6 +98,9 @@ def _declare(L):
     sig("ft_float_to_bf16", C.c_uint16, [C.c_float])
     sig("ft_f16_to_float", C.c_float, [C.c_uint16])
     sig("ft_float_to_f16", C.c_uint16, [C.c_float])
+    sig("ft_e4m3_to_float", C.c_float, [C.c_uint])
+    sig("ft_float_to_e4m3", C.c_uint, [C.c_float])
+    sig("ft_fp8_block_scale", C.c_uint, [C.c_float])
     # CUDA runtime (absent from the host-only library)
     sig("ft_comm_options_default", None, [vp])
     sig("ft_comm_create", i32, [C.POINTER(vp), i32, i32, i32, vp, vp, vp])

@@ -1,7 +1,7 @@
 """Enum values of the C ABI (include/flextree.h) and dtype tables."""
 import numpy as np
 
-UINT8, INT8, UINT16, INT16, INT32, INT64, FLOAT, DOUBLE, BOOL, LONG_LONG, UINT32, UINT64, HALF, BFLOAT16 = range(14)
+UINT8, INT8, UINT16, INT16, INT32, INT64, FLOAT, DOUBLE, BOOL, LONG_LONG, UINT32, UINT64, HALF, BFLOAT16, FP8_BLOCK = range(15)
 SUM, BAND, MAX, MIN, BOR = range(5)
 ALGO_AUTO, ALGO_ONESHOT, ALGO_STAGES, ALGO_NVLS, ALGO_RING = range(5)
 MODE_STAGING, MODE_REGISTERED = 0, 1
@@ -11,7 +11,7 @@ ALGOS = {"auto": ALGO_AUTO, "oneshot": ALGO_ONESHOT, "stages": ALGO_STAGES, "nvl
 ALGO_NAMES = {v: k for k, v in ALGOS.items()}
 
 DTYPE_SIZE = {UINT8: 1, INT8: 1, BOOL: 1, UINT16: 2, INT16: 2, HALF: 2, BFLOAT16: 2, INT32: 4, UINT32: 4,
-              FLOAT: 4, INT64: 8, UINT64: 8, DOUBLE: 8, LONG_LONG: 8}
+              FLOAT: 4, INT64: 8, UINT64: 8, DOUBLE: 8, LONG_LONG: 8, FP8_BLOCK: 1}
 
 NUMPY_DTYPE = {
     np.dtype(np.uint8): UINT8, np.dtype(np.int8): INT8, np.dtype(np.uint16): UINT16,

@@ -227,6 +227,16 @@ class Communicator:
         s = stream if stream is not None else torch.cuda.current_stream(self.device)
         return C.c_void_p(s.cuda_stream)
 
+    @staticmethod
+    def _wire_code(dt, wire_dtype):
+        if wire_dtype is None:
+            return dt
+        if isinstance(wire_dtype, str):
+            if wire_dtype in ("fp8", "fp8-block16", "fp8_block"):
+                return K.FP8_BLOCK  # opt-in block-scaled e4m3 wire
+            wire_dtype = {"bf16": torch.bfloat16, "fp16": torch.float16, "fp32": torch.float32}[wire_dtype]
+        return K.torch_dtype_code(wire_dtype)
+
     def allreduce(self, tensor, op="sum", out=None, scale=1.0, wire_dtype=None, stream=None):
         """In place (``out=None``) or out of place allreduce of a contiguous CUDA tensor.
 
@@ -240,7 +250,7 @@ class Communicator:
         if out.dtype != tensor.dtype or out.numel() != tensor.numel():
             raise ValueError("out must match the input dtype/size")
         dt = K.torch_dtype_code(tensor.dtype)
-        wt = dt if wire_dtype is None else K.torch_dtype_code(wire_dtype)
+        wt = self._wire_code(dt, wire_dtype)
         opc = K.OPS[op] if isinstance(op, str) else int(op)
         with torch.cuda.device(self.device):
             rc = self._L.ft_allreduce_ex(C.c_void_p(tensor.data_ptr()), C.c_void_p(out.data_ptr()), tensor.numel(),
@@ -255,7 +265,7 @@ class Communicator:
             raise ValueError("need one tensor per emulated rank")
         outs = tensors if outs is None else outs
         dt = K.torch_dtype_code(tensors[0].dtype)
-        wt = dt if wire_dtype is None else K.torch_dtype_code(wire_dtype)
+        wt = self._wire_code(dt, wire_dtype)
         opc = K.OPS[op] if isinstance(op, str) else int(op)
         s = (C.c_void_p * n)(*[t.data_ptr() for t in tensors])
         r = (C.c_void_p * n)(*[t.data_ptr() for t in outs])

@@ -28,7 +28,12 @@ def ddp_comm_hook(state, bucket):
     buf = bucket.buffer()
     comm = state.comm
     scale = 1.0 / comm.size if state.average else 1.0
-    wire = state.wire_dtype if (state.wire_dtype is not None and buf.dtype == torch.float32) else None
+    wire = None
+    if state.wire_dtype is not None:
+        if isinstance(state.wire_dtype, str) and state.wire_dtype.startswith("fp8"):
+            wire = state.wire_dtype if buf.dtype in (torch.float32, torch.bfloat16) else None
+        elif buf.dtype == torch.float32:
+            wire = state.wire_dtype
     state.calls += 1
     state.bytes += buf.numel() * buf.element_size()
     fut = torch.futures.Future(devices=[comm.device])

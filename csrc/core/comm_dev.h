@@ -82,6 +82,7 @@ struct StagedArgs {
   unsigned long long timeout_ns;  // 0 = spin forever
   int use_tma;  // CUDA back end: stage peer chunks through shared memory with cp.async.bulk (TMA)
   int lonely;   // ranks plan.nranks .. plan.nranks+lonely-1 are outside the tree (N = tree + lonely)
+  long long scale_plane_off;  // fp8 block-scaled wire: byte offset of the scale plane inside the window
   RankCall rc[FT_MAX_LOCAL];
 };
 

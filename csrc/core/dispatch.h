@@ -20,7 +20,7 @@ enum TypeGroup { TG_F32 = 1, TG_F16 = 2, TG_64 = 4, TG_I32 = 8, TG_SMALL = 16, T
 inline int dtype_group(int dt) {
   switch (dt) {
     case DT_FLOAT: return TG_F32;
-    case DT_HALF: case DT_BFLOAT16: return TG_F16;
+    case DT_HALF: case DT_BFLOAT16: case DT_FP8_BLOCK: return TG_F16;
     case DT_DOUBLE: case DT_INT64: case DT_UINT64: case DT_LONG_LONG: return TG_64;
     case DT_INT32: case DT_UINT32: return TG_I32;
     default: return TG_SMALL;
@@ -63,6 +63,11 @@ struct Dispatcher {
       if constexpr ((GROUPS & TG_F16) != 0) {
         if (io_dtype == DT_FLOAT && dtype == DT_BFLOAT16) return float_ops<bf16_t, float>(op, v, args...);
         if (io_dtype == DT_FLOAT && dtype == DT_HALF) return float_ops<f16_t, float>(op, v, args...);
+        // block-scaled fp8 wire: SUM only, vector path only (a pack is 16 values + a scale byte)
+        if (dtype == DT_FP8_BLOCK && op == OP_SUM && v) {
+          if (io_dtype == DT_FLOAT) { F<fp8_t, float, OpSum, 16>::run(args...); return true; }
+          if (io_dtype == DT_BFLOAT16) { F<fp8_t, bf16_t, OpSum, 16>::run(args...); return true; }
+        }
       }
       return false;
     }

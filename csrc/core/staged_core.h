@@ -778,6 +778,135 @@ struct StagedCta {
     }
   }
 
+  // ---- block-scaled fp8 wire (T == fp8_t, opt-in) -----------------------------------------------------------
+  // Same stages as above, but a pack is 16 e4m3 values that share one power-of-two scale stored in the
+  // window's scale plane (a.scale_plane_off + element/16). Every stage dequantises its inputs, reduces in
+  // fp32 and re-quantises its output block with a fresh scale; the own contribution of stage 0 is taken
+  // from the user buffer unquantised. Register-staged loads only (no TMA / NVLS / LL variants).
+  static constexpr bool kBlockScaled = SameType<T, fp8_t>::value;
+  FT_DEV long long scale_off(long long el) const { return a.scale_plane_off + (el >> 4); }
+  FT_DEV static void q_dequant(const PackT& p, uint8_t s, float* acc, bool first) {
+    const float sc = fp8_scale_value(s);
+#pragma unroll
+    for (int i = 0; i < VE; ++i) {
+      const float v = e4m3_to_float(reinterpret_cast<const uint8_t*>(&p)[i]) * sc;
+      acc[i] = first ? v : Op::apply(acc[i], v);
+    }
+  }
+  FT_DEV static PackT q_quant(const float* acc, uint8_t* s_out) {
+    float amax = 0.f;
+#pragma unroll
+    for (int i = 0; i < VE; ++i) {
+      const float m = acc[i] < 0 ? -acc[i] : acc[i];
+      amax = m > amax ? m : amax;
+    }
+    const uint8_t s = fp8_block_scale(amax);
+    const float inv = fp8_scale_inverse(s);
+    PackT o;
+#pragma unroll
+    for (int i = 0; i < VE; ++i) reinterpret_cast<uint8_t*>(&o)[i] = float_to_e4m3(acc[i] * inv);
+    *s_out = s;
+    return o;
+  }
+  FT_DEV static void q_load_user(const IO* x, long long el, int nvalid, float* acc) {
+    PackIO u = ld_user(x, el, nvalid);
+#pragma unroll
+    for (int i = 0; i < VE; ++i) acc[i] = i < nvalid ? (float)EU::up(u.e[i]) : 0.f;
+  }
+  FT_DEV void q_store_user(IO* y, long long el, int nvalid, const float* acc) const {
+    PackIO o;
+#pragma unroll
+    for (int i = 0; i < VE; ++i) o.e[i] = EU::down((typename EU::acc)acc[i]);
+    st_user(y, el, o, nvalid);
+  }
+  FT_DEV void q_copy_in_tile(int t) {
+    const int N = a.plan.nranks, g1 = a.plan.gap[1];
+    const int CV = (int)((a.lay.tile + VE - 1) / VE), total = N * CV;
+    char* wr = rc.win[r] + woff;
+    for (int q = be.tid(); q < total; q += be.nthr()) {
+      const int b = q / CV, vi = q - b * CV;
+      if ((b % g1) == (r % g1)) continue;
+      long long start;
+      const int n = tile_valid32(b, t, &start) - vi * VE;
+      if (n <= 0) continue;
+      const long long el = start + vi * VE;
+      float acc[VE];
+      q_load_user((const IO*)rc.send, el, n < VE ? n : VE, acc);
+      uint8_t sc;
+      PackT p = q_quant(acc, &sc);
+      st_win(wr, el, p);
+      BE::template st<1>(wr + scale_off(el), &sc);
+    }
+  }
+  FT_DEV void q_rs_tile(int k, int t) {
+    const Plan& P = a.plan;
+    const int w = P.width[k], gn = P.gap[k + 1], nb = P.nranks / gn, rmod = r % gn, npeers = w - 1;
+    const int CV = (int)((a.lay.tile + VE - 1) / VE), total = nb * CV;
+    const bool own_from_user = (k == 0) && (a.mode == MODE_STAGING);
+    const bool final_stage = (k == P.nstages - 1) && a.lonely == 0;
+    char* wr = rc.win[r] + woff;
+    for (int q = be.tid(); q < total; q += be.nthr()) {
+      const int bi = q / CV, vi = q - bi * CV;
+      long long start;
+      const int n = tile_valid32(rmod + bi * gn, t, &start) - vi * VE;
+      if (n <= 0) continue;
+      const long long el = start + vi * VE;
+      float acc[VE];
+      if (own_from_user) {
+        q_load_user((const IO*)rc.send, el, n < VE ? n : VE, acc);
+      } else {
+        uint8_t s0;
+        PackT p0 = ld_win(wr, el, false);
+        BE::template ld<1>(&s0, wr + scale_off(el), false);
+        q_dequant(p0, s0, acc, true);
+      }
+      for (int j = 0; j < npeers; ++j) {
+        const char* pw = rs_peer_ptr(k, j);
+        uint8_t sj;
+        PackT pj = ld_win(pw, el, true);
+        BE::template ld<1>(&sj, pw + scale_off(el), true);
+        q_dequant(pj, sj, acc, false);
+      }
+      if (final_stage && a.apply_scale) {
+#pragma unroll
+        for (int i = 0; i < VE; ++i) acc[i] *= (float)a.scale;
+      }
+      uint8_t sc;
+      PackT o = q_quant(acc, &sc);
+      st_win(wr, el, o);
+      BE::template st<1>(wr + scale_off(el), &sc);
+    }
+  }
+  FT_DEV void q_ag_tile(int k, int t) {
+    const Plan& P = a.plan;
+    const int w = P.width[k], g = P.gap[k], gn = P.gap[k + 1], base = stage_base(P, r, k), nb = P.nranks / gn;
+    const int CV = (int)((a.lay.tile + VE - 1) / VE), total = nb * CV * w;
+    const bool last = (k == 0);
+    char* wr = rc.win[r] + woff;
+    for (int q = be.tid(); q < total; q += be.nthr()) {
+      const int rest = q / CV, vi = q - rest * CV;
+      const int bi = rest / w, s_ = rest - bi * w;
+      const int p = base + s_ * g;
+      if (p == r && !last) continue;
+      long long start;
+      const int n = tile_valid32((p % gn) + bi * gn, t, &start) - vi * VE;
+      if (n <= 0) continue;
+      const long long el = start + vi * VE;
+      const char* pw = rc.win[p] + woff;
+      uint8_t sc;
+      PackT v = ld_win(pw, el, p != r);
+      BE::template ld<1>(&sc, pw + scale_off(el), p != r);
+      if (last) {
+        float acc[VE];
+        q_dequant(v, sc, acc, true);
+        q_store_user((IO*)rc.recv, el, n < VE ? n : VE, acc);
+      } else {
+        st_win(wr, el, v);
+        BE::template st<1>(wr + scale_off(el), &sc);
+      }
+    }
+  }
+
   // ---- lonely ranks (world size = tree ranks + L, the reference's "+1" trees) ------------------------------
   // Capability parity: the lonely ops of Send_Ops/Recv_Ops (mpi_mod.hpp:172-178, :208-211) and the lonely
   // branches of tree_allreduce (:981-987, :1019-1026, :1041-1099), which the reference ships as stubs
@@ -889,7 +1018,8 @@ struct StagedCta {
     // IN: publish my window to my stage-0 group
     if (a.mode == MODE_STAGING) {
       for (int j = 0; j < mine; ++j) {
-        copy_in_tile<CU>(cta + j * G);
+        if constexpr (kBlockScaled) q_copy_in_tile(cta + j * G);
+        else copy_in_tile<CU>(cta + j * G);
         be.sync();
         signal_group(PH_IN, 0, E + j + 1);
       }
@@ -902,7 +1032,8 @@ struct StagedCta {
     for (int k = 0; k < m; ++k) {
       for (int j = 0; j < mine; ++j) {
         wait_group(k == 0 ? (int)PH_IN : PH_RS0 + k - 1, k, E + j + 1);
-        if constexpr (TMA) be.template rs_tile_tma<T, IO, Op, VE>(*this, k, cta + j * G);
+        if constexpr (kBlockScaled) q_rs_tile(k, cta + j * G);
+        else if constexpr (TMA) be.template rs_tile_tma<T, IO, Op, VE>(*this, k, cta + j * G);
         else rs_dispatch(k, cta + j * G);
         be.sync();
         if (a.lonely > 0 && k == m - 1) {  // my block is reduced over the tree: add the lonely ranks' copies
@@ -922,7 +1053,8 @@ struct StagedCta {
     for (int k = m - 1; k >= 0; --k) {
       for (int j = 0; j < mine; ++j) {
         wait_group(k == m - 1 ? PH_RS0 + k : PH_AG0 + k + 1, k, E + j + 1);
-        if constexpr (TMA) be.template ag_tile_tma<T, IO, Op, VE>(*this, k, cta + j * G);
+        if constexpr (kBlockScaled) q_ag_tile(k, cta + j * G);
+        else if constexpr (TMA) be.template ag_tile_tma<T, IO, Op, VE>(*this, k, cta + j * G);
         else ag_tile<CU>(k, cta + j * G);
         if (k > 0) {
           be.sync();

@@ -22,13 +22,15 @@ namespace ft {
 enum DType {
   DT_UINT8 = 0, DT_INT8 = 1, DT_UINT16 = 2, DT_INT16 = 3, DT_INT32 = 4, DT_INT64 = 5,
   DT_FLOAT = 6, DT_DOUBLE = 7, DT_BOOL = 8, DT_LONG_LONG = 9,
-  DT_UINT32 = 10, DT_UINT64 = 11, DT_HALF = 12, DT_BFLOAT16 = 13, DT_COUNT = 14
+  DT_UINT32 = 10, DT_UINT64 = 11, DT_HALF = 12, DT_BFLOAT16 = 13,
+  DT_FP8_BLOCK = 14,  // wire-only: e4m3 values + one power-of-two scale byte per 16 elements (opt-in)
+  DT_COUNT = 15
 };
 enum RedOp { OP_SUM = 0, OP_BAND = 1, OP_MAX = 2, OP_MIN = 3, OP_BOR = 4, OP_COUNT = 5 };
 
 inline int dtype_size(int dt) {
   switch (dt) {
-    case DT_UINT8: case DT_INT8: case DT_BOOL: return 1;
+    case DT_UINT8: case DT_INT8: case DT_BOOL: case DT_FP8_BLOCK: return 1;
     case DT_UINT16: case DT_INT16: case DT_HALF: case DT_BFLOAT16: return 2;
     case DT_INT32: case DT_UINT32: case DT_FLOAT: return 4;
     case DT_INT64: case DT_UINT64: case DT_DOUBLE: case DT_LONG_LONG: return 8;
@@ -36,11 +38,11 @@ inline int dtype_size(int dt) {
   return 0;
 }
 inline bool dtype_is_float(int dt) {
-  return dt == DT_FLOAT || dt == DT_DOUBLE || dt == DT_HALF || dt == DT_BFLOAT16;
+  return dt == DT_FLOAT || dt == DT_DOUBLE || dt == DT_HALF || dt == DT_BFLOAT16 || dt == DT_FP8_BLOCK;
 }
 inline const char* dtype_name(int dt) {
   static const char* n[] = {"uint8", "int8", "uint16", "int16", "int32", "int64", "float32",
-                            "float64", "bool", "longlong", "uint32", "uint64", "float16", "bfloat16"};
+                            "float64", "bool", "longlong", "uint32", "uint64", "float16", "bfloat16", "fp8-block16"};
   return (dt >= 0 && dt < DT_COUNT) ? n[dt] : "?";
 }
 inline const char* op_name(int op) {
@@ -126,6 +128,49 @@ FT_HD f16_t f16_from_float(float f) {
   return r;
 }
 
+// ---- block-scaled fp8 wire format (opt-in) ------------------------------------------------------------------
+// A 16-byte pack holds 16 e4m3 values; their common scale 2^(s-127) travels as one byte s in a separate
+// "scale plane" of the window (1/16 of the payload). Every reduce-scatter stage dequantises, sums in
+// fp32 and re-quantises with a fresh scale, so the error grows with the number of stages (measured
+// bounds in the tests). Conversions are plain integer code so that CPU model and GPU agree bit for bit.
+struct fp8_t { uint8_t v; };
+
+FT_HD float e4m3_to_float(uint8_t b) {
+  const uint32_t sign = (uint32_t)(b & 0x80) << 24, e = (b >> 3) & 0xf, m = b & 7;
+  if (e == 0xf && m == 7) return bits_to_float(sign | 0x7fc00000u);  // NaN (e4m3 has no inf)
+  if (e == 0) {                                                          // subnormal: m * 2^-9
+    float f = (float)m * 0.001953125f;
+    return sign ? -f : f;
+  }
+  return bits_to_float(sign | ((e + 120) << 23) | (m << 20));
+}
+// round to nearest even, saturate to +-448, NaN -> 0x7f
+FT_HD uint8_t float_to_e4m3(float x) {
+  const uint32_t u = float_to_bits(x), sign = (u >> 24) & 0x80, a = u & 0x7fffffffu;
+  if (a > 0x7f800000u) return (uint8_t)(sign | 0x7f);
+  if (a >= 0x43e00000u) return (uint8_t)(sign | 0x7e);  // >= 448 (also inf): saturate
+  if (a < 0x3a800000u) return (uint8_t)sign;             // < 2^-10: below half of the smallest subnormal (2^-9)
+  int e = (int)(a >> 23) - 127;                          // unbiased exponent
+  uint32_t m = (a & 0x7fffffu) | 0x800000u;              // 24-bit significand
+  int shift = e < -6 ? (20 + (-6 - e)) : 20;             // bits dropped (subnormal results drop more)
+  uint32_t q = m >> shift, rem = m & ((1u << shift) - 1), half = 1u << (shift - 1);
+  if (rem > half || (rem == half && (q & 1u))) ++q;
+  uint32_t out = e < -6 ? q : (((uint32_t)(e + 7) << 3) + (q - 8u));  // q carries the implicit bit for normals
+  if (out > 0x7e) out = 0x7e;
+  return (uint8_t)(sign | out);
+}
+// scale byte for a block whose largest magnitude is amax: smallest power of two with amax / 2^e <= 448
+FT_HD uint8_t fp8_block_scale(float amax) {
+  const uint32_t a = float_to_bits(amax) & 0x7fffffffu;
+  if (a == 0 || a >= 0x7f800000u) return a == 0 ? 0 : 254;
+  int ex = (int)(a >> 23) - 126;                  // amax = m * 2^ex, m in [0.5, 1)
+  int e = ((a & 0x7fffffu) <= 0x600000u) ? ex - 9 : ex - 8;  // 448 = 0.875 * 2^9
+  int s = e + 127;
+  return (uint8_t)(s < 0 ? 0 : (s > 254 ? 254 : s));
+}
+FT_HD float fp8_scale_value(uint8_t s) { return bits_to_float(s == 0 ? 0x00400000u : ((uint32_t)s << 23)); }      // 2^(s-127)
+FT_HD float fp8_scale_inverse(uint8_t s) { return bits_to_float(s >= 254 ? 0x00400000u : ((uint32_t)(254 - s) << 23)); }  // 2^(127-s)
+
 // ---- accumulator traits ---------------------------------------------------------------------------
 template <typename T> struct Elem {  // default: integers and fp32/fp64 accumulate in themselves
   using acc = T;
@@ -155,6 +200,12 @@ template <> struct Elem<f16_t> {
   using acc = float;
   static FT_HD acc up(f16_t x) { return to_float(x); }
   static FT_HD f16_t down(acc a) { return f16_from_float(a); }
+  static constexpr bool is_float = true;
+};
+template <> struct Elem<fp8_t> {  // per-element view WITHOUT the block scale: only the quantised tile functions use it
+  using acc = float;
+  static FT_HD acc up(fp8_t x) { return e4m3_to_float(x.v); }
+  static FT_HD fp8_t down(acc a) { fp8_t r; r.v = float_to_e4m3(a); return r; }
   static constexpr bool is_float = true;
 };
 template <> struct Elem<bool8_t> {

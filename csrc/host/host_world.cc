@@ -111,13 +111,15 @@ long long ft_host_allreduce(void* h, const void* const* send, void* const* recv,
   if (lonely < 0 || a.plan.nranks + lonely != w->n) return -2;
   if (lonely > 0 && (algo != ALGO_STAGED || mode != MODE_STAGING)) return -8;
   a.lonely = lonely;
+  if (dtype == DT_FP8_BLOCK && (algo != ALGO_STAGED || lonely > 0 || mode != MODE_STAGING)) return -9;
   const int es = dtype_size(dtype), ios = dtype_size(io_dtype);
   if (!es || !ios) return -3;
   bool vec = true;
   for (int r = 0; r < w->n; ++r)
     vec = vec && ((uintptr_t)send[r] % 16 == 0) && ((uintptr_t)recv[r] % 16 == 0);
   a.lay = make_layout(count, a.plan.nranks, es, tile_bytes, vec);
-  if ((size_t)(a.lay.block * a.plan.nranks * es) > w->win_bytes) return -4;
+  a.scale_plane_off = ((long long)a.lay.block * a.plan.nranks * es + 255) & ~255LL;
+  if ((size_t)(a.scale_plane_off + (a.lay.block * a.plan.nranks) / 16 + 16) > w->win_bytes) return -4;
   if (algo == ALGO_ONESHOT) {
     size_t region = (w->ll_bytes / w->n) & ~(size_t)15;
     size_t lines = (size_t)((count * es + 7) / 8);
@@ -160,5 +162,8 @@ float ft_bf16_to_float(uint16_t v) { bf16_t b{v}; return to_float(b); }
 uint16_t ft_float_to_bf16(float f) { return bf16_from_float(f).v; }
 float ft_f16_to_float(uint16_t v) { f16_t b{v}; return to_float(b); }
 uint16_t ft_float_to_f16(float f) { return f16_from_float(f).v; }
+float ft_e4m3_to_float(unsigned code) { return e4m3_to_float((uint8_t)code); }
+unsigned ft_float_to_e4m3(float f) { return float_to_e4m3(f); }
+unsigned ft_fp8_block_scale(float amax) { return fp8_block_scale(amax); }
 
 }  // extern "C"

@@ -35,9 +35,10 @@ struct CudaBE {
   // ---- payload ------------------------------------------------------------------------------------
   template <int B>
   static __device__ __forceinline__ void ld(void* dst, const void* src, bool remote) {
-    if constexpr (B == 32) {
-      ld<16>(dst, src, remote);
-      ld<16>((char*)dst + 16, (const char*)src + 16, remote);
+    if constexpr (B > 16) {
+      static_assert(B % 16 == 0, "unsupported access width");
+#pragma unroll
+      for (int i = 0; i < B / 16; ++i) ld<16>((char*)dst + 16 * i, (const char*)src + 16 * i, remote);
     } else if constexpr (B == 16) {
       uint4 v;
       if (remote)
@@ -74,9 +75,10 @@ struct CudaBE {
   }
   template <int B>
   static __device__ __forceinline__ void st(void* dst, const void* src) {
-    if constexpr (B == 32) {
-      st<16>(dst, src);
-      st<16>((char*)dst + 16, (const char*)src + 16);
+    if constexpr (B > 16) {
+      static_assert(B % 16 == 0, "unsupported access width");
+#pragma unroll
+      for (int i = 0; i < B / 16; ++i) st<16>((char*)dst + 16 * i, (const char*)src + 16 * i);
     } else if constexpr (B == 16) {
       *reinterpret_cast<uint4*>(dst) = *reinterpret_cast<const uint4*>(src);
     } else if constexpr (B == 8) {

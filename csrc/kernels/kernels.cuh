@@ -63,19 +63,24 @@ struct CudaLaunch {
   }
   static void run(LaunchCtx* c) {
     c->supported = true;
-    switch (c->algo) {
-      case ALGO_STAGED: c->err = go<ALGO_STAGED>(c); break;
-      case ALGO_STAGED_TMA:
-        if constexpr (VE > 1) c->err = go<ALGO_STAGED_TMA>(c);
-        else c->supported = false;
-        break;
-      case ALGO_ONESHOT: c->err = go<ALGO_ONESHOT>(c); break;
-      case ALGO_RING: c->err = go<ALGO_RING>(c); break;
-      case ALGO_NVLS:
-        if constexpr (NvlsOk<T, Op>::value && VE > 1) c->err = go<ALGO_NVLS>(c);
-        else c->supported = false;
-        break;
-      default: c->supported = false;
+    if constexpr (SameType<T, fp8_t>::value) {  // block-scaled wire: register-staged P2P stages only
+      if (c->algo == ALGO_STAGED) c->err = go<ALGO_STAGED>(c);
+      else c->supported = false;
+    } else {
+      switch (c->algo) {
+        case ALGO_STAGED: c->err = go<ALGO_STAGED>(c); break;
+        case ALGO_STAGED_TMA:
+          if constexpr (VE > 1) c->err = go<ALGO_STAGED_TMA>(c);
+          else c->supported = false;
+          break;
+        case ALGO_ONESHOT: c->err = go<ALGO_ONESHOT>(c); break;
+        case ALGO_RING: c->err = go<ALGO_RING>(c); break;
+        case ALGO_NVLS:
+          if constexpr (NvlsOk<T, Op>::value && VE > 1) c->err = go<ALGO_NVLS>(c);
+          else c->supported = false;
+          break;
+        default: c->supported = false;
+      }
     }
   }
 };

@@ -361,8 +361,19 @@ ft_result_t do_allreduce(ft_comm* c, const void* const* send, void* const* recv,
     set_last_error(std::string("unsupported op/dtype: ") + op_name(op) + " on " + dtype_name(wire_dtype));
     return FT_ERR_UNSUPPORTED;
   }
-  if (io_dtype != wire_dtype && !(io_dtype == DT_FLOAT && (wire_dtype == DT_BFLOAT16 || wire_dtype == DT_HALF))) {
-    set_last_error("only fp32 user buffers with a bf16/fp16 wire are supported as a mixed format");
+  if (wire_dtype == DT_FP8_BLOCK && c->nranks == 1 && io_dtype != DT_FP8_BLOCK) wire_dtype = io_dtype;  // nothing to compress
+  const bool fp8_wire = wire_dtype == DT_FP8_BLOCK;
+  if (fp8_wire && !((io_dtype == DT_FLOAT || io_dtype == DT_BFLOAT16) && op == OP_SUM)) {
+    set_last_error("the block-scaled fp8 wire carries fp32 or bf16 user buffers, SUM only");
+    return FT_ERR_UNSUPPORTED;
+  }
+  if (io_dtype == DT_FP8_BLOCK) {
+    set_last_error("fp8-block16 is a wire format, not a buffer dtype");
+    return FT_ERR_INVALID;
+  }
+  if (io_dtype != wire_dtype && !fp8_wire &&
+      !(io_dtype == DT_FLOAT && (wire_dtype == DT_BFLOAT16 || wire_dtype == DT_HALF))) {
+    set_last_error("mixed formats: fp32 buffers with a bf16/fp16 wire, or fp32/bf16 buffers with the fp8 block-scaled wire");
     return FT_ERR_UNSUPPORTED;
   }
   if (count == 0) return FT_SUCCESS;
@@ -469,6 +480,14 @@ ft_result_t do_allreduce(ft_comm* c, const void* const* send, void* const* recv,
     algo = ALGO_STAGED;
     mode = MODE_STAGING;
   }
+  if (wire_dtype == DT_FP8_BLOCK) {  // block-scaled wire: register-staged P2P stages, private windows, vector path
+    if (!vec || lonely > 0) {
+      set_last_error("the fp8 block-scaled wire needs 16-byte aligned buffers and a full tree");
+      return FT_ERR_UNSUPPORTED;
+    }
+    if (algo != ALGO_STAGED) { algo = ALGO_STAGED; widths = {N}; }
+    mode = MODE_STAGING;
+  }
   if (!make_plan(widths.data(), (int)widths.size(), &a.plan) || a.plan.nranks + lonely != N) {
     set_last_error("stage widths " + to_string(widths) + " do not multiply to the world size " + std::to_string(N));
     return FT_ERR_INVALID;
@@ -476,7 +495,7 @@ ft_result_t do_allreduce(ft_comm* c, const void* const* send, void* const* recv,
 
   // TMA-staged tiles: vector path and whole 16-byte vectors only (blocks are padded to 16 bytes, so every
   // bulk copy is aligned).
-  const bool tma = algo == ALGO_STAGED && lonely == 0 && vec && (count % (size_t)(16 / es) == 0) &&
+  const bool tma = algo == ALGO_STAGED && lonely == 0 && vec && wire_dtype != DT_FP8_BLOCK && (count % (size_t)(16 / es) == 0) &&
                    (c->threads_override == 0 || c->threads_override >= 64) &&
                    (c->tma_override >= 0 ? c->tma_override : env_int("FT_TMA", 1)) != 0;
   const int T = N - lonely;  // ranks in the tree = number of blocks
@@ -505,6 +524,10 @@ ft_result_t do_allreduce(ft_comm* c, const void* const* send, void* const* recv,
     }
   } else if (mode == MODE_STAGING) {
     size_t need = (size_t)a.lay.block * (size_t)T * (size_t)es;
+    if (wire_dtype == DT_FP8_BLOCK) {
+      a.scale_plane_off = ((long long)need + 255) & ~255LL;
+      need = (size_t)a.scale_plane_off + need / 16 + 16;
+    }
     cudaStreamCaptureStatus cap = cudaStreamCaptureStatusNone;
     cudaStreamIsCapturing(stream, &cap);
     if (need > c->window_bytes || c->win.empty()) {

@@ -37,7 +37,10 @@ typedef enum {
 typedef enum {
   FT_UINT8 = 0, FT_INT8 = 1, FT_UINT16 = 2, FT_INT16 = 3, FT_INT32 = 4, FT_INT64 = 5,
   FT_FLOAT = 6, FT_DOUBLE = 7, FT_BOOL = 8, FT_LONG_LONG = 9,
-  FT_UINT32 = 10, FT_UINT64 = 11, FT_HALF = 12, FT_BFLOAT16 = 13
+  FT_UINT32 = 10, FT_UINT64 = 11, FT_HALF = 12, FT_BFLOAT16 = 13,
+  /* wire_dtype of ft_allreduce_ex only (opt-in): e4m3 values + one power-of-two scale byte per 16 elements,
+   * re-quantised at every reduce-scatter stage; carries fp32 or bf16 buffers, SUM, P2P stages. */
+  FT_FP8_BLOCK16 = 14
 } ft_dtype_t;
 
 typedef enum { FT_SUM = 0, FT_BAND = 1, FT_MAX = 2, FT_MIN = 3, FT_BOR = 4 } ft_op_t;

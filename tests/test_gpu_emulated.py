@@ -317,6 +317,44 @@ def test_lonely_ranks(n, widths):
     c.close()
 
 
+def test_fp8_block_scaled_wire_matches_cpu_model(comms):
+    """Opt-in fp8 wire on the GPU: same bytes as the CPU model of the same templates, error within bounds."""
+    n, count, widths = 8, 100000, [2, 4]
+    c = comms(n)
+    c.set_algo("stages")
+    c.set_widths(widths)
+    xs = [(RNG.standard_normal(count) * 3).astype(np.float32) for _ in range(n)]
+    ts = [dev(x) for x in xs]
+    c.allreduce_multi(ts, scale=1.0 / n, wire_dtype="fp8")
+    torch.cuda.synchronize()
+    assert c.error() == 0
+    w = ft.HostWorld(n, window_bytes=1 << 20)
+    bufs = []
+    for x in xs:
+        raw = np.empty(count * 4 + 64, dtype=np.uint8)
+        off = (-raw.ctypes.data) % 16
+        v = raw[off:off + count * 4].view(np.float32)
+        v[:] = x
+        bufs.append(v)
+    info = c.last_call()
+    assert w.allreduce(bufs, None, widths=widths, ctas=info["ctas"], tile_bytes=info["tile_bytes"],
+                       dtype_code=ft.FP8_BLOCK, io_dtype_code=ft.FLOAT, scale=1.0 / n) == 0
+    for r in range(n):
+        np.testing.assert_array_equal(ts[r].cpu().numpy(), bufs[r])
+    exact = np.mean(np.stack(xs).astype(np.float64), 0)
+    rel = np.sqrt(np.mean((ts[0].cpu().numpy() - exact) ** 2)) / np.sqrt(np.mean(exact ** 2))
+    assert rel < 0.15, rel
+    # bf16 buffers too
+    tb = [dev(x).to(torch.bfloat16) for x in xs]
+    c.allreduce_multi(tb, scale=1.0 / n, wire_dtype="fp8")
+    torch.cuda.synchronize()
+    assert c.error() == 0
+    rel = np.sqrt(np.mean((tb[0].float().cpu().numpy() - exact) ** 2)) / np.sqrt(np.mean(exact ** 2))
+    assert rel < 0.15, rel
+    c.set_widths(None)
+    c.set_algo("auto")
+
+
 def test_phase_trace(comms):
     c = comms(8)
     c.set_algo("stages")

@@ -149,6 +149,57 @@ def test_fp32_io_bf16_wire_with_scale():
     assert np.max(np.abs(buf[0] - exact)) < 0.03
 
 
+@pytest.mark.parametrize("n,widths", [(2, [2]), (8, [8]), (8, [2, 4]), (8, [2, 2, 2])])
+def test_fp8_block_scaled_wire(n, widths):
+    """Opt-in fp8 wire: e4m3 values + a power-of-two scale per 16 elements, re-quantised at every stage.
+    fp32 user buffers in and out, fused 1/N. The error must stay within the e4m3 resolution (2^-4 relative
+    to the largest magnitude of a 16-block) times a small factor per stage."""
+    count = 4096 + 32
+    xf = [RNG.standard_normal(count).astype(np.float32) * np.float32(10.0 ** RNG.integers(-3, 3)) for _ in range(n)]
+    w = HostWorld(n, window_bytes=1 << 16)
+    buf = [aligned_copy(x) for x in xf]
+    assert w.allreduce(buf, None, widths=widths, ctas=2, tile_bytes=256, dtype_code=K.FP8_BLOCK,
+                       io_dtype_code=K.FLOAT, scale=1.0 / n) == 0
+    exact = np.mean(np.stack(xf).astype(np.float64), 0)
+    for r in range(1, n):
+        np.testing.assert_array_equal(buf[r], buf[0])  # every rank decodes the same bytes
+    blocks = exact[:count // 16 * 16].reshape(-1, 16)
+    # scale of the comparison: the largest partial-sum magnitude a block can see, bounded by sum |x_i| / n
+    bound = np.stack([np.abs(x.astype(np.float64)) for x in xf]).sum(0)[:count // 16 * 16].reshape(-1, 16).max(1) / n
+    err = np.abs(buf[0][:count // 16 * 16].astype(np.float64).reshape(-1, 16) - blocks).max(1)
+    stages = len(widths)
+    assert np.all(err <= bound * 0.0625 * (1 + stages)), float((err / bound).max())
+    rel_rms = np.sqrt(np.mean((buf[0] - exact) ** 2)) / np.sqrt(np.mean(exact ** 2))
+    assert rel_rms < 0.06 * stages + 0.03, rel_rms
+    # NVLS / one-shot / registered have no block-scaled variant
+    assert w.allreduce(buf, None, algo="oneshot", dtype_code=K.FP8_BLOCK, io_dtype_code=K.FLOAT) == -9
+
+
+def test_fp8_conversions():
+    import ctypes as C
+    L = ft._lib.load()
+    # every e4m3 code round-trips; monotone; saturation and ties
+    vals = []
+    for code in range(256):
+        f = L.ft_e4m3_to_float(code)
+        if code & 0x7f == 0x7f:
+            assert np.isnan(f)
+            continue
+        vals.append((code, f))
+        assert L.ft_float_to_e4m3(C.c_float(f)) == (code if code != 0x80 else 0x80), hex(code)
+    pos = sorted(f for c, f in vals if c < 0x80)
+    assert pos[0] == 0.0 and pos[1] == 2.0 ** -9 and pos[-1] == 448.0
+    assert L.ft_float_to_e4m3(C.c_float(1e9)) == 0x7e and L.ft_float_to_e4m3(C.c_float(-1e9)) == 0xfe
+    assert L.ft_float_to_e4m3(C.c_float(2.0 ** -10)) == 0          # tie -> even (0)
+    assert L.ft_float_to_e4m3(C.c_float(2.0 ** -10 * 1.01)) == 1   # above the tie -> smallest subnormal
+    assert L.ft_float_to_e4m3(C.c_float(1.0625)) == L.ft_float_to_e4m3(C.c_float(1.0))  # tie -> even mantissa
+    for amax in (0.0, 1e-30, 1.0, 447.0, 448.0, 449.0, 3e38):
+        s = L.ft_fp8_block_scale(C.c_float(amax))
+        if amax > 0:
+            scaled = amax * 2.0 ** (127 - s)
+            assert scaled <= 448.0 * (1 + 1e-6) and (scaled > 224.0 or s in (0, 254)), (amax, s, scaled)
+
+
 def test_scale_epilogue_fp32():
     n, count = 6, 333
     xf = make_inputs(n, count, np.float32)
