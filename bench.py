@@ -15,7 +15,9 @@ N == 1: there is no peer, so the same kernels are run for R=8 logical ranks emul
 (one cooperative launch, every "peer" in local HBM) - this measures the kernel path against HBM instead
 of NVLink and is labelled as such in `config`.
 
-value = aggregate bus bandwidth = ranks * busbw,  busbw = (bytes / t) * 2 (R-1) / R  (NCCL definition).
+value = aggregate bus bandwidth over the job's GPUs = n_gpus * busbw,  busbw = (bytes / t) * 2 (R-1) / R
+(NCCL definition, R = ranks). At N == 1 that is the one GPU's figure: the bus bandwidth each of its 8
+emulated ranks sees (all traffic stays in HBM).
 """
 import argparse
 import json
@@ -49,47 +51,63 @@ def parse():
 
 
 class ClockSampler:
-    """nvidia-smi clocks/throttle reasons DURING the timed region (B200_PROFILING.md recipe)."""
+    """nvidia-smi clocks/throttle reasons DURING the measured region (B200_PROFILING.md recipe): one
+    long-lived `nvidia-smi -lms 100` child, started before warm-up and terminated (by its own handle) after
+    the timed loop."""
     Q = ("index,clocks.sm,clocks.max.sm,power.draw,clocks_event_reasons.active,clocks_event_reasons.hw_slowdown,"
          "clocks_event_reasons.hw_thermal_slowdown,clocks_event_reasons.sw_thermal_slowdown,"
          "clocks_event_reasons.sw_power_cap")
 
     def __init__(self, gpu_index):
         self.idx = gpu_index
-        self.samples = []
-        self._stop = threading.Event()
+        self.proc = None
+        self.lines = []
         self._t = None
 
-    def _run(self):
-        while not self._stop.is_set():
-            try:
-                out = subprocess.run(["nvidia-smi", f"--query-gpu={self.Q}", "--format=csv,noheader,nounits",
-                                      "-i", str(self.idx)], capture_output=True, text=True, timeout=5).stdout
-                for line in out.strip().splitlines():
-                    f = [x.strip() for x in line.split(",")]
-                    if len(f) >= 9:
-                        self.samples.append(f)
-            except Exception:
-                pass
-            self._stop.wait(0.2)
+    def _pump(self):
+        try:
+            for line in self.proc.stdout:
+                self.lines.append((time.perf_counter(), line))
+        except Exception:
+            pass
 
     def start(self):
-        self._t = threading.Thread(target=self._run, daemon=True)
-        self._t.start()
+        try:
+            self.proc = subprocess.Popen(["nvidia-smi", f"--query-gpu={self.Q}", "--format=csv,noheader,nounits",
+                                          "-lms", "100", "-i", str(self.idx)], stdout=subprocess.PIPE,
+                                         stderr=subprocess.DEVNULL, text=True)
+            self._t = threading.Thread(target=self._pump, daemon=True)
+            self._t.start()
+        except Exception:
+            self.proc = None
 
-    def stop(self):
-        self._stop.set()
-        if self._t:
-            self._t.join(timeout=6)
-        sm = sorted(float(s[1]) for s in self.samples if s[1].replace(".", "").isdigit())
-        mx = [float(s[2]) for s in self.samples if s[2].replace(".", "").isdigit()]
+    def stop(self, t_begin=None, t_end=None):
+        if self.proc is not None:
+            self.proc.terminate()
+            try:
+                self.proc.wait(timeout=5)
+            except Exception:
+                self.proc.kill()
+            if self._t:
+                self._t.join(timeout=5)
+        rows = []
+        for ts, line in self.lines:
+            f = [x.strip() for x in line.split(",")]
+            if len(f) >= 9:
+                rows.append((ts, f))
+        timed = [f for ts, f in rows if t_begin is not None and t_begin <= ts <= t_end]
+        use = timed if len(timed) >= 3 else [f for _, f in rows]
+        sm = sorted(float(f[1]) for f in use if f[1].replace(".", "").isdigit())
+        mx = [float(f[2]) for f in use if f[2].replace(".", "").isdigit()]
+        pw = [float(f[3]) for f in use if f[3].replace(".", "").isdigit()]
         reasons = set()
-        for s in self.samples:
-            for name, v in zip(("hw_slowdown", "hw_thermal_slowdown", "sw_thermal_slowdown", "sw_power_cap"), s[5:9]):
+        for f in use:
+            for name, v in zip(("hw_slowdown", "hw_thermal_slowdown", "sw_thermal_slowdown", "sw_power_cap"), f[5:9]):
                 if v.lower().startswith("active"):
                     reasons.add(name)
         return {"sm_mhz": sm[len(sm) // 2] if sm else None, "sm_max_mhz": max(mx) if mx else None,
-                "reasons": sorted(reasons), "samples": len(self.samples)}
+                "power_w_max": max(pw) if pw else None, "reasons": sorted(reasons), "samples": len(use),
+                "samples_in_timed_loop": len(timed), "window": "timed loop" if len(timed) >= 3 else "warm-up + timed loop"}
 
 
 def busbw(nbytes, seconds, ranks):
@@ -138,7 +156,7 @@ def run_reference(args):
     bb = busbw(count * 4, sec, ranks)
     check = [ln for ln in p.stdout.splitlines() if ln.startswith("CHECK 0")]
     out = {
-        "impl": "reference", "metric": METRIC, "value": bb * ranks, "unit": "GB/s", "n_gpus": n,
+        "impl": "reference", "metric": METRIC, "value": bb * n, "unit": "GB/s", "n_gpus": n,
         "steps": args.steps, "warmup": args.warmup, "ms_per_step": sec * 1e3, "higher_is_better": True,
         "scaling": "weak", "vs_baseline": None, "dtype": "fp32", "data": "synthetic (data[i]=i, reference benchmark.cpp:119-123)",
         "busbw_per_rank_GBps": bb, "algbw_GBps": count * 4 / sec / 1e9,
@@ -146,7 +164,7 @@ def run_reference(args):
                    "parallelism": f"{ranks} CPU ranks (reference has no GPU path; MPI subset shim over shared memory)",
                    "widths": env["FT_TOPO"] or f"{ranks}", "timing": "reference's own per-repeat MPI_Wtime on rank 0",
                    "wall_s": round(wall, 2)},
-        "e2e": {"value": bb * ranks, "unit": "GB/s", "h2d_bytes_per_step": 0, "d2h_bytes_per_step": 0,
+        "e2e": {"value": bb * n, "unit": "GB/s", "h2d_bytes_per_step": 0, "d2h_bytes_per_step": 0,
                 "note": "host-resident data: the reference's timed region is already end to end"},
         "gpu_launches": 0,
         "check": check[0] if check else None,
@@ -237,13 +255,13 @@ def main():
         return 4
     del want
 
+    sampler = ClockSampler(local_rank)
+    if rank == 0:
+        sampler.start()
     for _ in range(args.warmup):
         refill()
         step()
     barrier()
-    sampler = ClockSampler(local_rank)
-    if rank == 0:
-        sampler.start()
     ev = [(torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)) for _ in range(args.steps)]
     barrier()
     t_wall0 = time.perf_counter()
@@ -254,7 +272,7 @@ def main():
         ev[i][1].record()
     barrier()
     t_wall = time.perf_counter() - t_wall0
-    clocks = sampler.stop() if rank == 0 else None
+    clocks = sampler.stop(t_wall0, t_wall0 + t_wall) if rank == 0 else None
     ms = [a.elapsed_time(b) for a, b in ev]
     total_ms = torch.tensor([sum(ms)], device=dev, dtype=torch.float64)
     if not emulated:
@@ -331,7 +349,7 @@ def main():
             roof = "NVLink 770 GB/s per direction (measured peer copy, B200_PROFILING.md)"
             frac = bb / 770.0
         out = {
-            "metric": METRIC, "value": bb * ranks, "unit": "GB/s", "n_gpus": n, "steps": args.steps,
+            "metric": METRIC, "value": bb * n, "unit": "GB/s", "n_gpus": n, "steps": args.steps,
             "warmup": args.warmup, "ms_per_step": ms_per_step, "higher_is_better": True, "scaling": "weak",
             "vs_baseline": None, "dtype": args.dtype, "data": "synthetic (randn, fixed seed)",
             "busbw_per_rank_GBps": bb, "algbw_GBps": nbytes / (ms_per_step / 1e3) / 1e9,
@@ -344,7 +362,7 @@ def main():
                        "l2": "message > L2 and re-filled (256 MiB written) between timed steps",
                        "call": info, "wall_s_timed_loop": round(t_wall, 3)},
             "clocks": clocks,
-            "e2e": {"value": e2e_bb * ranks, "unit": "GB/s", "ms_per_step": e2e_ms.item(), "steps": e2e_steps,
+            "e2e": {"value": e2e_bb * n, "unit": "GB/s", "ms_per_step": e2e_ms.item(), "steps": e2e_steps,
                     "h2d_bytes_per_step": nbytes * nloc, "d2h_bytes_per_step": 11 * esize,
                     "api": "Communicator.allreduce on a symmetric tensor; input copied from pinned host memory each step"},
             "gpu_launches": args.steps,
