@@ -27,10 +27,16 @@ def run(args, backend, comm, dev, rank, world, local):
     torch.manual_seed(1234)
     pdtype = torch.bfloat16 if args.param_dtype == "bf16" else torch.float32
     model, make_batch, loss_fn, per_sample = build(args.model, dev, pdtype)
-    ddp = DDP(model, device_ids=[local], bucket_cap_mb=args.bucket_mb, gradient_as_bucket_view=True)
     state = None
+    engine = None
+    if backend == "flextree-dp":  # zero-copy engine: gradients live in symmetric buckets
+        engine = ft.FlexTreeDataParallel(model, comm, bucket_mb=args.bucket_mb, max_ctas=args.max_ctas,
+                                         wire_dtype=("fp8" if args.wire == "fp8" else None))
+        ddp = engine
+    else:
+        ddp = DDP(model, device_ids=[local], bucket_cap_mb=args.bucket_mb, gradient_as_bucket_view=True)
     if backend == "flextree":
-        wire = torch.bfloat16 if args.wire == "bf16" else None
+        wire = torch.bfloat16 if args.wire == "bf16" else ("fp8" if args.wire == "fp8" else None)
         state = ft.FlexTreeHookState(comm, wire_dtype=wire, max_ctas=args.max_ctas)
         ddp.register_comm_hook(state, ft.ddp_comm_hook)
     opt = torch.optim.SGD(ddp.parameters(), lr=args.lr, momentum=0.9)
@@ -39,9 +45,14 @@ def run(args, backend, comm, dev, rank, world, local):
 
     def step():
         x, y = make_batch(args.batch, g)
-        opt.zero_grad(set_to_none=True)
+        if engine is not None:
+            engine.zero_grad()
+        else:
+            opt.zero_grad(set_to_none=True)
         loss = loss_fn(ddp, x, y)
         loss.backward()
+        if engine is not None:
+            engine.synchronize()
         opt.step()
         return loss
 
@@ -62,6 +73,9 @@ def run(args, backend, comm, dev, rank, world, local):
            "ms_per_step": round(ms.item(), 3), "items_per_s": round(args.batch * per_sample * world / (ms.item() / 1e3), 1),
            "params": nparam, "param_dtype": args.param_dtype, "wire": args.wire if backend == "flextree" else "native",
            "final_loss": round(torch.stack(losses)[-3:].float().mean().item(), 5)}
+    if engine is not None:
+        rec["buckets"] = len(engine.buckets)
+        rec["device_error"] = comm.error()
     if state is not None:
         rec["hook_calls"] = state.calls
         rec["hook_bytes_per_step"] = state.bytes // max(1, args.steps + args.warmup)
@@ -77,8 +91,8 @@ def main():
     ap.add_argument("--batch", type=int, default=32)
     ap.add_argument("--steps", type=int, default=10)
     ap.add_argument("--warmup", type=int, default=3)
-    ap.add_argument("--comm", default="both", choices=["nccl", "flextree", "both"])
-    ap.add_argument("--wire", default="native", choices=["native", "bf16"])
+    ap.add_argument("--comm", default="both", choices=["nccl", "flextree", "flextree-dp", "both", "all"])
+    ap.add_argument("--wire", default="native", choices=["native", "bf16", "fp8"])
     ap.add_argument("--param-dtype", default="fp32", choices=["fp32", "bf16"])
     ap.add_argument("--bucket-mb", type=int, default=25)
     ap.add_argument("--lr", type=float, default=0.01)
@@ -90,18 +104,20 @@ def main():
     dev = torch.device("cuda", local)
     dist.init_process_group("nccl", device_id=dev)
     torch.backends.cudnn.benchmark = True
-    comm = ft.init() if args.comm in ("flextree", "both") else None
+    comm = ft.init() if args.comm != "nccl" else None
     results, params = [], {}
-    for backend in (["nccl", "flextree"] if args.comm == "both" else [args.comm]):
+    order = {"both": ["nccl", "flextree"], "all": ["nccl", "flextree", "flextree-dp"]}.get(args.comm, [args.comm])
+    for backend in order:
         rec, flat = run(args, backend, comm, dev, rank, world, local)
         results.append(rec)
         params[backend] = flat
         torch.cuda.empty_cache()
-    if len(params) == 2:
-        a, b = params["nccl"], params["flextree"]
-        rel = ((a - b).norm() / a.norm().clamp_min(1e-12)).item()
+    if "nccl" in params and len(params) > 1:
+        a = params["nccl"]
         for r in results:
-            r["param_rel_diff_vs_other"] = rel
+            if r["comm"] != "nccl":
+                b = params[r["comm"]]
+                r["param_rel_diff_vs_nccl"] = ((a - b).norm() / a.norm().clamp_min(1e-12)).item()
     if rank == 0:
         for r in results:
             line = json.dumps(r)

@@ -159,6 +159,7 @@ def main():
                                    torch.nn.GELU(), torch.nn.Linear(512, 10)).to(dev)
     m_ref, m_ft = make(), make()
     m_ft.load_state_dict(m_ref.state_dict())
+    make_state = {k: v.clone() for k, v in m_ref.state_dict().items()}
     d_ref = DDP(m_ref, device_ids=[local], bucket_cap_mb=1)
     d_ft = DDP(m_ft, device_ids=[local], bucket_cap_mb=1)
     state = ft.FlexTreeHookState(comm)
@@ -177,6 +178,32 @@ def main():
     assert state.calls > 0 and comm.error() == 0
     for p_ref, p_ft in zip(m_ref.parameters(), m_ft.parameters()):
         assert torch.allclose(p_ref, p_ft, rtol=1e-4, atol=1e-5), "DDP hook diverged from NCCL DDP"
+
+    # 8. zero-copy data-parallel engine (gradients in symmetric buckets) vs the same NCCL DDP run
+    m_dp = make()
+    m_dp.load_state_dict(make_state)
+    dp = ft.FlexTreeDataParallel(m_dp, comm, bucket_mb=1)
+    o_dp = torch.optim.SGD(m_dp.parameters(), lr=0.05)
+    g2 = torch.Generator(device=dev).manual_seed(4242 + rank)
+    m_ref2 = make()
+    m_ref2.load_state_dict(make_state)
+    d_ref2 = DDP(m_ref2, device_ids=[local], bucket_cap_mb=1)
+    o_ref2 = torch.optim.SGD(d_ref2.parameters(), lr=0.05)
+    for step in range(5):
+        xb = torch.randn(64, 256, device=dev, generator=g2)
+        yb = torch.randint(0, 10, (64,), device=dev, generator=g2)
+        o_ref2.zero_grad()
+        torch.nn.functional.cross_entropy(d_ref2(xb), yb).backward()
+        o_ref2.step()
+        dp.zero_grad()
+        torch.nn.functional.cross_entropy(dp(xb), yb).backward()
+        dp.synchronize()
+        o_dp.step()
+    torch.cuda.synchronize()
+    assert comm.error() == 0
+    assert comm.last_call()["mode"] == "registered"
+    for p_ref, p_dp in zip(m_ref2.parameters(), m_dp.parameters()):
+        assert torch.allclose(p_ref, p_dp, rtol=1e-4, atol=1e-5), "FlexTreeDataParallel diverged from NCCL DDP"
 
     dist.barrier()
     ft.shutdown()
