@@ -93,7 +93,7 @@ def _declare(L):
     sig("ft_host_clear_error", None, [vp])
     sig("ft_host_epoch", C.c_ulonglong, [vp, i32])
     sig("ft_host_allreduce", i64, [vp, C.POINTER(vp), C.POINTER(vp), i64, i32, i32, i32, i32, pi32, i32,
-                                   i32, i64, i32, dbl, i32, C.c_ulonglong, i32, i32])
+                                   i32, i64, i32, dbl, i32, C.c_ulonglong, i32, i32, i32])
     sig("ft_bf16_to_float", C.c_float, [C.c_uint16])
     sig("ft_float_to_bf16", C.c_uint16, [C.c_float])
     sig("ft_f16_to_float", C.c_float, [C.c_uint16])
@@ -127,4 +127,8 @@ def _declare(L):
     sig("ft_allreduce_ex", i32, [vp, vp, C.c_size_t, i32, i32, i32, dbl, vp, vp])
     sig("ft_allreduce_multi", i32, [C.POINTER(vp), C.POINTER(vp), C.c_size_t, i32, i32, i32, dbl, vp, vp])
     sig("ft_comm_last_call", i32, [vp, vp])
+    sig("ft_reduce_scatter", i32, [vp, vp, C.c_size_t, i32, i32, vp, vp])
+    sig("ft_all_gather", i32, [vp, vp, C.c_size_t, i32, vp, vp])
+    sig("ft_reduce_scatter_multi", i32, [C.POINTER(vp), C.POINTER(vp), C.c_size_t, i32, i32, vp, vp])
+    sig("ft_all_gather_multi", i32, [C.POINTER(vp), C.POINTER(vp), C.c_size_t, i32, vp, vp])
     sig("ft_allreduce_emulated_noalloc", i32, [C.POINTER(vp), C.POINTER(vp), i32, C.c_size_t, i32, i32, vp])

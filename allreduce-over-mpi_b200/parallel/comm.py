@@ -274,3 +274,48 @@ class Communicator:
                                             self._stream(stream))
         _check(self._L, rc, "ft_allreduce_multi")
         return outs
+
+    # ---- the halves ------------------------------------------------------------------------------------------------
+    def reduce_scatter(self, tensor, out, op="sum", stream=None):
+        """out (numel/size elements) = this rank's block of the reduction of `tensor` across ranks."""
+        n = self.size
+        if tensor.numel() != out.numel() * n or tensor.dtype != out.dtype:
+            raise ValueError("reduce_scatter: input must hold size * out.numel() elements of out's dtype")
+        opc = K.OPS[op] if isinstance(op, str) else int(op)
+        with torch.cuda.device(self.device):
+            rc = self._L.ft_reduce_scatter(C.c_void_p(tensor.data_ptr()), C.c_void_p(out.data_ptr()), out.numel(),
+                                           K.torch_dtype_code(out.dtype), opc, self._h, self._stream(stream))
+        _check(self._L, rc, "ft_reduce_scatter")
+        return out
+
+    def all_gather(self, tensor, out, stream=None):
+        """out (size * numel elements) = the blocks of all ranks in rank order."""
+        n = self.size
+        if out.numel() != tensor.numel() * n or tensor.dtype != out.dtype:
+            raise ValueError("all_gather: out must hold size * input.numel() elements of the input dtype")
+        with torch.cuda.device(self.device):
+            rc = self._L.ft_all_gather(C.c_void_p(tensor.data_ptr()), C.c_void_p(out.data_ptr()), tensor.numel(),
+                                       K.torch_dtype_code(out.dtype), self._h, self._stream(stream))
+        _check(self._L, rc, "ft_all_gather")
+        return out
+
+    def reduce_scatter_multi(self, tensors, outs, op="sum", stream=None):
+        n = self.emulated_ranks
+        opc = K.OPS[op] if isinstance(op, str) else int(op)
+        s = (C.c_void_p * n)(*[t.data_ptr() for t in tensors])
+        r = (C.c_void_p * n)(*[t.data_ptr() for t in outs])
+        with torch.cuda.device(self.device):
+            rc = self._L.ft_reduce_scatter_multi(s, r, outs[0].numel(), K.torch_dtype_code(outs[0].dtype), opc, self._h,
+                                                 self._stream(stream))
+        _check(self._L, rc, "ft_reduce_scatter_multi")
+        return outs
+
+    def all_gather_multi(self, tensors, outs, stream=None):
+        n = self.emulated_ranks
+        s = (C.c_void_p * n)(*[t.data_ptr() for t in tensors])
+        r = (C.c_void_p * n)(*[t.data_ptr() for t in outs])
+        with torch.cuda.device(self.device):
+            rc = self._L.ft_all_gather_multi(s, r, tensors[0].numel(), K.torch_dtype_code(outs[0].dtype), self._h,
+                                             self._stream(stream))
+        _check(self._L, rc, "ft_all_gather_multi")
+        return outs

@@ -44,11 +44,11 @@ class HostWorld:
 
     def allreduce(self, send, recv=None, op="sum", algo="stages", widths=None, ctas=2, tile_bytes=4096,
                   mode=K.MODE_STAGING, scale=None, dtype_code=None, io_dtype_code=None,
-                  timeout_s=20.0, skip_rank=-1, lonely=0):
+                  timeout_s=20.0, skip_rank=-1, lonely=0, phases=0, count=None):
         """send/recv: lists of numpy arrays (one per rank). recv=None -> in place."""
         n = self.n
         recv = send if recv is None else recv
-        count = send[0].size
+        count = send[0].size if count is None else count
         if dtype_code is None:
             dtype_code = K.NUMPY_DTYPE[send[0].dtype]
         if io_dtype_code is None:
@@ -62,5 +62,5 @@ class HostWorld:
             self._h, s, r, count, dtype_code, io_dtype_code, K.OPS[op] if isinstance(op, str) else op,
             K.ALGOS[algo] if isinstance(algo, str) else algo, w, len(widths), ctas, tile_bytes, mode,
             1.0 if scale is None else float(scale), 0 if scale is None else 1,
-            int(timeout_s * 1e9), skip_rank, lonely)
+            int(timeout_s * 1e9), skip_rank, lonely, phases)
         return rc

@@ -55,6 +55,8 @@ struct CommDev {
 // 2+m+i = i-th AG stage done (stage m-1-i), last used slot = exit. Slot FT_TRACE_SLOTS-1 holds the count.
 static const int FT_TRACE_SLOTS = 24;
 
+enum Phases { PHASES_ALLREDUCE = 0, PHASES_REDUCE_SCATTER = 1, PHASES_ALL_GATHER = 2 };
+
 enum Mode {
   MODE_STAGING = 0,     // user buffers are private: copy-in to the symmetric window, parity double-buffer
   MODE_REGISTERED = 1   // the user buffer IS the symmetric window (in place): zero copy + exit barrier
@@ -83,6 +85,8 @@ struct StagedArgs {
   int use_tma;  // CUDA back end: stage peer chunks through shared memory with cp.async.bulk (TMA)
   int lonely;   // ranks plan.nranks .. plan.nranks+lonely-1 are outside the tree (N = tree + lonely)
   long long scale_plane_off;  // fp8 block-scaled wire: byte offset of the scale plane inside the window
+  int phases;   // 0 = allreduce, 1 = reduce-scatter only (recv gets my block), 2 = all-gather only (send is my block)
+  int reserved2_;
   RankCall rc[FT_MAX_LOCAL];
 };
 

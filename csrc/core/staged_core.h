@@ -907,6 +907,40 @@ struct StagedCta {
     }
   }
 
+  // ---- the two halves as collectives of their own (ZeRO / FSDP style users) ------------------------------
+  // The reference's algorithm IS a reduce-scatter followed by an all-gather (mpi_mod.hpp:988-1029 /
+  // :1050-1060); exposing the halves costs two small copy loops.
+  // reduce-scatter epilogue: my fully reduced block r, tile t -> recv[0 .. B)
+  FT_DEV void half_rs_out_tile(int t) {
+    long long start;
+    const int n = tile_valid32(r, t, &start);
+    if (n <= 0) return;
+    const long long blk0 = (long long)r * a.lay.block;
+    const char* wr = rc.win[r] + woff;
+    IO* y = (IO*)rc.recv;
+    const int nvec = (n + VE - 1) / VE;
+    for (int q = be.tid(); q < nvec; q += be.nthr()) {
+      const long long el = start + (long long)q * VE;
+      const int nv = n - q * VE < VE ? n - q * VE : VE;
+      st_user(y, el - blk0, wire_to_io(ld_win(wr, el * (long long)sizeof(T), false)), nv);
+    }
+  }
+  // all-gather prologue: send[0 .. B) -> my block r of my window, tile t
+  FT_DEV void half_ag_in_tile(int t) {
+    long long start;
+    const int n = tile_valid32(r, t, &start);
+    if (n <= 0) return;
+    const long long blk0 = (long long)r * a.lay.block;
+    char* wr = rc.win[r] + woff;
+    const IO* x = (const IO*)rc.send;
+    const int nvec = (n + VE - 1) / VE;
+    for (int q = be.tid(); q < nvec; q += be.nthr()) {
+      const long long el = start + (long long)q * VE;
+      const int nv = n - q * VE < VE ? n - q * VE : VE;
+      st_win(wr, el * (long long)sizeof(T), io_to_wire(ld_user(x, el - blk0, nv)));
+    }
+  }
+
   // ---- lonely ranks (world size = tree ranks + L, the reference's "+1" trees) ------------------------------
   // Capability parity: the lonely ops of Send_Ops/Recv_Ops (mpi_mod.hpp:172-178, :208-211) and the lonely
   // branches of tree_allreduce (:981-987, :1019-1026, :1041-1099), which the reference ships as stubs
@@ -1015,8 +1049,17 @@ struct StagedCta {
     }
 
     trace(0);
+    if (a.phases == PHASES_ALL_GATHER) {
+      // my block is already "reduced": place it in my window and announce it like a finished last RS stage
+      for (int j = 0; j < mine; ++j) {
+        half_ag_in_tile(cta + j * G);
+        be.sync();
+        signal_group(PH_RS0 + m - 1, m - 1, E + j + 1);
+      }
+    }
     // IN: publish my window to my stage-0 group
-    if (a.mode == MODE_STAGING) {
+    if (a.phases == PHASES_ALL_GATHER) {
+    } else if (a.mode == MODE_STAGING) {
       for (int j = 0; j < mine; ++j) {
         if constexpr (kBlockScaled) q_copy_in_tile(cta + j * G);
         else copy_in_tile<CU>(cta + j * G);
@@ -1029,7 +1072,7 @@ struct StagedCta {
     trace(1);
 
     // reduce-scatter, stage-major so that a wait is almost always for a long-finished tile
-    for (int k = 0; k < m; ++k) {
+    for (int k = 0; k < m && a.phases != PHASES_ALL_GATHER; ++k) {
       for (int j = 0; j < mine; ++j) {
         wait_group(k == 0 ? (int)PH_IN : PH_RS0 + k - 1, k, E + j + 1);
         if constexpr (kBlockScaled) q_rs_tile(k, cta + j * G);
@@ -1049,8 +1092,11 @@ struct StagedCta {
       trace(2 + k);
     }
 
+    if (a.phases == PHASES_REDUCE_SCATTER) {
+      for (int j = 0; j < mine; ++j) half_rs_out_tile(cta + j * G);  // my own writes, same CTA: no flag needed
+    }
     // all-gather, stages unwound in reverse
-    for (int k = m - 1; k >= 0; --k) {
+    for (int k = m - 1; k >= 0 && a.phases != PHASES_REDUCE_SCATTER; --k) {
       for (int j = 0; j < mine; ++j) {
         wait_group(k == m - 1 ? PH_RS0 + k : PH_AG0 + k + 1, k, E + j + 1);
         if constexpr (kBlockScaled) q_ag_tile(k, cta + j * G);

@@ -98,7 +98,7 @@ unsigned long long ft_host_epoch(void* h, int rank) { return ((HostWorld*)h)->ep
 long long ft_host_allreduce(void* h, const void* const* send, void* const* recv, long long count,
                             int dtype, int io_dtype, int op, int algo, const int* widths, int nstages,
                             int ctas, long long tile_bytes, int mode, double scale, int apply_scale,
-                            unsigned long long timeout_ns, int skip_rank, int lonely) {
+                            unsigned long long timeout_ns, int skip_rank, int lonely, int phases) {
   auto* w = (HostWorld*)h;
   StagedArgs a;
   memset(&a, 0, sizeof a);
@@ -111,12 +111,15 @@ long long ft_host_allreduce(void* h, const void* const* send, void* const* recv,
   if (lonely < 0 || a.plan.nranks + lonely != w->n) return -2;
   if (lonely > 0 && (algo != ALGO_STAGED || mode != MODE_STAGING)) return -8;
   a.lonely = lonely;
+  a.phases = phases;
+  if (phases != PHASES_ALLREDUCE && (algo != ALGO_STAGED || lonely > 0 || mode != MODE_STAGING || count % w->n)) return -10;
   if (dtype == DT_FP8_BLOCK && (algo != ALGO_STAGED || lonely > 0 || mode != MODE_STAGING)) return -9;
   const int es = dtype_size(dtype), ios = dtype_size(io_dtype);
   if (!es || !ios) return -3;
   bool vec = true;
   for (int r = 0; r < w->n; ++r)
     vec = vec && ((uintptr_t)send[r] % 16 == 0) && ((uintptr_t)recv[r] % 16 == 0);
+  if (phases != PHASES_ALLREDUCE && ((count / w->n) * es) % 16) vec = false;  // blocks must not be padded
   a.lay = make_layout(count, a.plan.nranks, es, tile_bytes, vec);
   a.scale_plane_off = ((long long)a.lay.block * a.plan.nranks * es + 255) & ~255LL;
   if ((size_t)(a.scale_plane_off + (a.lay.block * a.plan.nranks) / 16 + 16) > w->win_bytes) return -4;

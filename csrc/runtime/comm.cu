@@ -351,7 +351,7 @@ ft_result_t check_device_error(ft_comm* c) {
 
 // The one place a collective is resolved and launched. send/recv: per logical rank.
 ft_result_t do_allreduce(ft_comm* c, const void* const* send, void* const* recv, size_t count, int io_dtype,
-                         int wire_dtype, int op, double scale, cudaStream_t stream) {
+                         int wire_dtype, int op, double scale, cudaStream_t stream, int phases = PHASES_ALLREDUCE) {
   const int N = c->nranks, L = c->nlocal;
   if (io_dtype < 0 || io_dtype >= DT_COUNT || wire_dtype < 0 || wire_dtype >= DT_COUNT) {
     set_last_error("bad dtype");
@@ -392,6 +392,17 @@ ft_result_t do_allreduce(ft_comm* c, const void* const* send, void* const* recv,
     if (!r[(size_t)l]) { set_last_error("null recvbuf"); return FT_ERR_INVALID; }
     vec = vec && ((uintptr_t)s[(size_t)l] % 16 == 0) && ((uintptr_t)r[(size_t)l] % 16 == 0);
     in_place = in_place && s[(size_t)l] == r[(size_t)l];
+  }
+
+  if (phases != PHASES_ALLREDUCE) {
+    // the halves: `count` is the TOTAL element count (nranks * per-rank block); blocks must not be padded
+    if (count % (size_t)N) { set_last_error("reduce_scatter/all_gather: total count must be a multiple of the world size"); return FT_ERR_INVALID; }
+    if (((count / (size_t)N) * (size_t)es) % 16) vec = false;  // scalar path keeps block == per-rank count exactly
+    in_place = false;
+    if (N == 1) {
+      if (s[0] != r[0]) FT_CHECK_RT(cudaMemcpyAsync(r[0], s[0], count * (size_t)ios, cudaMemcpyDeviceToDevice, stream));
+      return FT_SUCCESS;
+    }
   }
 
   // ---- N == 1: copy fast path (mpi_mod.hpp:1181-1188) ---------------------------------------------
@@ -480,6 +491,14 @@ ft_result_t do_allreduce(ft_comm* c, const void* const* send, void* const* recv,
     algo = ALGO_STAGED;
     mode = MODE_STAGING;
   }
+  if (phases != PHASES_ALLREDUCE) {  // the halves run on the P2P stage kernels with private windows
+    if (lonely > 0 || wire_dtype == DT_FP8_BLOCK) {
+      set_last_error("reduce_scatter/all_gather: no lonely trees / fp8 wire");
+      return FT_ERR_UNSUPPORTED;
+    }
+    if (algo != ALGO_STAGED) { algo = ALGO_STAGED; widths = {N}; }
+    mode = MODE_STAGING;
+  }
   if (wire_dtype == DT_FP8_BLOCK) {  // block-scaled wire: register-staged P2P stages, private windows, vector path
     if (!vec || lonely > 0) {
       set_last_error("the fp8 block-scaled wire needs 16-byte aligned buffers and a full tree");
@@ -502,6 +521,7 @@ ft_result_t do_allreduce(ft_comm* c, const void* const* send, void* const* recv,
   Shape sh = pick_shape(c, algo, mode, tma, msg_bytes, T, es);
   a.lay = make_layout((long long)count, T, es, sh.tile_bytes, vec);
   a.lonely = lonely;
+  a.phases = phases;
   // flag values encode the tile ordinal in FT_EPOCH_SHIFT bits (ring: steps * tiles)
   {
     long long per_cta = (a.lay.ntiles + sh.ctas - 1) / sh.ctas;
@@ -964,6 +984,37 @@ ft_result_t ft_allreduce_multi(const void* const* sendbufs, void* const* recvbuf
   if (sendbufs)
     for (int l = 0; l < comm->nlocal; ++l) s[(size_t)l] = sendbufs[l];
   return do_allreduce(comm, s.data(), recvbufs, count, (int)dtype, (int)wire_dtype, (int)op, scale, (cudaStream_t)stream);
+}
+
+// The two halves of the algorithm as collectives (reduce-scatter: recv = my block of the reduction;
+// all-gather: send = my block). Emulated communicators pass one pointer per logical rank.
+static ft_result_t half_collective(const void* const* sendbufs, void* const* recvbufs, size_t per_rank_count,
+                                   ft_dtype_t dtype, ft_op_t op, ft_comm_t* comm, void* stream, int phases) {
+  if (!comm || !sendbufs || !recvbufs) return FT_ERR_INVALID;
+  return do_allreduce(comm, sendbufs, recvbufs, per_rank_count * (size_t)comm->nranks, (int)dtype, (int)dtype, (int)op, 1.0,
+                      (cudaStream_t)stream, phases);
+}
+ft_result_t ft_reduce_scatter(const void* sendbuf, void* recvbuf, size_t recvcount, ft_dtype_t dtype, ft_op_t op,
+                              ft_comm_t* comm, void* stream) {
+  if (comm && comm->kind == COMM_EMULATED) { set_last_error("emulated communicator: use ft_reduce_scatter_multi"); return FT_ERR_INVALID; }
+  const void* s[1] = {sendbuf};
+  void* r[1] = {recvbuf};
+  return half_collective(s, r, recvcount, dtype, op, comm, stream, PHASES_REDUCE_SCATTER);
+}
+ft_result_t ft_all_gather(const void* sendbuf, void* recvbuf, size_t sendcount, ft_dtype_t dtype, ft_comm_t* comm,
+                          void* stream) {
+  if (comm && comm->kind == COMM_EMULATED) { set_last_error("emulated communicator: use ft_all_gather_multi"); return FT_ERR_INVALID; }
+  const void* s[1] = {sendbuf};
+  void* r[1] = {recvbuf};
+  return half_collective(s, r, sendcount, dtype, FT_SUM, comm, stream, PHASES_ALL_GATHER);
+}
+ft_result_t ft_reduce_scatter_multi(const void* const* sendbufs, void* const* recvbufs, size_t recvcount, ft_dtype_t dtype,
+                                    ft_op_t op, ft_comm_t* comm, void* stream) {
+  return half_collective(sendbufs, recvbufs, recvcount, dtype, op, comm, stream, PHASES_REDUCE_SCATTER);
+}
+ft_result_t ft_all_gather_multi(const void* const* sendbufs, void* const* recvbufs, size_t sendcount, ft_dtype_t dtype,
+                                ft_comm_t* comm, void* stream) {
+  return half_collective(sendbufs, recvbufs, sendcount, dtype, FT_SUM, comm, stream, PHASES_ALL_GATHER);
 }
 
 ft_result_t ft_comm_last_call(const ft_comm_t* c, ft_call_info_t* out) {

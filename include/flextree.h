@@ -185,6 +185,19 @@ ft_result_t ft_allreduce_multi(const void* const* sendbufs, void* const* recvbuf
                                ft_dtype_t dtype, ft_dtype_t wire_dtype, ft_op_t op, double scale,
                                ft_comm_t* comm, void* stream);
 
+/* The two halves of the algorithm as collectives of their own (the reference's tree_allreduce is a
+ * reduce-scatter loop followed by an all-gather loop, mpi_mod.hpp:988-1029 / :1050-1060).
+ * ft_reduce_scatter: sendbuf holds nranks*recvcount elements, recvbuf receives this rank's reduced block.
+ * ft_all_gather: sendbuf holds sendcount elements (this rank's block), recvbuf nranks*sendcount. */
+ft_result_t ft_reduce_scatter(const void* sendbuf, void* recvbuf, size_t recvcount, ft_dtype_t dtype, ft_op_t op,
+                              ft_comm_t* comm, void* stream);
+ft_result_t ft_all_gather(const void* sendbuf, void* recvbuf, size_t sendcount, ft_dtype_t dtype, ft_comm_t* comm,
+                          void* stream);
+ft_result_t ft_reduce_scatter_multi(const void* const* sendbufs, void* const* recvbufs, size_t recvcount,
+                                    ft_dtype_t dtype, ft_op_t op, ft_comm_t* comm, void* stream);
+ft_result_t ft_all_gather_multi(const void* const* sendbufs, void* const* recvbufs, size_t sendcount,
+                                ft_dtype_t dtype, ft_comm_t* comm, void* stream);
+
 /* What the last call on this communicator resolved to (for logs, tests and the benchmark). */
 typedef struct {
   int algo;

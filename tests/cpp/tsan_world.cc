@@ -13,7 +13,7 @@ void* ft_host_world_create(int, size_t, size_t);
 void ft_host_world_destroy(void*);
 void* ft_host_registered(void*, int);
 long long ft_host_allreduce(void*, const void* const*, void* const*, long long, int, int, int, int,
-                            const int*, int, int, long long, int, double, int, unsigned long long, int, int);
+                            const int*, int, int, long long, int, double, int, unsigned long long, int, int, int);
 }
 
 static int run(int n, std::vector<int> widths, int algo, int mode, long long count, int ctas, long long tile, int lonely = 0) {
@@ -31,7 +31,7 @@ static int run(int n, std::vector<int> widths, int algo, int mode, long long cou
   for (int rep = 0; rep < 3; ++rep) {
     if (mode) for (int i = 0; i < n; ++i) for (long long j = 0; j < count; ++j) ((float*)s[i])[j] = (float)(i + 1) * (float)(j % 7);
     long long rc = ft_host_allreduce(w, s.data(), r.data(), count, 6, 6, 0, algo, widths.data(), (int)widths.size(),
-                                     ctas, tile, mode, 1.0, 0, 20000000000ull, -1, lonely);
+                                     ctas, tile, mode, 1.0, 0, 20000000000ull, -1, lonely, 0);
     if (rc) { printf("rc=%lld\n", rc); bad = 1; }
     float tot = (float)n * (n + 1) / 2;
     for (int i = 0; i < n; ++i)

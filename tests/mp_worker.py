@@ -127,6 +127,22 @@ def main():
         assert comm.last_call()["mode"] == "registered"
     comm.set_algo("auto")
 
+    # 5b. the halves against torch.distributed
+    comm.set_algo("stages")
+    per = 50000
+    x = torch.randn(per * world, device=dev, generator=g)
+    mine = torch.empty(per, device=dev)
+    comm.reduce_scatter(x, mine)
+    ref = torch.empty(per, device=dev)
+    dist.reduce_scatter_tensor(ref, x.clone())
+    check(mine, ref, 1e-5, "reduce_scatter")
+    full = torch.empty(per * world, device=dev)
+    comm.all_gather(mine, full)
+    ref_full = torch.empty(per * world, device=dev)
+    dist.all_gather_into_tensor(ref_full, mine)
+    check(full, ref_full, 0, "all_gather")
+    comm.set_algo("auto")
+
     # 6. CUDA graph capture + replay
     comm.set_algo("stages")
     n = 1 << 18

@@ -355,6 +355,31 @@ def test_fp8_block_scaled_wire_matches_cpu_model(comms):
     c.set_algo("auto")
 
 
+@pytest.mark.parametrize("n,widths,per_rank", [(8, [2, 4], 4096), (8, [8], 1000), (4, [2, 2], 65536), (6, [3, 2], 37)])
+def test_reduce_scatter_and_all_gather(comms, n, widths, per_rank):
+    c = comms(n)
+    c.set_algo("stages")
+    c.set_widths(widths)
+    total = per_rank * n
+    xs = [torch.randn(total, device="cuda") for _ in range(n)]
+    outs = [torch.zeros(per_rank, device="cuda") for _ in range(n)]
+    c.reduce_scatter_multi(xs, outs)
+    torch.cuda.synchronize()
+    assert c.error() == 0
+    full = torch.stack(xs).double().sum(0)
+    for r in range(n):
+        assert torch.allclose(outs[r].double(), full[r * per_rank:(r + 1) * per_rank], rtol=1e-5, atol=1e-5)
+    gathered = [torch.zeros(total, device="cuda") for _ in range(n)]
+    c.all_gather_multi(outs, gathered)
+    torch.cuda.synchronize()
+    assert c.error() == 0
+    want = torch.cat(outs)
+    for r in range(n):
+        assert torch.equal(gathered[r], want)
+    c.set_widths(None)
+    c.set_algo("auto")
+
+
 def test_phase_trace(comms):
     c = comms(8)
     c.set_algo("stages")

@@ -365,6 +365,42 @@ def test_lonely_ranks(n, widths, lonely):
                        mode=K.MODE_REGISTERED) == -8   # lonely trees use private windows only
 
 
+@pytest.mark.parametrize("n,widths", [(4, [4]), (6, [2, 3]), (8, [2, 2, 2])])
+@pytest.mark.parametrize("per_rank", [4, 37, 1024])
+def test_reduce_scatter_and_all_gather_halves(n, widths, per_rank):
+    """The two halves of the algorithm as collectives of their own."""
+    w = HostWorld(n, window_bytes=1 << 16)
+    total = per_rank * n
+    xs = make_inputs(n, total, np.int32)
+    send = [aligned_copy(x) for x in xs]
+    recv = [aligned_empty(per_rank, np.int32) for _ in range(n)]
+    assert w.allreduce(send, recv, widths=widths, ctas=2, tile_bytes=128, phases=1, count=total) == 0
+    with np.errstate(over="ignore"):
+        full = np.sum(np.stack(xs), 0, dtype=np.int32)
+    for r in range(n):
+        np.testing.assert_array_equal(recv[r], full[r * per_rank:(r + 1) * per_rank], err_msg=f"rs rank {r}")
+        np.testing.assert_array_equal(send[r], xs[r])
+    blocks = [aligned_copy(x[:per_rank]) for x in make_inputs(n, per_rank, np.float32)]
+    outs = [aligned_empty(total, np.float32) for _ in range(n)]
+    assert w.allreduce(blocks, outs, widths=widths, ctas=3, tile_bytes=64, phases=2, count=total) == 0
+    want = np.concatenate(blocks)
+    for r in range(n):
+        np.testing.assert_array_equal(outs[r], want, err_msg=f"ag rank {r}")
+    # RS followed by AG == allreduce
+    xf = make_inputs(n, total, np.float32)
+    part = [aligned_empty(per_rank, np.float32) for _ in range(n)]
+    assert w.allreduce([aligned_copy(x) for x in xf], part, widths=widths, phases=1, count=total) == 0
+    allr = [aligned_empty(total, np.float32) for _ in range(n)]
+    assert w.allreduce(part, allr, widths=widths, phases=2, count=total) == 0
+    ref = [aligned_copy(x) for x in xf]
+    assert w.allreduce(ref, None, widths=widths) == 0
+    vec = (per_rank * 4) % 16 == 0
+    if vec:  # same block split -> same summation order -> same bits
+        np.testing.assert_array_equal(allr[0], ref[0])
+    else:
+        np.testing.assert_allclose(allr[0], ref[0], rtol=1e-5, atol=1e-5)
+
+
 def test_watchdog_fires_instead_of_hanging():
     """Fault injection: one rank never joins the collective. The others must report a timeout."""
     n = 4
