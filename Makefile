@@ -22,7 +22,7 @@ CXXFLAGS := -std=c++17 -O2 -fPIC -Wall -Wextra -Wno-unknown-pragmas -Wno-maybe-u
 NVFLAGS := -ccbin /usr/bin/g++ -std=c++17 -O3 $(ARCH) -lineinfo -Xcompiler -fPIC -Xcompiler -Wall -Iinclude $(VERDEFS) --expt-relaxed-constexpr
 
 PLANNER_SRC := csrc/planner/factorize.cc csrc/planner/cost_model.cc csrc/planner/schedule.cc csrc/planner/c_api.cc
-HOST_SRC := csrc/host/host_world.cc csrc/host/host_run_all.cc $(wildcard csrc/host/host_run_g*.cc)
+HOST_SRC := csrc/host/host_world.cc csrc/host/host_comm.cc csrc/host/host_run_all.cc $(wildcard csrc/host/host_run_g*.cc)
 CUDA_SRC := $(wildcard csrc/kernels/*.cu) $(wildcard csrc/runtime/*.cu)
 RT_CC_SRC := $(wildcard csrc/runtime/*.cc)
 

@@ -1,0 +1,112 @@
+"""Multi-process CPU communicator (csrc/host/host_comm.cc): one process per rank, shared-memory windows,
+the same algorithm templates as the GPU kernels. Works under any torch.distributed backend (gloo on
+machines without GPUs) - this is what the CPU multi-process tests drive, and it is a usable CPU allreduce
+in its own right (the reference is exactly that, over MPI: allreduce_over_mpi/mpi_mod.hpp:1167-1221)."""
+import ctypes as C
+
+import numpy as np
+import torch
+
+from .. import _lib
+from ..ops import constants as K
+
+_AG_FN = C.CFUNCTYPE(C.c_int, C.c_void_p, C.c_void_p, C.c_void_p, C.c_size_t)
+
+
+class HostCommunicator:
+    def __init__(self, group=None, window_bytes=8 << 20, ll_bytes=1 << 20):
+        import torch.distributed as dist
+        self._L = L = _lib.load()
+        vp, i32, i64 = C.c_void_p, C.c_int, C.c_longlong
+        L.ft_host_comm_create.restype = i32
+        L.ft_host_comm_create.argtypes = [C.POINTER(vp), i32, i32, vp, vp, C.c_size_t, C.c_size_t]
+        L.ft_host_comm_destroy.argtypes = [vp]
+        L.ft_host_comm_registered.restype = vp
+        L.ft_host_comm_registered.argtypes = [vp]
+        L.ft_host_comm_error.restype = C.c_uint
+        L.ft_host_comm_error.argtypes = [vp]
+        L.ft_host_comm_allreduce.restype = i64
+        L.ft_host_comm_allreduce.argtypes = [vp, vp, vp, i64, i32, i32, i32, i32, C.POINTER(i32), i32, i32, i64, i32,
+                                             C.c_double, i32, C.c_ulonglong, i32, i32]
+        self.rank, self.size = dist.get_rank(group), dist.get_world_size(group)
+        world = self.size
+
+        def _allgather(_ctx, send, recv, nbytes):
+            try:
+                src = (C.c_ubyte * nbytes).from_address(send)
+                t = torch.frombuffer(src, dtype=torch.uint8).clone()
+                if "nccl" in dist.get_backend(group):
+                    t = t.cuda()
+                out = [torch.empty_like(t) for _ in range(world)]
+                dist.all_gather(out, t, group=group)
+                flat = torch.cat(out).cpu().contiguous()
+                C.memmove(recv, flat.data_ptr(), nbytes * world)
+                return 0
+            except Exception as e:
+                import sys
+                print(f"[flextree] host bootstrap allgather failed: {e!r}", file=sys.stderr)
+                return 1
+
+        self._cb = _AG_FN(_allgather)
+        self._h = vp()
+        rc = L.ft_host_comm_create(C.byref(self._h), self.rank, world, C.cast(self._cb, vp), None, window_bytes, ll_bytes)
+        if rc:
+            raise RuntimeError(f"ft_host_comm_create failed ({rc}): {L.ft_last_error().decode()}")
+        self.window_bytes = window_bytes
+
+    def close(self):
+        if getattr(self, "_h", None) and self._h.value:
+            self._L.ft_host_comm_destroy(self._h)
+            self._h = C.c_void_p()
+
+    def registered(self, count, dtype):
+        """numpy view of this rank's registered (zero-copy) region."""
+        ptr = self._L.ft_host_comm_registered(self._h)
+        nbytes = count * np.dtype(dtype).itemsize
+        return np.frombuffer((C.c_char * nbytes).from_address(ptr), dtype=dtype, count=count)
+
+    def error(self):
+        return int(self._L.ft_host_comm_error(self._h))
+
+    def _call(self, send_ptr, recv_ptr, count, dcode, iocode, op, algo, widths, ctas, tile_bytes, mode, scale, lonely, phases,
+              timeout_s):
+        widths = list(widths) if widths is not None else [self.size - lonely]
+        w = (C.c_int * len(widths))(*widths)
+        rc = self._L.ft_host_comm_allreduce(
+            self._h, send_ptr, recv_ptr, count, dcode, iocode, K.OPS[op] if isinstance(op, str) else op,
+            K.ALGOS[algo] if isinstance(algo, str) else algo, w, len(widths), ctas, tile_bytes, mode,
+            1.0 if scale is None else float(scale), 0 if scale is None else 1, int(timeout_s * 1e9), lonely, phases)
+        if rc:
+            raise RuntimeError(f"host allreduce failed: code {rc}")
+
+    @staticmethod
+    def _as_numpy(x):
+        if isinstance(x, torch.Tensor):
+            if x.dtype == torch.bfloat16:
+                return x.view(torch.int16).numpy().view(np.uint16), K.BFLOAT16
+            a = x.numpy()
+            return a, K.NUMPY_DTYPE[a.dtype]
+        return x, K.NUMPY_DTYPE[x.dtype]
+
+    def allreduce(self, x, out=None, op="sum", algo="stages", widths=None, ctas=2, tile_bytes=16384, scale=None,
+                  wire=None, registered=False, lonely=0, timeout_s=30.0):
+        a, code = self._as_numpy(x)
+        o, _ = self._as_numpy(out) if out is not None else (a, code)
+        dcode = code if wire is None else wire
+        self._call(a.ctypes.data, o.ctypes.data, a.size, dcode, code, op, algo, widths, ctas, tile_bytes,
+                   K.MODE_REGISTERED if registered else K.MODE_STAGING, scale, lonely, 0, timeout_s)
+        return out if out is not None else x
+
+    def reduce_scatter(self, x, out, op="sum", widths=None, ctas=2, tile_bytes=16384):
+        a, code = self._as_numpy(x)
+        o, _ = self._as_numpy(out)
+        self._call(a.ctypes.data, o.ctypes.data, a.size, code, code, op, "stages", widths, ctas, tile_bytes,
+                   K.MODE_STAGING, None, 0, 1, 30.0)
+        return out
+
+    def all_gather(self, x, out, widths=None, ctas=2, tile_bytes=16384):
+        a, code = self._as_numpy(x)
+        o, _ = self._as_numpy(out)
+        self._call(a.ctypes.data, o.ctypes.data, o.size, code, code, "sum", "stages", widths, ctas, tile_bytes,
+                   K.MODE_STAGING, None, 0, 2, 30.0)
+        return out

@@ -1,0 +1,203 @@
+// Multi-process CPU communicator: the same algorithm templates as the GPU kernels, one process per rank,
+// windows / flag pads / LL buffers in POSIX shared memory that every rank maps. This is the CPU data
+// plane across processes - what the reference is (an MPI_Allreduce over point-to-point messages between
+// CPU processes, allreduce_over_mpi/mpi_mod.hpp:1167-1221) without needing an MPI library: the bootstrap is
+// the same byte all-gather callback the GPU communicator uses (torch.distributed/gloo in the tests).
+#include <errno.h>
+#include <fcntl.h>
+#include <stdio.h>
+#include <stdlib.h>
+#include <string.h>
+#include <sys/mman.h>
+#include <sys/stat.h>
+#include <sys/time.h>
+#include <unistd.h>
+
+#include <string>
+#include <vector>
+
+#include "../../include/flextree.h"
+#include "../core/dispatch.h"
+#include "../core/staged_core.h"
+#include "../planner/cost_model.h"
+
+namespace ft {
+void set_last_error(const std::string& s);
+bool host_run_group(int group, int dtype, int io_dtype, int op, bool vec, const StagedArgs* a, int algo);
+}  // namespace ft
+using namespace ft;
+
+struct ft_host_comm {
+  int rank = 0, nranks = 1;
+  ft_allgather_fn ag = nullptr;
+  void* ctx = nullptr;
+  size_t win_bytes = 0, ll_bytes = 0, seg_bytes = 0, total_bytes = 0;
+  std::vector<char*> maps;       // whole shared mapping of every rank
+  std::vector<char*> win_table;  // window segment base of every rank
+  CommDev cd;
+  uint64_t epoch = 0;
+  unsigned done = 0, err = 0;
+  bool allgather(const void* s, void* r, size_t n) const {
+    if (nranks == 1) { memcpy(r, s, n); return true; }
+    return ag && ag(ctx, s, r, n) == 0;
+  }
+};
+
+static std::string shm_name(unsigned long long token, int rank) {
+  char buf[96];
+  snprintf(buf, sizeof buf, "/flextree.%llx.%d", token, rank);
+  return buf;
+}
+
+extern "C" {
+
+ft_result_t ft_host_comm_create(ft_host_comm** out, int rank, int nranks, ft_allgather_fn ag, void* ctx,
+                                size_t window_bytes, size_t ll_bytes) {
+  if (!out || nranks < 1 || nranks > FT_MAX_RANKS || rank < 0 || rank >= nranks || (nranks > 1 && !ag)) {
+    set_last_error("ft_host_comm_create: bad arguments");
+    return FT_ERR_INVALID;
+  }
+  auto* c = new ft_host_comm;
+  c->rank = rank;
+  c->nranks = nranks;
+  c->ag = ag;
+  c->ctx = ctx;
+  c->win_bytes = ((window_bytes ? window_bytes : (size_t)(4 << 20)) + 4095) & ~(size_t)4095;
+  c->ll_bytes = ((ll_bytes ? ll_bytes : (size_t)(1 << 20)) + 4095) & ~(size_t)4095;
+  c->seg_bytes = 3 * c->win_bytes + 4096;  // [parity 0 | parity 1 | registered]
+  const size_t pad_off = c->seg_bytes, ll_off = pad_off + ((FT_PAD_BYTES + 4095) & ~(size_t)4095);
+  c->total_bytes = ll_off + 2 * c->ll_bytes + 4096;
+
+  unsigned long long tok = 0;
+  if (rank == 0) {
+    timeval tv;
+    gettimeofday(&tv, nullptr);
+    tok = ((unsigned long long)getpid() << 32) ^ ((unsigned long long)tv.tv_sec << 20) ^ (unsigned long long)tv.tv_usec;
+  }
+  std::vector<unsigned long long> toks((size_t)nranks);
+  if (!c->allgather(&tok, toks.data(), sizeof tok)) { set_last_error("bootstrap allgather failed"); delete c; return FT_ERR_INTERNAL; }
+  tok = toks[0];
+
+  // create + size + zero my segment
+  const std::string mine = shm_name(tok, rank);
+  int fd = shm_open(mine.c_str(), O_CREAT | O_EXCL | O_RDWR, 0600);
+  char ok = fd >= 0 && ftruncate(fd, (off_t)c->total_bytes) == 0;
+  std::vector<char> oks((size_t)nranks);
+  c->allgather(&ok, oks.data(), 1);  // also the "everybody has created its segment" barrier
+  for (char o : oks) ok = ok && o;
+  if (!ok) {
+    if (fd >= 0) { close(fd); shm_unlink(mine.c_str()); }
+    set_last_error(std::string("shm_open/ftruncate failed: ") + strerror(errno));
+    delete c;
+    return FT_ERR_NOMEM;
+  }
+  c->maps.assign((size_t)nranks, nullptr);
+  ok = 1;
+  for (int p = 0; p < nranks; ++p) {
+    int pfd = p == rank ? fd : shm_open(shm_name(tok, p).c_str(), O_RDWR, 0600);
+    void* m = pfd >= 0 ? mmap(nullptr, c->total_bytes, PROT_READ | PROT_WRITE, MAP_SHARED, pfd, 0) : MAP_FAILED;
+    if (pfd >= 0 && p != rank) close(pfd);
+    if (m == MAP_FAILED) { ok = 0; break; }
+    c->maps[(size_t)p] = (char*)m;
+  }
+  close(fd);
+  c->allgather(&ok, oks.data(), 1);  // everybody has mapped everything: names can go
+  shm_unlink(mine.c_str());
+  for (char o : oks) ok = ok && o;
+  if (!ok) { set_last_error("mapping a peer's shared segment failed"); delete c; return FT_ERR_NOMEM; }
+
+  memset(&c->cd, 0, sizeof c->cd);
+  c->cd.rank = rank;
+  c->cd.nranks = nranks;
+  c->win_table.resize((size_t)nranks);
+  for (int p = 0; p < nranks; ++p) {
+    c->win_table[(size_t)p] = c->maps[(size_t)p];
+    c->cd.pad[p] = (uint64_t*)(c->maps[(size_t)p] + pad_off);
+    c->cd.ll[p] = c->maps[(size_t)p] + ll_off;
+  }
+  c->cd.epoch = &c->epoch;
+  c->cd.done = &c->done;
+  c->cd.err = &c->err;
+  c->cd.ll_bytes = c->ll_bytes;
+  c->cd.trace = nullptr;
+  *out = c;
+  return FT_SUCCESS;
+}
+
+ft_result_t ft_host_comm_destroy(ft_host_comm* c) {
+  if (!c) return FT_SUCCESS;
+  char x = 0;
+  std::vector<char> all((size_t)c->nranks);
+  c->allgather(&x, all.data(), 1);  // nobody unmaps while a peer may still read
+  for (char* m : c->maps)
+    if (m) munmap(m, c->total_bytes);
+  delete c;
+  return FT_SUCCESS;
+}
+
+int ft_host_comm_rank(const ft_host_comm* c) { return c->rank; }
+int ft_host_comm_size(const ft_host_comm* c) { return c->nranks; }
+unsigned ft_host_comm_error(const ft_host_comm* c) { return c->err; }
+void* ft_host_comm_registered(ft_host_comm* c) { return c->win_table[(size_t)c->rank] + 2 * c->win_bytes; }
+size_t ft_host_comm_window_bytes(const ft_host_comm* c) { return c->win_bytes; }
+
+// One collective for this process's rank. Same argument meaning as ft_host_allreduce (host_world.cc).
+long long ft_host_comm_allreduce(ft_host_comm* c, const void* send, void* recv, long long count, int dtype, int io_dtype,
+                                 int op, int algo, const int* widths, int nstages, int ctas, long long tile_bytes,
+                                 int mode, double scale, int apply_scale, unsigned long long timeout_ns, int lonely,
+                                 int phases) {
+  StagedArgs a;
+  memset(&a, 0, sizeof a);
+  const int N = c->nranks;
+  if (send == FT_IN_PLACE || !send) send = recv;
+  if (N == 1) {
+    if (send != recv) memcpy(recv, send, (size_t)count * (size_t)dtype_size(io_dtype));
+    return 0;
+  }
+  if (algo == ALGO_RING || algo == ALGO_NVLS || algo == ALGO_ONESHOT) {
+    int flat = N;
+    if (!make_plan(&flat, 1, &a.plan)) return -1;
+    lonely = 0;
+  } else if (!make_plan(widths, nstages, &a.plan)) {
+    return -1;
+  }
+  if (lonely < 0 || a.plan.nranks + lonely != N) return -2;
+  if (lonely > 0 && (algo != ALGO_STAGED || mode != MODE_STAGING)) return -8;
+  if (phases != PHASES_ALLREDUCE && (algo != ALGO_STAGED || lonely > 0 || mode != MODE_STAGING || count % N)) return -10;
+  if (dtype == DT_FP8_BLOCK && (algo != ALGO_STAGED || lonely > 0 || mode != MODE_STAGING)) return -9;
+  const int es = dtype_size(dtype), ios = dtype_size(io_dtype);
+  if (!es || !ios) return -3;
+  // every rank must take the same code path: alignment is agreed on collectively
+  char vec = ((uintptr_t)send % 16 == 0) && ((uintptr_t)recv % 16 == 0);
+  if (phases != PHASES_ALLREDUCE && ((count / N) * es) % 16) vec = 0;
+  std::vector<char> vs((size_t)N);
+  if (!c->allgather(&vec, vs.data(), 1)) return -11;
+  for (char v : vs) vec = vec && v;
+  a.lonely = lonely;
+  a.phases = phases;
+  a.lay = make_layout(count, a.plan.nranks, es, tile_bytes, vec != 0);
+  a.scale_plane_off = ((long long)a.lay.block * a.plan.nranks * es + 255) & ~255LL;
+  if ((size_t)(a.scale_plane_off + (a.lay.block * a.plan.nranks) / 16 + 16) > c->win_bytes) return -4;
+  if (algo == ALGO_ONESHOT) {
+    size_t region = (c->ll_bytes / (size_t)N) & ~(size_t)15;
+    if ((size_t)((count * es + 7) / 8) * 16 > region) return -5;
+  }
+  if (ctas < 1 || ctas > FT_MAX_CTAS) return -6;
+  a.nlocal = 1;
+  a.ctas = ctas;
+  a.mode = mode;
+  a.apply_scale = apply_scale;
+  a.scale = scale;
+  a.win_off0 = mode == MODE_REGISTERED ? 2 * (long long)c->win_bytes : 0;
+  a.win_stride = mode == MODE_REGISTERED ? 0 : (long long)c->win_bytes;
+  a.timeout_ns = timeout_ns;
+  a.rc[0].comm = &c->cd;
+  a.rc[0].send = send;
+  a.rc[0].recv = recv;
+  a.rc[0].win = c->win_table.data();
+  a.rc[0].mc = nullptr;
+  if (!host_run_group(dtype_group(dtype), dtype, io_dtype, op, vec != 0, &a, algo)) return -7;
+  return c->err ? (long long)c->err : 0;
+}
+
+}  // extern "C"

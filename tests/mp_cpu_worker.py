@@ -1,0 +1,102 @@
+"""CPU multi-process worker (torch.distributed gloo): the algorithm templates across real processes with
+shared-memory windows, checked against gloo's all_reduce. Launched by tests/test_multiprocess_cpu.py."""
+import os
+import sys
+
+import numpy as np
+import torch
+import torch.distributed as dist
+
+sys.path.insert(0, os.path.dirname(os.path.dirname(os.path.abspath(__file__))))
+import flextree as ft  # noqa: E402
+
+
+def main():
+    dist.init_process_group("gloo")
+    rank, world = dist.get_rank(), dist.get_world_size()
+    comm = ft.HostCommunicator()
+    assert comm.rank == rank and comm.size == world
+    g = torch.Generator().manual_seed(7 + rank)
+
+    def ref_sum(t, op=dist.ReduceOp.SUM):
+        r = t.clone()
+        dist.all_reduce(r, op=op)
+        return r
+
+    # every factorization of the world size, a few sizes, in place / out of place
+    for widths in ft.enumerate_widths(world):
+        for count in (1, 7, 1000, 20001):
+            x = torch.randn(count, generator=g)
+            ref = ref_sum(x.double()).float()
+            out = torch.zeros(count)
+            comm.allreduce(x, out=out, widths=widths, ctas=3, tile_bytes=1024)
+            assert torch.allclose(out, ref, rtol=1e-5, atol=1e-5), (widths, count)
+            y = x.clone()
+            comm.allreduce(y, widths=widths, ctas=2, tile_bytes=4096)
+            assert torch.equal(y, out)
+            chk = y.clone()
+            dist.broadcast(chk, 0)
+            assert torch.equal(chk, y), "ranks differ"
+    # other algorithms
+    for algo in ("oneshot", "ring", "nvls"):
+        x = torch.randn(3000, generator=g)
+        ref = ref_sum(x.double()).float()
+        comm.allreduce(x, algo=algo, ctas=2, tile_bytes=2048)
+        assert torch.allclose(x, ref, rtol=1e-5, atol=1e-5), algo
+    # dtypes / ops
+    xi = torch.randint(-1000, 1000, (5000,), generator=g, dtype=torch.int32)
+    ref = ref_sum(xi, dist.ReduceOp.MAX)
+    comm.allreduce(xi, op="max")
+    assert torch.equal(xi, ref)
+    xb = torch.randint(0, 255, (777,), generator=g, dtype=torch.uint8)
+    ref = ref_sum(xb, dist.ReduceOp.BAND)
+    comm.allreduce(xb, op="band")
+    assert torch.equal(xb, ref)
+    # fused average, bf16 wire for fp32 data, fp8 block-scaled wire
+    x = torch.randn(4096, generator=g)
+    ref = ref_sum(x.double()).float() / world
+    y = x.clone()
+    comm.allreduce(y, scale=1.0 / world)
+    assert torch.allclose(y, ref, rtol=1e-5, atol=1e-6)
+    y = x.clone()
+    comm.allreduce(y, scale=1.0 / world, wire=ft.BFLOAT16)
+    assert torch.allclose(y, ref, rtol=3e-2, atol=3e-2)
+    y = x.clone()
+    comm.allreduce(y, scale=1.0 / world, wire=ft.FP8_BLOCK)
+    assert (y - ref).abs().max() < 0.35
+    # registered (zero-copy) region, repeated
+    view = comm.registered(2048, np.float32)
+    for it in range(3):
+        src = torch.randn(2048, generator=g)
+        ref = ref_sum(src.double()).float()
+        view[:] = src.numpy()
+        comm.allreduce(view, registered=True, ctas=2, tile_bytes=1024)
+        assert np.allclose(view, ref.numpy(), rtol=1e-5, atol=1e-5)
+    # the halves
+    per = 257
+    x = torch.randn(per * world, generator=g)
+    mine = torch.zeros(per)
+    comm.reduce_scatter(x, mine)
+    full = ref_sum(x.double()).float()
+    assert torch.allclose(mine, full[rank * per:(rank + 1) * per], rtol=1e-5, atol=1e-5)
+    gathered = torch.zeros(per * world)
+    comm.all_gather(mine, gathered)
+    assert torch.allclose(gathered, full, rtol=1e-5, atol=1e-5)
+    # lonely ranks (tree smaller than the world)
+    if world >= 3:
+        tree = {3: [2], 4: [3], 5: [2, 2], 6: [5], 7: [2, 3], 8: [2, 3]}[world]
+        lonely = world - int(np.prod(tree))
+        x = torch.randn(999, generator=g)
+        ref = ref_sum(x.double()).float()
+        comm.allreduce(x, widths=tree, lonely=lonely)
+        assert torch.allclose(x, ref, rtol=1e-5, atol=1e-5)
+    assert comm.error() == 0
+    dist.barrier()
+    comm.close()
+    if rank == 0:
+        print("MP_CPU_WORKER_OK", flush=True)
+    dist.destroy_process_group()
+
+
+if __name__ == "__main__":
+    main()
