@@ -19,6 +19,9 @@ $CXX $FLAGS '-DGIT_REPO_VERSION="reference"' '-DGIT_REPO_DATE="unknown"' '-DGIT_
   -I"$HERE/mpi_shim" -I"$HERE/glog_shim" \
   "$OUT/src/allreduce_over_mpi/benchmark.cpp" "$HERE/mpi_shim/mpi_shim.cc" -o "$OUT/bin/allreduce_over_mpi" -lpthread
 $CXX -std=c++17 -O2 "$HERE/mpi_shim/ftmpirun.cc" -o "$OUT/bin/ftmpirun"
+# oracle driver: the reference header, unmodified, on caller-supplied data (tests/test_reference_oracle.py)
+$CXX $FLAGS -I"$HERE/mpi_shim" -I"$HERE/glog_shim" -I"$OUT/src/allreduce_over_mpi" \
+  "$HERE/ref_oracle.cc" "$HERE/mpi_shim/mpi_shim.cc" -o "$OUT/bin/ref_oracle" -lpthread
 # the offline planner of the reference (cost_model/main.cpp), unmodified
 $CXX -std=c++14 -O0 -w "$OUT/src/cost_model/main.cpp" -o "$OUT/bin/cost_model" || echo "cost_model build failed (non-fatal)" >&2
 echo "reference built in $OUT/bin"

@@ -1,4 +1,5 @@
 // extern "C" surface of the planner (declared in include/flextree.h). Pure CPU.
+#include <stdio.h>
 #include <stdlib.h>
 #include <string.h>
 
@@ -32,6 +33,11 @@ extern "C" {
 
 const char* ft_last_error(void) { return g_last_error.c_str(); }
 const char* ft_version_string(void) { return FT_VERSION_STRING; }
+// Probe that the library is the one in use (parity: FT_enabled(), mpi_mod.hpp:8-12).
+int ft_enabled(void) {
+  fputs("FlexTree enabled", stdout);
+  return 0;
+}
 
 uint64_t ft_count_factorizations(uint64_t n) { return count_factorizations(n); }
 

@@ -51,6 +51,7 @@ typedef enum { FT_ALGO_AUTO = 0, FT_ALGO_ONESHOT = 1, FT_ALGO_STAGES = 2, FT_ALG
 
 const char* ft_last_error(void);      /* thread-local description of the last failure */
 const char* ft_version_string(void);  /* "flextree-b200 x.y (git describe, date)" */
+int ft_enabled(void);                 /* prints "FlexTree enabled", returns 0 (FT_enabled(), mpi_mod.hpp:8-12) */
 
 /* ------------------------------------------------------------------------------------------------
  * Planner (pure CPU, no CUDA needed)

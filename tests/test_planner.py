@@ -200,3 +200,13 @@ def test_link_model_json_roundtrip(tmp_path):
     assert d["alpha_sync_us"] == 3.5 and d["beta_p2p_GBps"] == 650.0 and d["has_nvls"] is True
     with pytest.raises(ValueError):
         ft.LinkModel(str(tmp_path / "missing.json"))
+
+
+def test_legacy_enumerator_getwidth2_sets():
+    """The reference's older enumerator (getWidth2, cost_model/GetWidth.h:51-227) yields the same SET, sorted:
+    `getWidth2(8)` = 1*8, 2*2*2, 2*4, 4*2, 8*1 and `getWidth2(12)` = sorted(getWidth(12))."""
+    assert sorted(fmt(ft.enumerate_widths(8, True))) == sorted(["1*8", "2*2*2", "2*4", "4*2", "8*1"])
+    assert sorted(map(tuple, ft.enumerate_widths(8, True))) == [(1, 8), (2, 2, 2), (2, 4), (4, 2), (8, 1)]
+    assert len(ft.enumerate_widths(12, True)) == 9
+    # no 9-stage limit here (getWidth2 caps the depth at 9): 2^12 has a 12-stage tree
+    assert [2] * 12 in ft.enumerate_widths(4096)
