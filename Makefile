@@ -73,9 +73,9 @@ fdtest:
 	$(B)/fd_channel_test 8
 # compute-sanitizer on the single-GPU emulation (one tool per invocation, see B200_PROFILING.md)
 memcheck:
-	compute-sanitizer --tool memcheck python bench/ncu_target.py
+	compute-sanitizer --tool memcheck python bench/sanitize_target.py
 racecheck:
-	compute-sanitizer --tool racecheck python bench/ncu_target.py
+	compute-sanitizer --tool racecheck python bench/sanitize_target.py
 
 clean:
 	rm -rf $(B) $(LIBDIR)/*.so

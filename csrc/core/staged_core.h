@@ -432,41 +432,49 @@ struct StagedCta {
   // In-switch reduction of my block of tile t: one multimem.ld_reduce pulls and sums the N copies,
   // one multimem.st broadcasts the result into every rank's window.
   template <int UNR> FT_DEV void nvls_reduce_tile(int t) {
-    const Layout& L = a.lay;
-    long long start, n = tile_valid(r, t, &start);
+    long long start;
+    const long long n = tile_valid(r, t, &start);
     if (n <= 0) return;
     const long long nvec = (n + VE - 1) / VE;
     const int nth = be.nthr(), tid = be.tid();
-    for (long long q0 = 0; q0 < nvec; q0 += (long long)nth * UNR) {
-      PackT v[UNR];
-      bool ok[UNR];
+    const long long step = (long long)nth * UNR;
+    const long long base = woff + start * (long long)sizeof(T);
+    // Software pipeline: the next batch of multimem.ld_reduce is issued before the current batch is
+    // broadcast, so the inbound (reduced data) and outbound (multimem.st) directions of the links overlap
+    // inside one thread instead of alternating.
+    PackT cur[UNR], nxt[UNR];
+    auto load = [&](PackT* v, long long q0) {
 #pragma unroll
       for (int u = 0; u < UNR; ++u) {
-        long long q = q0 + (long long)u * nth + tid;
-        ok[u] = q < nvec;
-        if (ok[u]) v[u] = be.template mc_ld_reduce<T, Op, VE>(rc, woff + (start + q * VE) * (long long)sizeof(T), a.plan.nranks);
+        const long long q = q0 + (long long)u * nth + tid;
+        if (q < nvec) v[u] = be.template mc_ld_reduce<T, Op, VE>(rc, base + q * (long long)sizeof(PackT), a.plan.nranks);
       }
-      if constexpr (EL::is_float) {
-        if (a.apply_scale) {  // the switch returned the final sum: scale it once, before the broadcast
+    };
+    load(cur, 0);
+    for (long long q0 = 0; q0 < nvec; q0 += step) {
+      const bool more = q0 + step < nvec;
+      if (more) load(nxt, q0 + step);
 #pragma unroll
-          for (int u = 0; u < UNR; ++u) {
-            if (!ok[u]) continue;
+      for (int u = 0; u < UNR; ++u) {
+        const long long q = q0 + (long long)u * nth + tid;
+        if (q >= nvec) continue;
+        if constexpr (EL::is_float) {
+          if (a.apply_scale) {  // the switch returned the final sum: scale it once, before the broadcast
             A acc[VE];
 #pragma unroll
-            for (int i = 0; i < VE; ++i) acc[i] = EL::up(v[u].e[i]);
+            for (int i = 0; i < VE; ++i) acc[i] = EL::up(cur[u].e[i]);
             scale_acc(acc);
 #pragma unroll
-            for (int i = 0; i < VE; ++i) v[u].e[i] = EL::down(acc[i]);
+            for (int i = 0; i < VE; ++i) cur[u].e[i] = EL::down(acc[i]);
           }
         }
+        be.template mc_st<T, VE>(rc, base + q * (long long)sizeof(PackT), cur[u], a.plan.nranks);
       }
+      if (more) {
 #pragma unroll
-      for (int u = 0; u < UNR; ++u) {
-        long long q = q0 + (long long)u * nth + tid;
-        if (ok[u]) be.template mc_st<T, VE>(rc, woff + (start + q * VE) * (long long)sizeof(T), v[u], a.plan.nranks);
+        for (int u = 0; u < UNR; ++u) cur[u] = nxt[u];
       }
     }
-    (void)L;
   }
 
   // Local copy of every block of tile t from my window to the user buffer through the epilogue.
@@ -543,6 +551,29 @@ struct StagedCta {
   // call's tag, so there is no separate barrier: latency is one NVLink store hop.
   // (No counterpart in the reference, which has no latency-optimised path.)
   static constexpr int LE = 8 / (int)sizeof(T) > 0 ? 8 / (int)sizeof(T) : 1;  // elements per line
+  // my payload of LL line i in wire format
+  FT_DEV Pack<T, LE> ll_own(long long e0, int nv) const {
+    const IO* x = (const IO*)rc.send;
+    Pack<T, LE> own;
+    if (VE > 1 && nv == LE) {
+      Pack<IO, LE> raw;
+      BE::template ld<(int)sizeof(Pack<IO, LE>)>(&raw, x + e0, false);
+#pragma unroll
+      for (int q = 0; q < LE; ++q) {
+        if constexpr (kRawIO) own.e[q] = raw.e[q];
+        else own.e[q] = EL::down((A)EU::up(raw.e[q]));
+      }
+    } else {
+      for (int q = 0; q < LE; ++q) {
+        IO t0;
+        if (q < nv) BE::template ld<(int)sizeof(IO)>(&t0, x + e0 + q, false);
+        else BE::template ld<(int)sizeof(IO)>(&t0, x + e0, false);
+        if constexpr (kRawIO) own.e[q] = t0;
+        else own.e[q] = EL::down((A)EU::up(t0));
+      }
+    }
+    return own;
+  }
   FT_DEV void run_oneshot() {
     scale_out_ = true;
     const int N = a.plan.nranks, G = a.ctas;
@@ -551,40 +582,30 @@ struct StagedCta {
     const uint32_t tag = (uint32_t)(E >> FT_EPOCH_SHIFT);  // epoch + 1, never 0 for 2^32 calls
     const size_t region = (cd.ll_bytes / (size_t)N) & ~(size_t)15;
     const size_t par_off = ((E >> FT_EPOCH_SHIFT) & 1) ? cd.ll_bytes : 0;
-    const IO* x = (const IO*)rc.send;
     IO* y = (IO*)rc.recv;
     const long long stride = (long long)G * be.nthr();
-    for (long long i = (long long)cta * be.nthr() + be.tid(); i < nlines; i += stride) {
+    const long long first_line = (long long)cta * be.nthr() + be.tid();
+    // pass 1: push ALL of my lines to every peer before polling anything, so a thread that owns several lines
+    // pays one NVLink round trip in total instead of one per line
+    for (long long i = first_line; i < nlines; i += stride) {
       const long long e0 = i * LE;
       const int nv = (count - e0) < LE ? (int)(count - e0) : LE;
-      // own payload in wire format
-      Pack<T, LE> own;
-      if (VE > 1 && nv == LE) {
-        Pack<IO, LE> raw;
-        BE::template ld<(int)sizeof(Pack<IO, LE>)>(&raw, x + e0, false);
-#pragma unroll
-        for (int q = 0; q < LE; ++q) {
-          if constexpr (kRawIO) own.e[q] = raw.e[q];
-          else own.e[q] = EL::down((A)EU::up(raw.e[q]));
-        }
-      } else {
-        for (int q = 0; q < LE; ++q) {
-          IO t0;
-          if (q < nv) BE::template ld<(int)sizeof(IO)>(&t0, x + e0 + q, false);
-          else BE::template ld<(int)sizeof(IO)>(&t0, x + e0, false);
-          if constexpr (kRawIO) own.e[q] = t0;
-          else own.e[q] = EL::down((A)EU::up(t0));
-        }
-      }
+      const Pack<T, LE> own = ll_own(e0, nv);
       uint32_t d[2] = {0, 0};
       memcpy(d, &own, sizeof(own) < 8 ? sizeof(own) : 8);
       for (int p = 0; p < N; ++p) {
         if (p == r) continue;
         be.ll_st(cd.ll[p] + par_off + (size_t)r * region + (size_t)i * 16, d[0], d[1], tag);
       }
+    }
+    // pass 2: poll the N-1 copies of each line, reduce in ascending rank order (identical on every rank)
+    for (long long i = first_line; i < nlines; i += stride) {
+      const long long e0 = i * LE;
+      const int nv = (count - e0) < LE ? (int)(count - e0) : LE;
+      const Pack<T, LE> own = ll_own(e0, nv);
       A acc[LE] = {};
       bool first = true;
-      for (int q = 0; q < N; ++q) {  // ascending rank order, identical on every rank
+      for (int q = 0; q < N; ++q) {
         Pack<T, LE> in;
         if (q == r) {
           in = own;

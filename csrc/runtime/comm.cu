@@ -305,7 +305,7 @@ Shape pick_shape(const ft_comm* c, int algo, int mode, bool tma, size_t msg_byte
   if (algo == ALGO_ONESHOT) {
     long long lines = ((long long)msg_bytes + 7) / 8;  // one LL line (8 payload bytes) per thread
     ctas = (int)((lines + s.threads - 1) / s.threads);
-    if (ctas > 32) ctas = 32;
+    if (ctas > 64) ctas = 64;
     tile = kMinTile;
   } else if (algo == ALGO_NVLS) {
     // multimem.ld_reduce/st saturate the switch path from very few SMs (8 CTAs reach 796 GB/s busbw at
