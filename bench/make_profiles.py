@@ -25,7 +25,7 @@ def sweep_table(n, fname, note=""):
         return
     shutil.copy(os.path.join(G, fname), os.path.join(P, "raw", fname))
     sizes = sorted({r["bytes"] for r in rows if "bytes" in r})
-    out = [f"# Allreduce sweep, {n} x B200, fp32 SUM, in place on symmetric buffers", "",
+    out = [f"# Allreduce sweep, {str(n).split('_')[0]} x B200, {'bf16' if 'bf16' in str(n) else 'fp32'} SUM, in place on symmetric buffers", "",
            "Device time (CUDA events around back-to-back calls, MAX over ranks / reps); `busbw = bytes/t * 2(N-1)/N`.",
            f"Source: `bench/sweep.py` under torchrun, raw lines in `profiles/raw/{fname}`. {note}", "",
            "| bytes | NCCL us | NCCL busbw | flextree auto us | algo | busbw GB/s | model est us | speed-up vs NCCL |",
@@ -111,6 +111,7 @@ def ncu_summary(rep, out_name, title):
 def main():
     os.makedirs(os.path.join(P, "raw"), exist_ok=True)
     sweep_table(8, "sweep_n8.jsonl", "TMA-staged P2P tiles on; NVLS available.")
+    sweep_table("8_bf16", "sweep_n8_bf16.jsonl", "bf16 (multimem.ld_reduce with fp32 accumulation in the switch).")
     sweep_table(4, "sweep_n4.jsonl", "(taken before the AG source-rotation fix: flat `stages 4` improved afterwards)")
     sweep_table(2, "sweep_n2_tma.jsonl", "TMA-staged P2P tiles on.")
     tune_table(8, "tunes_n8.jsonl", "register-staged P2P + NVLS")

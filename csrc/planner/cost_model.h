@@ -62,7 +62,7 @@ struct LinkModel {
   double beta_p2p_1peer_GBps = 615.0;  // ... from a single peer
   int fanin_knee = 7;
   double beta_nvls_GBps = 539.0;  // link rate of multimem ld_reduce/st: bytes = (1 + 1/N) * S
-  double beta_ll_GBps = 167.0;    // LL: rate at which the N-1 peer copies are pushed/polled ...
+  double beta_ll_GBps = 400.0;    // LL: rate at which the N-1 peer copies are pushed/polled (two-pass kernel) ...
   double beta_ll_self_GBps = 2000.0;  // ... plus a per-message term independent of N (negligible in the fit)
   double gamma_hbm_GBps = 6000.0; // local HBM copy/reduce traffic rate
   double half_bw_bytes = 4.0e6;   // per-stage bytes at which a P2P stage reaches half its peak rate

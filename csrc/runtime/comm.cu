@@ -317,7 +317,7 @@ Shape pick_shape(const ft_comm* c, int algo, int mode, bool tma, size_t msg_byte
     ctas = (int)(want < 2 ? 2 : (want > nvls_max ? nvls_max : want));
     if (ctas > max_ctas) ctas = max_ctas;
     tile = (block_bytes + ctas - 1) / ctas;
-    const long long kNvlsMaxTile = env_ll("FT_NVLS_MAX_TILE_BYTES", mode == MODE_REGISTERED ? (2 << 20) : (512 << 10));
+    const long long kNvlsMaxTile = env_ll("FT_NVLS_MAX_TILE_BYTES", mode == MODE_REGISTERED ? (4 << 20) : (512 << 10));
     if (tile > kNvlsMaxTile) tile = kNvlsMaxTile;
     if (tile < 4096) tile = 4096;
   } else {
