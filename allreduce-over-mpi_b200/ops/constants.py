@@ -21,7 +21,16 @@ NUMPY_DTYPE = {
 }
 
 
+_TORCH_TABLE = None
+
+
 def torch_dtype_code(dt):
+    global _TORCH_TABLE
+    if _TORCH_TABLE is not None:
+        try:
+            return _TORCH_TABLE[dt]
+        except KeyError:
+            raise TypeError(f"flextree: unsupported dtype {dt}")
     import torch
     table = {torch.uint8: UINT8, torch.int8: INT8, torch.int16: INT16, torch.int32: INT32,
              torch.int64: INT64, torch.float32: FLOAT, torch.float64: DOUBLE, torch.bool: BOOL,
@@ -29,6 +38,7 @@ def torch_dtype_code(dt):
     for name, code in (("uint16", UINT16), ("uint32", UINT32), ("uint64", UINT64)):
         if hasattr(torch, name):
             table[getattr(torch, name)] = code
+    _TORCH_TABLE = table
     if dt not in table:
         raise TypeError(f"flextree: unsupported dtype {dt}")
     return table[dt]

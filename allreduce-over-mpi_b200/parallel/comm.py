@@ -252,10 +252,11 @@ class Communicator:
         dt = K.torch_dtype_code(tensor.dtype)
         wt = self._wire_code(dt, wire_dtype)
         opc = K.OPS[op] if isinstance(op, str) else int(op)
-        with torch.cuda.device(self.device):
-            rc = self._L.ft_allreduce_ex(C.c_void_p(tensor.data_ptr()), C.c_void_p(out.data_ptr()), tensor.numel(),
-                                         dt, wt, opc, float(scale), self._h, self._stream(stream))
-        _check(self._L, rc, "ft_allreduce")
+        # (the native call selects the communicator's device itself; no torch device context on the hot path)
+        rc = self._L.ft_allreduce_ex(tensor.data_ptr(), out.data_ptr(), tensor.numel(),
+                                     dt, wt, opc, float(scale), self._h, self._stream(stream))
+        if rc:
+            _check(self._L, rc, "ft_allreduce")
         return out
 
     def allreduce_multi(self, tensors, op="sum", outs=None, scale=1.0, wire_dtype=None, stream=None):
@@ -269,10 +270,10 @@ class Communicator:
         opc = K.OPS[op] if isinstance(op, str) else int(op)
         s = (C.c_void_p * n)(*[t.data_ptr() for t in tensors])
         r = (C.c_void_p * n)(*[t.data_ptr() for t in outs])
-        with torch.cuda.device(self.device):
-            rc = self._L.ft_allreduce_multi(s, r, tensors[0].numel(), dt, wt, opc, float(scale), self._h,
-                                            self._stream(stream))
-        _check(self._L, rc, "ft_allreduce_multi")
+        rc = self._L.ft_allreduce_multi(s, r, tensors[0].numel(), dt, wt, opc, float(scale), self._h,
+                                        self._stream(stream))
+        if rc:
+            _check(self._L, rc, "ft_allreduce_multi")
         return outs
 
     # ---- the halves ------------------------------------------------------------------------------------------------

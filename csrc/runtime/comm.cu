@@ -71,7 +71,33 @@ struct LocalGroup {
 
 }  // namespace
 
+// Resolved launch of one message shape. Everything do_allreduce derives from (count, dtypes, op, scale, buffer
+// kind, policy) is kept so that the steady state of a training loop costs one lookup + one kernel launch on
+// the host ("communicator: plan cache keyed by (bytes, dtype, op)"; the reference instead rebuilds
+// its schedule tables and request arrays on every call, mpi_mod.hpp:964-972).
+struct PlanKey {
+  size_t count, uoff;
+  double scale;
+  int io, wire, op, phases, useg;
+  bool vec, in_place;
+  unsigned long long gen;
+  bool operator==(const PlanKey& o) const {
+    return count == o.count && uoff == o.uoff && scale == o.scale && io == o.io && wire == o.wire && op == o.op &&
+           phases == o.phases && useg == o.useg && vec == o.vec && in_place == o.in_place && gen == o.gen;
+  }
+};
+struct PlanEntry {
+  PlanKey key;
+  StagedArgs args;  // rc[] is filled per call
+  int launch_algo, threads, mode;
+  ft_call_info_t info;
+  unsigned long long last_use;
+};
+
 struct ft_comm {
+  std::vector<PlanEntry> plans;          // small LRU
+  unsigned long long policy_gen = 1;     // bumped by every setter / (re)allocation: invalidates the cache
+  unsigned long long use_clock = 0;
   CommKind kind = COMM_PROCESS;
   int rank = 0, nranks = 1, device = 0;
   int nlocal = 1;  // logical ranks served by this object (N for COMM_EMULATED)
@@ -210,6 +236,8 @@ void destroy_segments(std::vector<Segment>* v) {
 
 ft_result_t grow_window(ft_comm* c, size_t need_per_parity) {
   if (need_per_parity <= c->window_bytes && !c->win.empty()) return FT_SUCCESS;
+  c->policy_gen++;
+  if (c->group) for (auto* m : c->group->members) if (m) m->policy_gen++;
   size_t nb = c->window_bytes;
   while (nb < need_per_parity) nb *= 2;
   nb = (nb + 4095) & ~(size_t)4095;
@@ -377,14 +405,17 @@ ft_result_t do_allreduce(ft_comm* c, const void* const* send, void* const* recv,
     return FT_ERR_UNSUPPORTED;
   }
   if (count == 0) return FT_SUCCESS;
-  FT_CHECK_RT(cudaSetDevice(c->device));
+  {
+    int cur = -1;
+    if (cudaGetDevice(&cur) != cudaSuccess || cur != c->device) FT_CHECK_RT(cudaSetDevice(c->device));
+  }
   const int es = dtype_size(wire_dtype), ios = dtype_size(io_dtype);
   const bool is_float = dtype_is_float(wire_dtype);
   const bool apply_scale = is_float && scale != 1.0;
   const size_t msg_bytes = count * (size_t)es;
 
-  std::vector<const void*> s((size_t)L);
-  std::vector<void*> r((size_t)L);
+  const void* s[FT_MAX_LOCAL];
+  void* r[FT_MAX_LOCAL];
   bool vec = true, in_place = true;
   for (int l = 0; l < L; ++l) {
     r[(size_t)l] = recv[l];
@@ -427,6 +458,38 @@ ft_result_t do_allreduce(ft_comm* c, const void* const* send, void* const* recv,
       if (find_user_seg(c, l, r[(size_t)l], count * (size_t)ios, &o2) != useg || o2 != uoff) useg = -1;
     }
     if (useg >= 0 && uoff % 16 == 0 && env_int("FT_REGISTERED", 1)) mode = MODE_REGISTERED;
+    if (mode != MODE_REGISTERED) { useg = -1; uoff = 0; }
+  }
+
+  // ---- plan cache: a message shape seen before under the same policy is one lookup + one launch ----------
+  PlanKey key{count, uoff, scale, io_dtype, wire_dtype, op, phases, useg, vec, in_place, c->policy_gen};
+  for (PlanEntry& e : c->plans) {
+    if (!(e.key == key)) continue;
+    StagedArgs a2 = e.args;
+    for (int l = 0; l < L; ++l) {
+      RankCall& rc = a2.rc[l];
+      rc.comm = c->d_comm + l;
+      rc.send = s[l];
+      rc.recv = r[l];
+      const Segment* seg = nullptr;
+      if (e.info.algo != ALGO_ONESHOT) seg = e.mode == MODE_REGISTERED ? &c->user[(size_t)useg].seg[(size_t)l] : &c->win[(size_t)l];
+      rc.win = seg ? seg->d_table : nullptr;
+      rc.mc = seg ? seg->mc_base : nullptr;
+    }
+    LaunchCtx ctx;
+    ctx.args = &a2;
+    ctx.algo = e.launch_algo;
+    ctx.threads = e.threads;
+    ctx.cooperative = c->kind == COMM_EMULATED && N > 1;
+    ctx.stream = stream;
+    if (!cuda_launch(wire_dtype, io_dtype, op, vec, &ctx) || !ctx.supported || ctx.err != cudaSuccess) {
+      set_last_error(std::string("kernel launch: ") + cudaGetErrorString(ctx.err));
+      (void)cudaGetLastError();
+      return FT_ERR_CUDA;
+    }
+    e.last_use = ++c->use_clock;
+    c->last = e.info;
+    return FT_SUCCESS;
   }
 
   // ---- algorithm + widths --------------------------------------------------------------------------------
@@ -588,8 +651,8 @@ ft_result_t do_allreduce(ft_comm* c, const void* const* send, void* const* recv,
   for (int l = 0; l < L; ++l) {
     RankCall& rc = a.rc[l];
     rc.comm = c->d_comm + l;
-    rc.send = s[(size_t)l];
-    rc.recv = r[(size_t)l];
+    rc.send = s[l];
+    rc.recv = r[l];
     const Segment* seg = nullptr;
     if (algo != ALGO_ONESHOT) seg = mode == MODE_REGISTERED ? &c->user[(size_t)useg].seg[(size_t)l] : &c->win[(size_t)l];
     rc.win = seg ? seg->d_table : nullptr;
@@ -626,6 +689,26 @@ ft_result_t do_allreduce(ft_comm* c, const void* const* send, void* const* recv,
   li.est_us = est;
   FT_LOG(2, "rank %d allreduce count=%zu %s/%s algo=%s widths=%s ctas=%d tile=%lld mode=%d", c->rank, count,
          dtype_name(wire_dtype), op_name(op), algo_name(algo), to_string(widths).c_str(), sh.ctas, li.tile_bytes, mode);
+  if (mode == (useg >= 0 ? MODE_REGISTERED : MODE_STAGING) && key.gen == c->policy_gen) {
+    // remember the resolved launch (the generation is unchanged, i.e. nothing was (re)allocated on the way)
+    PlanEntry e;
+    e.key = key;
+    e.args = a;
+    e.launch_algo = ctx.algo;
+    e.threads = sh.threads;
+    e.mode = mode;
+    e.info = li;
+    e.last_use = ++c->use_clock;
+    const size_t kMaxPlans = 32;
+    if (c->plans.size() < kMaxPlans) {
+      c->plans.push_back(e);
+    } else {
+      size_t victim = 0;
+      for (size_t i = 1; i < c->plans.size(); ++i)
+        if (c->plans[i].last_use < c->plans[victim].last_use) victim = i;
+      c->plans[victim] = e;
+    }
+  }
   return check_device_error(c);
 }
 
@@ -806,6 +889,7 @@ ft_result_t ft_comm_clear_error(ft_comm_t* c) {
 }
 
 ft_result_t ft_comm_set_widths(ft_comm_t* c, const int* widths, int nstages) {
+  c->policy_gen++;
   if (!widths || nstages <= 0) {
     c->widths_override.clear();
     c->lonely_override = 0;
@@ -831,17 +915,20 @@ ft_result_t ft_comm_set_widths(ft_comm_t* c, const int* widths, int nstages) {
   return FT_SUCCESS;
 }
 ft_result_t ft_comm_set_algo(ft_comm_t* c, ft_algo_t algo) {
+  c->policy_gen++;
   if ((int)algo < 0 || (int)algo > ALGO_RING) return FT_ERR_INVALID;
   c->algo_override = (int)algo;
   return FT_SUCCESS;
 }
 ft_result_t ft_comm_set_link_model(ft_comm_t* c, const ft_link_model_t* m) {
+  c->policy_gen++;
   const bool probed = c->model.has_nvls;  // what the hardware/bootstrap allows
   c->model = m ? m->m : LinkModel();
   c->model.has_nvls = probed;
   return FT_SUCCESS;
 }
 ft_result_t ft_comm_set_launch(ft_comm_t* c, int ctas, int threads, long long tile_bytes) {
+  c->policy_gen++;
   if (ctas < 0 || ctas > FT_MAX_CTAS || threads < 0 || threads > FT_MAX_THREADS || (threads % 32) || tile_bytes < 0)
     return FT_ERR_INVALID;
   c->ctas_override = ctas;
@@ -881,12 +968,14 @@ int ft_comm_trace_read(ft_comm_t* c, int local, unsigned long long* ns, int cap)
 }
 
 ft_result_t ft_comm_set_max_ctas(ft_comm_t* c, int max_ctas) {
+  c->policy_gen++;
   if (max_ctas < 0) return FT_ERR_INVALID;
   c->max_ctas = max_ctas;
   return FT_SUCCESS;
 }
 
 ft_result_t ft_comm_set_tma(ft_comm_t* c, int on) {
+  c->policy_gen++;
   c->tma_override = on < 0 ? -1 : (on ? 1 : 0);
   return FT_SUCCESS;
 }
@@ -898,6 +987,7 @@ ft_result_t ft_comm_reserve(ft_comm_t* c, size_t bytes) {
 }
 
 ft_result_t ft_symm_alloc(ft_comm_t* c, size_t bytes, void** ptr) {
+  c->policy_gen++;
   if (!ptr || bytes == 0) return FT_ERR_INVALID;
   size_t padded = ((bytes + 4095) & ~(size_t)4095) + 4096;  // tail pad: full-vector accesses stay inside
   std::string err;
@@ -942,6 +1032,7 @@ ft_result_t ft_symm_alloc(ft_comm_t* c, size_t bytes, void** ptr) {
 }
 
 ft_result_t ft_symm_free(ft_comm_t* c, void* ptr) {
+  c->policy_gen++;
   for (size_t i = 0; i < c->user.size(); ++i) {
     Segment& s = c->user[i].seg[0];
     if (s.kind != SEG_NONE && s.base[(size_t)s.self] == (char*)ptr) {
@@ -980,10 +1071,9 @@ ft_result_t ft_allreduce_ex(const void* sendbuf, void* recvbuf, size_t count, ft
 ft_result_t ft_allreduce_multi(const void* const* sendbufs, void* const* recvbufs, size_t count, ft_dtype_t dtype,
                                ft_dtype_t wire_dtype, ft_op_t op, double scale, ft_comm_t* comm, void* stream) {
   if (!comm || !recvbufs) return FT_ERR_INVALID;
-  std::vector<const void*> s((size_t)comm->nlocal, FT_IN_PLACE);
-  if (sendbufs)
-    for (int l = 0; l < comm->nlocal; ++l) s[(size_t)l] = sendbufs[l];
-  return do_allreduce(comm, s.data(), recvbufs, count, (int)dtype, (int)wire_dtype, (int)op, scale, (cudaStream_t)stream);
+  const void* s[FT_MAX_LOCAL];
+  for (int l = 0; l < comm->nlocal; ++l) s[l] = sendbufs ? sendbufs[l] : FT_IN_PLACE;
+  return do_allreduce(comm, s, recvbufs, count, (int)dtype, (int)wire_dtype, (int)op, scale, (cudaStream_t)stream);
 }
 
 // The two halves of the algorithm as collectives (reduce-scatter: recv = my block of the reduction;
