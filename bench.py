@@ -29,6 +29,9 @@ import time
 
 ROOT = os.path.dirname(os.path.abspath(__file__))
 sys.path.insert(0, ROOT)
+# NCCL (bootstrap only) prints its version banner on stdout when NCCL_DEBUG=VERSION: keep stdout to the one JSON line
+if os.environ.get("NCCL_DEBUG", "VERSION").upper() == "VERSION":
+    os.environ["NCCL_DEBUG"] = "WARN"
 
 METRIC = "allreduce_aggregate_busbw"
 EMULATED_RANKS = 8

@@ -4,7 +4,7 @@
   python -m torch.distributed.run --nproc-per-node N --master-addr 127.0.0.1 bench/sweep.py \
       [--min-bytes 1024] [--max-bytes 1073741824] [--dtype fp32|bf16] [--out gpurun_out/sweep.jsonl] [--all-widths]
 
-Each (size, implementation) pair: 5 warm-up calls, then `reps` back-to-back calls between two CUDA
+Each (size, implementation) pair: 10 warm-up calls, then `reps` back-to-back calls between two CUDA
 events (same method as nccl-tests), time = MAX over ranks / reps. flextree runs in place on symmetric
 (registered) buffers and, with --staging, also on private buffers; NCCL runs dist.all_reduce in place.
 busbw = bytes/t * 2(N-1)/N. One JSON object per line.
@@ -53,7 +53,7 @@ def main():
 
     def timed(fn, nbytes):
         reps = 50 if nbytes <= (1 << 20) else (20 if nbytes <= (64 << 20) else 8)
-        for _ in range(5):
+        for _ in range(10):
             fn()
         torch.cuda.synchronize()
         dist.barrier()
