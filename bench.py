@@ -181,6 +181,11 @@ def main():
     args = parse()
     if args.impl == "reference":
         return run_reference(args)
+    # stdout must carry exactly one JSON line: native libraries (NCCL's version banner) also write to fd 1,
+    # so everything except that line is sent to stderr
+    real_stdout = os.dup(1)
+    os.dup2(2, 1)
+    sys.stdout = os.fdopen(os.dup(2), "w")
 
     import torch
     import torch.distributed as dist
@@ -373,7 +378,7 @@ def main():
         }
         if sweep:
             out["sweep"] = sweep
-        print(json.dumps(out))
+        os.write(real_stdout, (json.dumps(out) + "\n").encode())
     comm.close()
     if not emulated:
         dist.destroy_process_group()
