@@ -112,8 +112,8 @@ def main():
     os.makedirs(os.path.join(P, "raw"), exist_ok=True)
     sweep_table(8, "sweep_n8.jsonl", "TMA-staged P2P tiles on; NVLS available.")
     sweep_table("8_bf16", "sweep_n8_bf16.jsonl", "bf16 (multimem.ld_reduce with fp32 accumulation in the switch).")
-    sweep_table(4, "sweep_n4.jsonl", "(taken before the AG source-rotation fix: flat `stages 4` improved afterwards)")
-    sweep_table(2, "sweep_n2_tma.jsonl", "TMA-staged P2P tiles on.")
+    sweep_table(4, "sweep_n4.jsonl", "TMA-staged P2P tiles on; NVLS available.")
+    sweep_table(2, "sweep_n2.jsonl", "TMA-staged P2P tiles on; `sta` columns are private (non-symmetric) buffers.")
     tune_table(8, "tunes_n8.jsonl", "register-staged P2P + NVLS")
     tune_table(2, "tunes_n2_tma.jsonl", "TMA-staged P2P + NVLS")
     tune_table(2, "tunes_n2.jsonl", "register-staged P2P + NVLS")
@@ -122,7 +122,8 @@ def main():
     tune_table(2, "tune_n2.jsonl", "256 MiB, threads x CTAs x tile, register-staged P2P")
     ncu_summary("prof_staged.ncu-rep", "ncu_staged_tma_emulated.md",
                 "TMA-staged flat allreduce, 8 logical ranks on 1 B200, 64 MiB fp32 (ft_allreduce_kernel<float,float,OpSum,4,5>)")
-    for f in ("ddp_n8.jsonl", "bench8.json", "bench1.json", "bench_ref1.json", "launches.csv"):
+    for f in ("ddp_n8.jsonl", "bench8.json", "bench4.json", "bench2.json", "bench1.json", "bench_ref1.json", "bench_ref2.json",
+              "bench_ref4.json", "bench_ref8.json", "launches.csv"):
         if os.path.exists(os.path.join(G, f)):
             shutil.copy(os.path.join(G, f), os.path.join(P, "raw", f))
 
