@@ -72,3 +72,21 @@ def test_bench_reference_arm_json():
     assert d["impl"] == "reference"
     if "unavailable" not in d:
         assert d["n_gpus"] == 2 and d["value"] > 0 and d["config"]["ranks"] == 2 and d["check"].startswith("CHECK 0")
+
+
+def test_public_header_is_c99_and_cxx11(tmp_path):
+    """include/flextree.h must stay usable from plain C (the reference's entry point is a C signature)."""
+    src = tmp_path / "hdr.c"
+    src.write_text('#define STANDALONE_TEST\n#include "flextree.h"\nint main(void) { ft_comm_options_t o; (void)o; return (int)FT_SUCCESS; }\n')
+    inc = os.path.join(ROOT, "include")
+    r = subprocess.run(["gcc", "-std=c99", "-Wall", "-Wextra", "-pedantic", "-Werror", f"-I{inc}", "-fsyntax-only", str(src)],
+                       capture_output=True, text=True)
+    assert r.returncode == 0, r.stderr
+    r = subprocess.run(["g++", "-std=c++11", "-Wall", "-Wextra", "-Werror", f"-I{inc}", "-fsyntax-only", "-x", "c++", str(src)],
+                       capture_output=True, text=True)
+    assert r.returncode == 0, r.stderr
+    cuda_inc = "/usr/local/cuda/include"
+    if os.path.isdir(cuda_inc):  # the C example compiles against the header
+        r = subprocess.run(["gcc", "-std=c99", f"-I{inc}", f"-I{cuda_inc}", "-fsyntax-only",
+                            os.path.join(ROOT, "examples", "c_local_allreduce.c")], capture_output=True, text=True)
+        assert r.returncode == 0, r.stderr
