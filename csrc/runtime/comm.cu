@@ -317,7 +317,7 @@ Shape pick_shape(const ft_comm* c, int algo, int mode, bool tma, size_t msg_byte
   if (max_ctas > FT_MAX_CTAS) max_ctas = FT_MAX_CTAS;
   if (c->kind == COMM_EMULATED) {
     // cooperative launch: nranks*ctas CTAs must be co-resident
-    int per_sm = s.threads <= 256 ? 2 : 1;
+    int per_sm = (s.threads <= 256 && !tma) ? 2 : 1;  // the TMA ring takes the whole shared memory of an SM
     max_ctas = c->sm_count * per_sm / nranks;
     if (max_ctas < 1) max_ctas = 1;
   }
@@ -451,7 +451,9 @@ ft_result_t do_allreduce(ft_comm* c, const void* const* send, void* const* recv,
   int mode = MODE_STAGING;
   int useg = -1;
   size_t uoff = 0;
-  if (in_place && io_dtype == wire_dtype && vec && N > 1) {
+  // Zero-copy needs whole 16-byte vectors: the in-place kernels store full vectors into the window, and a
+  // ragged tail would spill into whatever follows a sub-view of a symmetric tensor.
+  if (in_place && io_dtype == wire_dtype && vec && N > 1 && count % (size_t)(16 / ios) == 0) {
     useg = find_user_seg(c, 0, r[0], count * (size_t)ios, &uoff);
     for (int l = 1; l < L && useg >= 0; ++l) {
       size_t o2 = 0;
@@ -577,7 +579,8 @@ ft_result_t do_allreduce(ft_comm* c, const void* const* send, void* const* recv,
 
   // TMA-staged tiles: vector path and whole 16-byte vectors only (blocks are padded to 16 bytes, so every
   // bulk copy is aligned).
-  const bool tma = algo == ALGO_STAGED && lonely == 0 && vec && wire_dtype != DT_FP8_BLOCK && (count % (size_t)(16 / es) == 0) &&
+  const int want_threads = c->threads_override ? c->threads_override : env_int("FT_THREADS", 512);
+  const bool tma = algo == ALGO_STAGED && lonely == 0 && vec && wire_dtype != DT_FP8_BLOCK && want_threads >= 64 && (count % (size_t)(16 / es) == 0) &&
                    (c->threads_override == 0 || c->threads_override >= 64) &&
                    (c->tma_override >= 0 ? c->tma_override : env_int("FT_TMA", 1)) != 0;
   const int T = N - lonely;  // ranks in the tree = number of blocks

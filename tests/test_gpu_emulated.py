@@ -198,6 +198,30 @@ def test_registered_zero_copy_in_place(comms):
     c.set_algo("auto")
 
 
+def test_odd_prefix_of_symmetric_tensor_does_not_touch_the_rest(comms):
+    """A ragged view of a registered buffer must not take the zero-copy path (full-vector stores would spill
+    past the view)."""
+    n = 4
+    c = comms(n)
+    c.set_algo("stages")
+    bufs = c.symm_empty(4096, torch.float32)
+    for r in range(n):
+        bufs[r].fill_(float(r + 1))
+    views = [b[:1001] for b in bufs]
+    c.allreduce_multi(views)
+    torch.cuda.synchronize()
+    assert c.error() == 0 and c.last_call()["mode"] == "staging"
+    for r in range(n):
+        assert torch.all(bufs[r][:1001] == 10.0) and torch.all(bufs[r][1001:] == float(r + 1))
+    views = [b[:1024] for b in bufs]   # whole vectors: zero-copy
+    c.allreduce_multi(views)
+    torch.cuda.synchronize()
+    assert c.last_call()["mode"] == "registered"
+    for r in range(n):
+        assert torch.all(bufs[r][:1001] == 40.0) and torch.all(bufs[r][1024:] == float(r + 1))
+    c.set_algo("auto")
+
+
 def test_unaligned_views_use_scalar_path(comms):
     n, count = 4, 10001
     c = comms(n)
