@@ -167,6 +167,9 @@ __device__ __forceinline__ void ag_tile_tma_impl(Cta& c, const TmaRing& R, int k
   const int w = P.width[k], g = P.gap[k], gn = P.gap[k + 1], base = stage_base(P, c.r, k), nb = P.nranks / gn;
   const bool last = (k == 0);
   const int my_digit = (c.r - base) / g;
+  // Several logical ranks on ONE GPU (emulation): there are no links to balance, and walking the sources in the
+  // same order on every rank lets the readers of a block hit in L2 behind the first one.
+  const int rot = c.a.nlocal > 1 ? 0 : my_digit + 1;
   const bool self_needed = last && !(c.a.mode == MODE_REGISTERED && Cta::kRawIO);
   const int CH = kTmaMaxChunk;
   char* wr = c.rc.win[c.r] + c.woff;
@@ -181,7 +184,7 @@ __device__ __forceinline__ void ag_tile_tma_impl(Cta& c, const TmaRing& R, int k
       // Start from my right-hand neighbour in the group and go round: if every rank walked the sources in
       // the same order, all of them would pull from the same GPU at the same time (measured at N=4: flat AG
       // 852 us vs 640 us for the 2x2 plan at 256 MiB before this rotation).
-      const int p = base + ((my_digit + 1 + s_) % w) * g;
+      const int p = base + ((rot + s_) % w) * g;
       if (p == c.r && !self_needed) continue;
       long long start;
       const int n = c.tile_valid32((p % gn) + bi * gn, t, &start);
