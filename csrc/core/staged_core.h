@@ -783,19 +783,14 @@ struct StagedCta {
     be.finish(cd, a.ctas);
   }
 
-  template <int UNR_DUMMY = 0> FT_DEV void rs_dispatch(int k, int t) {
-    const int w = a.plan.width[k];
+  // Register-staged reduce-scatter tile: pick the (vectors per thread, peers per batch) shape so that ~8 remote
+  // 16-byte loads are in flight per thread whatever the stage width (more than that spills at 512 threads).
+  FT_DEV void rs_dispatch(int k, int t) {
     if constexpr (VE == 1) {
-      rs_tile<1, 4>(k, t);
+      rs_tile<1, 4>(k, t);  // scalar path (unaligned user buffers): correctness first
     } else {
-#if defined(FT_PROBE) && FT_PROBE == 1
-      rs_tile<4, 1>(k, t);
-#elif defined(FT_PROBE) && FT_PROBE == 2
-      rs_tile<2, 4>(k, t);
-#else
-      if (w == 2) rs_tile<4, 1>(k, t);   // one peer: more vectors per thread instead
+      if (a.plan.width[k] == 2) rs_tile<4, 1>(k, t);  // one peer: more vectors per thread instead
       else rs_tile<2, 4>(k, t);
-#endif
     }
   }
 

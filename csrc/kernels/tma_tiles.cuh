@@ -153,8 +153,6 @@ __device__ __forceinline__ void rs_tile_tma_impl(Cta& c, const TmaRing& R, int k
       }
     }
   }
-  // every thread advances the ring position by the same amount
-  if (warp == 0 && lane != 0) { /* `it` already advanced in the loop header */ }
   c.pipe_it = it;
 }
 
