@@ -30,6 +30,7 @@ def main():
     ap.add_argument("--all-widths", action="store_true")
     ap.add_argument("--staging", action="store_true")
     ap.add_argument("--factor", type=int, default=4)
+    ap.add_argument("--only-auto", action="store_true", help="measure NCCL and flextree auto only")
     ap.add_argument("--tma", type=int, default=-1, help="1/0 force TMA-staged P2P tiles on/off")
     ap.add_argument("--tune", action="store_true", help="scan CTAs x tile bytes at --max-bytes instead of sweeping sizes")
     ap.add_argument("--tune-sizes", default="", help="comma list of message bytes: scan CTAs x tile at each (small grid)")
@@ -80,6 +81,8 @@ def main():
         impls.append(("nvls", None))
     if args.all_widths:
         impls += [("stages", w) for w in ft.enumerate_widths(world) if w != [world]]
+    if args.only_auto:
+        impls = [("auto", None)]
 
     if args.tune:
         count = args.max // es
