@@ -516,32 +516,56 @@ struct StagedCta {
   FT_DEV void run_nvls() {
     const int G = a.ctas, nt = a.lay.ntiles;
     const int mine = cta < nt ? (nt - cta + G - 1) / G : 0;
-    constexpr int CU = (VE == 1) ? 1 : 4;
+    constexpr int CU = (VE == 1) ? 1 : 8;
+    constexpr int RU = (VE == 1) ? 1 : 8;
     if (a.mode == MODE_STAGING) {
-      for (int j = 0; j < mine; ++j) {
-        copy_in_all_tile<CU>(cta + j * G);
+      // Private buffers: three passes per tile (user -> window, in-switch reduce, window -> user). They are
+      // interleaved tile by tile and skewed by one tile, so that the HBM-bound copies of one CTA overlap the
+      // link-bound reduce of another and every flag wait sits behind a tile's worth of work (measured on
+      // 8 GPUs: phase-major order cost 1104 us per 256 MiB against 579 us for zero-copy buffers).
+      if (mine > 0) {
+        copy_in_all_tile<CU>(cta);
         be.sync();
-        signal_group(PH_IN, 0, E + j + 1);
+        signal_group(PH_IN, 0, E + 1);
       }
-    } else {
-      signal_group(PH_IN, 0, E + mine);
+      for (int j = 0; j < mine; ++j) {
+        if (j + 1 < mine) {
+          copy_in_all_tile<CU>(cta + (j + 1) * G);
+          be.sync();
+          signal_group(PH_IN, 0, E + j + 2);
+        }
+        wait_group(PH_IN, 0, E + j + 1);
+        nvls_reduce_tile<RU>(cta + j * G);
+        be.sync();
+        signal_group(PH_RS0, 0, E + j + 1);
+        if (j > 0) {
+          wait_group(PH_RS0, 0, E + j);
+          out_tile<CU>(cta + (j - 1) * G);
+        }
+      }
+      if (mine > 0) {
+        wait_group(PH_RS0, 0, E + mine);
+        out_tile<CU>(cta + (mine - 1) * G);
+      }
+      be.finish(cd, a.ctas);
+      return;
     }
+    // zero-copy (registered) buffers
+    signal_group(PH_IN, 0, E + mine);
     for (int j = 0; j < mine; ++j) {
       wait_group(PH_IN, 0, E + j + 1);
-      nvls_reduce_tile<(VE == 1) ? 1 : 8>(cta + j * G);
+      nvls_reduce_tile<RU>(cta + j * G);
       be.sync();
       signal_group(PH_RS0, 0, E + j + 1);
     }
-    const bool need_out = !(a.mode == MODE_REGISTERED && kRawIO);
+    const bool need_out = !kRawIO;
     for (int j = 0; j < mine; ++j) {
       wait_group(PH_RS0, 0, E + j + 1);
       if (need_out) out_tile<CU>(cta + j * G);
     }
-    if (a.mode == MODE_REGISTERED) {
-      be.sync();
-      signal_group(PH_END, 0, E + 1);
-      wait_group(PH_END, 0, E + 1);
-    }
+    be.sync();
+    signal_group(PH_END, 0, E + 1);
+    wait_group(PH_END, 0, E + 1);
     be.finish(cd, a.ctas);
   }
 

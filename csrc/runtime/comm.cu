@@ -159,7 +159,7 @@ void apply_options(ft_comm* c, const ft_comm_options_t* o) {
   ft_comm_options_default(&d);
   if (o) d = *o;
   c->window_bytes = d.window_bytes ? d.window_bytes : (size_t)env_ll("FT_WINDOW_BYTES", 64ll << 20);
-  c->ll_bytes = d.ll_bytes ? d.ll_bytes : (size_t)env_ll("FT_LL_BYTES", 8ll << 20);
+  c->ll_bytes = d.ll_bytes ? d.ll_bytes : (size_t)env_ll("FT_LL_BYTES", 32ll << 20);
   c->window_bytes = (c->window_bytes + 4095) & ~(size_t)4095;
   c->ll_bytes = (c->ll_bytes + 4095) & ~(size_t)4095;
   int mc = d.use_multicast;
@@ -339,15 +339,25 @@ Shape pick_shape(const ft_comm* c, int algo, int mode, bool tma, size_t msg_byte
     // multimem.ld_reduce/st saturate the switch path from very few SMs (8 CTAs reach 796 GB/s busbw at
     // 256 MiB on 8 GPUs) and every tile boundary costs two system fences with multicast stores in
     // flight: few CTAs, one big tile each (profiles/tune_n8.md).
-    // Private (staging) buffers add a local copy-in and copy-out pass that needs many more SMs.
-    const int nvls_max = mode == MODE_REGISTERED ? 8 : 64;
-    long long want = block_bytes / (64 << 10);
-    ctas = (int)(want < 2 ? 2 : (want > nvls_max ? nvls_max : want));
-    if (ctas > max_ctas) ctas = max_ctas;
-    tile = (block_bytes + ctas - 1) / ctas;
-    const long long kNvlsMaxTile = env_ll("FT_NVLS_MAX_TILE_BYTES", mode == MODE_REGISTERED ? (4 << 20) : (512 << 10));
-    if (tile > kNvlsMaxTile) tile = kNvlsMaxTile;
-    if (tile < 4096) tile = 4096;
+    if (mode == MODE_REGISTERED) {
+      long long want = block_bytes / (64 << 10);
+      ctas = (int)(want < 2 ? 2 : (want > 8 ? 8 : want));
+      if (ctas > max_ctas) ctas = max_ctas;
+      tile = (block_bytes + ctas - 1) / ctas;
+      const long long kNvlsMaxTile = env_ll("FT_NVLS_MAX_TILE_BYTES", 4 << 20);
+      if (tile > kNvlsMaxTile) tile = kNvlsMaxTile;
+      if (tile < 4096) tile = 4096;
+    } else {
+      // Private buffers add a local copy-in and copy-out pass (HBM-bound, needs many more SMs); the three
+      // passes are interleaved tile by tile, so every CTA should own several tiles.
+      long long want = block_bytes / (32 << 10);
+      ctas = (int)(want < 2 ? 2 : (want > 64 ? 64 : want));
+      if (ctas > max_ctas) ctas = max_ctas;
+      tile = block_bytes / ((long long)ctas * 4);
+      const long long kMaxT = env_ll("FT_NVLS_MAX_TILE_BYTES", 256 << 10);
+      if (tile > kMaxT) tile = kMaxT;
+      if (tile < (16 << 10)) tile = 16 << 10;
+    }
   } else {
     // P2P pull kernels: as many CTAs as there are minimum-size tiles, up to the whole GPU; then one tile per
     // CTA until the tile would exceed kMaxTile
