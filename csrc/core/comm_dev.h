@@ -86,7 +86,7 @@ struct StagedArgs {
   int lonely;   // ranks plan.nranks .. plan.nranks+lonely-1 are outside the tree (N = tree + lonely)
   long long scale_plane_off;  // fp8 block-scaled wire: byte offset of the scale plane inside the window
   int phases;   // 0 = allreduce, 1 = reduce-scatter only (recv gets my block), 2 = all-gather only (send is my block)
-  int reserved2_;
+  int nvls_reducers;  // NVLS with private buffers: CTAs per rank that only run the in-switch reduce (rest copy)
   RankCall rc[FT_MAX_LOCAL];
 };
 

@@ -512,6 +512,80 @@ struct StagedCta {
     }
   }
 
+  // NVLS with private (non-symmetric) user buffers. Three passes per tile - user -> window (HBM), in-switch
+  // reduce (NVLink), window -> user (HBM) - that must overlap to reach the link rate. CTAs are therefore split
+  // by ROLE: the last `nvls_reducers` CTAs of every rank only run multimem.ld_reduce/st, all the others only
+  // copy (a few tiles ahead in, then out as results arrive). Roles meet through per-TILE flags (slot =
+  // tile mod FT_MAX_CTAS, value grows with tile / FT_MAX_CTAS) that every rank also sends to itself.
+  // Measured on 8 GPUs before the split: 1104 us (phase-major) / 922 us (tile-major, one role) per 256 MiB,
+  // against 579 us for zero-copy buffers and 720 us for NCCL.
+  FT_DEV uint64_t tile_flag(int t) const { return E + (uint64_t)(t / FT_MAX_CTAS) + 1; }
+  FT_DEV void signal_all_tile(int phase, int t) {  // to every rank, myself included
+    const int N = a.plan.nranks, slot = t % FT_MAX_CTAS;
+    for (int p = be.tid(); p < N; p += be.nthr()) {
+      be.fence();
+      be.flag_st(cd.pad[p] + pad_slot(phase, slot, r), tile_flag(t));
+    }
+  }
+  FT_DEV void wait_all_tile(int phase, int t) {
+    const int N = a.plan.nranks, slot = t % FT_MAX_CTAS;
+    for (int p = be.tid(); p < N; p += be.nthr()) {
+      spin(cd.pad[r] + pad_slot(phase, slot, p), tile_flag(t), phase, p);
+      be.acquire(cd.pad[r] + pad_slot(phase, slot, p));
+    }
+    be.sync();
+  }
+  FT_DEV void run_nvls_private() {
+    const int G = a.ctas, nt = a.lay.ntiles;
+    constexpr int CU = (VE == 1) ? 1 : 8;
+    constexpr int RU = (VE == 1) ? 1 : 8;
+    const int Gr = a.nvls_reducers > 0 && a.nvls_reducers < G ? a.nvls_reducers : (G > 1 ? 1 : 0);
+    const int Gc = G - Gr;
+    if (Gr == 0) {  // a single CTA plays both roles, tile by tile
+      for (int t = 0; t < nt; ++t) {
+        copy_in_all_tile<CU>(t);
+        be.sync();
+        signal_all_tile(PH_IN, t);
+        wait_all_tile(PH_IN, t);
+        nvls_reduce_tile<RU>(t);
+        be.sync();
+        signal_all_tile(PH_RS0, t);
+        wait_all_tile(PH_RS0, t);
+        out_tile<CU>(t);
+        be.sync();
+      }
+    } else if (cta < Gc) {
+      // copy role: tiles cta, cta + Gc, ...; stay up to kAhead tiles ahead with the copy-in
+      const int mine = cta < nt ? (nt - cta + Gc - 1) / Gc : 0;
+      constexpr int kAhead = 2;
+      int jin = 0, jout = 0;
+      while (jout < mine) {
+        if (jin < mine && jin - jout < kAhead) {
+          const int t = cta + jin * Gc;
+          copy_in_all_tile<CU>(t);
+          be.sync();
+          signal_all_tile(PH_IN, t);
+          ++jin;
+        } else {
+          const int t = cta + jout * Gc;
+          wait_all_tile(PH_RS0, t);
+          out_tile<CU>(t);
+          ++jout;
+        }
+      }
+    } else {
+      // reduce role: tiles q, q + Gr, ...
+      const int q = cta - Gc;
+      for (int t = q; t < nt; t += Gr) {
+        wait_all_tile(PH_IN, t);
+        nvls_reduce_tile<RU>(t);
+        be.sync();
+        signal_all_tile(PH_RS0, t);
+      }
+    }
+    be.finish(cd, a.ctas);
+  }
+
   // NVLS allreduce. Plan must be the flat {N} plan (stage-0 group == everybody).
   FT_DEV void run_nvls() {
     const int G = a.ctas, nt = a.lay.ntiles;
@@ -519,35 +593,7 @@ struct StagedCta {
     constexpr int CU = (VE == 1) ? 1 : 8;
     constexpr int RU = (VE == 1) ? 1 : 8;
     if (a.mode == MODE_STAGING) {
-      // Private buffers: three passes per tile (user -> window, in-switch reduce, window -> user). They are
-      // interleaved tile by tile and skewed by one tile, so that the HBM-bound copies of one CTA overlap the
-      // link-bound reduce of another and every flag wait sits behind a tile's worth of work (measured on
-      // 8 GPUs: phase-major order cost 1104 us per 256 MiB against 579 us for zero-copy buffers).
-      if (mine > 0) {
-        copy_in_all_tile<CU>(cta);
-        be.sync();
-        signal_group(PH_IN, 0, E + 1);
-      }
-      for (int j = 0; j < mine; ++j) {
-        if (j + 1 < mine) {
-          copy_in_all_tile<CU>(cta + (j + 1) * G);
-          be.sync();
-          signal_group(PH_IN, 0, E + j + 2);
-        }
-        wait_group(PH_IN, 0, E + j + 1);
-        nvls_reduce_tile<RU>(cta + j * G);
-        be.sync();
-        signal_group(PH_RS0, 0, E + j + 1);
-        if (j > 0) {
-          wait_group(PH_RS0, 0, E + j);
-          out_tile<CU>(cta + (j - 1) * G);
-        }
-      }
-      if (mine > 0) {
-        wait_group(PH_RS0, 0, E + mine);
-        out_tile<CU>(cta + (mine - 1) * G);
-      }
-      be.finish(cd, a.ctas);
+      run_nvls_private();
       return;
     }
     // zero-copy (registered) buffers

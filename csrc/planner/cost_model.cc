@@ -147,7 +147,8 @@ double predict_us(const LinkModel& m, int algo, const Widths& widths, int n, dou
     }
     case ALGO_STAGED: {
       double t = m.alpha_launch_us;
-      if (!registered) t += S / (m.gamma_hbm_GBps * 1e3) * 2.0 / 8.0;  // copy-in mostly overlapped
+      // private buffers: an extra publish phase + local copies (measured: ~22 us + S / 4.5 TB/s)
+      if (!registered) t += 4.0 * hop(widths.empty() ? n : widths[0]) + S / (0.75 * m.gamma_hbm_GBps * 1e3);
       t += hop(widths.empty() ? n : widths[0]);  // input-ready hop
       double g = 1;
       for (int w : widths) {
@@ -164,7 +165,8 @@ double predict_us(const LinkModel& m, int algo, const Widths& widths, int n, dou
       if (!m.has_nvls) return 1e30;
       // three all-to-all flag hops (input ready, reduced, exit) + a constant for the multicast stores in flight
       double t = m.alpha_launch_us + 3.0 * hop(n) + m.alpha_nvls_us;
-      if (!registered) t += S / (m.gamma_hbm_GBps * 1e3) * 4.0 / 8.0;
+      // private buffers: copy-in and copy-out roles + two more flag hops per tile
+      if (!registered) t += 4.0 * hop(n) + 4.0 * S / (m.gamma_hbm_GBps * 1e3) * 0.25 + 10.0;
       // per-GPU link traffic (each direction): every rank's copy of all N blocks goes up to the switch once
       // (S, including the requester's own copy) plus its reduced block broadcast (S/N)  ->  (1 + 1/N) S,
       // against 2 (N-1)/N S for the P2P stages: NVLS loses at N = 2 and wins from N = 4 up.

@@ -299,6 +299,7 @@ int find_user_seg(const ft_comm* c, int l, const void* p, size_t bytes, size_t* 
 struct Shape {
   int ctas, threads;
   long long tile_bytes;
+  int nvls_reducers = 0;  // NVLS with private buffers: CTAs that only reduce (the others copy)
 };
 
 // Launch shape heuristics. Measured on 2xB200 (profiles/tune_n2.md): the pull kernels are bound by bytes
@@ -348,15 +349,21 @@ Shape pick_shape(const ft_comm* c, int algo, int mode, bool tma, size_t msg_byte
       if (tile > kNvlsMaxTile) tile = kNvlsMaxTile;
       if (tile < 4096) tile = 4096;
     } else {
-      // Private buffers add a local copy-in and copy-out pass (HBM-bound, needs many more SMs); the three
-      // passes are interleaved tile by tile, so every CTA should own several tiles.
-      long long want = block_bytes / (32 << 10);
-      ctas = (int)(want < 2 ? 2 : (want > 64 ? 64 : want));
-      if (ctas > max_ctas) ctas = max_ctas;
-      tile = block_bytes / ((long long)ctas * 4);
-      const long long kMaxT = env_ll("FT_NVLS_MAX_TILE_BYTES", 256 << 10);
-      if (tile > kMaxT) tile = kMaxT;
+      // Private buffers: role-split kernel (run_nvls_private). Up to 8 CTAs only reduce in the switch, the
+      // others copy user <-> window; tiles small enough that the pipeline fills quickly, large enough that the
+      // two fences per tile stay cheap.
+      tile = block_bytes / 64;
+      if (tile > (256 << 10)) tile = 256 << 10;
       if (tile < (16 << 10)) tile = 16 << 10;
+      tile = env_ll("FT_NVLS_MAX_TILE_BYTES", tile);
+      const long long ntiles = (block_bytes + tile - 1) / tile;
+      int gr = (int)(ntiles / 4);
+      gr = gr < 1 ? 1 : (gr > 8 ? 8 : gr);
+      int cap2 = max_ctas < 64 ? max_ctas : 64;
+      int gc = (int)(ntiles < (long long)(cap2 - gr) ? ntiles : (long long)(cap2 - gr));
+      if (gc < 1) gc = 1;
+      ctas = gr + gc;
+      s.nvls_reducers = gr;
     }
   } else {
     // P2P pull kernels: as many CTAs as there are minimum-size tiles, up to the whole GPU; then one tile per
@@ -370,6 +377,7 @@ Shape pick_shape(const ft_comm* c, int algo, int mode, bool tma, size_t msg_byte
   }
   ctas = c->ctas_override ? c->ctas_override : env_int("FT_CTAS", ctas);
   if (ctas < 1) ctas = 1;
+  if (s.nvls_reducers >= ctas) s.nvls_reducers = ctas > 1 ? (ctas >= 8 ? ctas / 4 : 1) : 0;
   if (ctas > FT_MAX_CTAS) ctas = FT_MAX_CTAS;
   if (c->kind == COMM_EMULATED && ctas > max_ctas) ctas = max_ctas;
   s.ctas = ctas;
@@ -598,6 +606,7 @@ ft_result_t do_allreduce(ft_comm* c, const void* const* send, void* const* recv,
   a.lay = make_layout((long long)count, T, es, sh.tile_bytes, vec);
   a.lonely = lonely;
   a.phases = phases;
+  a.nvls_reducers = sh.nvls_reducers;
   // flag values encode the tile ordinal in FT_EPOCH_SHIFT bits (ring: steps * tiles)
   {
     long long per_cta = (a.lay.ntiles + sh.ctas - 1) / sh.ctas;

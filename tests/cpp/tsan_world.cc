@@ -50,6 +50,8 @@ int main() {
   bad |= run(8, {2, 2, 2}, 2, 1, 6000, 2, 256);
   bad |= run(8, {8}, 2, 1, 6000, 3, 128);
   bad |= run(4, {4}, 3, 0, 3000, 2, 256);
+  bad |= run(4, {4}, 3, 0, 30000, 5, 256);
+  bad |= run(8, {8}, 3, 0, 20000, 8, 128);
   bad |= run(4, {4}, 3, 1, 3000, 2, 256);
   bad |= run(5, {1}, 4, 0, 3000, 2, 256);
   bad |= run(5, {1}, 4, 1, 3000, 2, 256);

@@ -401,6 +401,25 @@ def test_reduce_scatter_and_all_gather_halves(n, widths, per_rank):
         np.testing.assert_allclose(allr[0], ref[0], rtol=1e-5, atol=1e-5)
 
 
+@pytest.mark.parametrize("n,ctas", [(2, 1), (4, 2), (4, 5), (8, 8), (8, 3)])
+def test_nvls_private_buffers_role_split(n, ctas):
+    """NVLS with private buffers: copy CTAs and reduce CTAs meet through per-tile flags (incl. self flags)."""
+    w = HostWorld(n, window_bytes=1 << 20)
+    for count, tile in ((40000, 256), (1001, 64), (3, 64), (65536, 4096)):
+        xf = make_inputs(n, count, np.float32)
+        send = [aligned_copy(x) for x in xf]
+        recv = [aligned_empty(count, np.float32) for _ in range(n)]
+        for it in range(2):  # twice: per-tile flag slots are reused with the next epoch
+            assert w.allreduce(send, recv, algo="nvls", ctas=ctas, tile_bytes=tile, scale=0.5) == 0
+            acc = xf[0].copy()
+            for a in xf[1:]:
+                acc = acc + a
+            acc = acc * np.float32(0.5)
+            for r in range(n):
+                np.testing.assert_array_equal(recv[r], acc, err_msg=f"count {count} rank {r}")
+                np.testing.assert_array_equal(send[r], xf[r])
+
+
 def test_watchdog_fires_instead_of_hanging():
     """Fault injection: one rank never joins the collective. The others must report a timeout."""
     n = 4
