@@ -539,20 +539,37 @@ struct StagedCta {
     const int G = a.ctas, nt = a.lay.ntiles;
     constexpr int CU = (VE == 1) ? 1 : 8;
     constexpr int RU = (VE == 1) ? 1 : 8;
-    const int Gr = a.nvls_reducers > 0 && a.nvls_reducers < G ? a.nvls_reducers : (G > 1 ? 1 : 0);
+    const int Gr = a.nvls_reducers > 0 && a.nvls_reducers < G ? a.nvls_reducers : 0;
     const int Gc = G - Gr;
-    if (Gr == 0) {  // a single CTA plays both roles, tile by tile
-      for (int t = 0; t < nt; ++t) {
-        copy_in_all_tile<CU>(t);
+    if (Gr == 0) {
+      // Every CTA plays both roles on its own tiles (t = cta + j*G), skewed by one tile so that each flag wait
+      // sits behind a tile's worth of work. Best for mid-size messages (measured on 8 GPUs: 80 us at 16 MiB,
+      // 232 us at 64 MiB against 115 / 279 us for the role split, which wins from ~128 MiB up).
+      const int mine = cta < nt ? (nt - cta + G - 1) / G : 0;
+      if (mine > 0) {
+        copy_in_all_tile<CU>(cta);
         be.sync();
-        signal_all_tile(PH_IN, t);
+        signal_all_tile(PH_IN, cta);
+      }
+      for (int j = 0; j < mine; ++j) {
+        const int t = cta + j * G;
+        if (j + 1 < mine) {
+          copy_in_all_tile<CU>(t + G);
+          be.sync();
+          signal_all_tile(PH_IN, t + G);
+        }
         wait_all_tile(PH_IN, t);
         nvls_reduce_tile<RU>(t);
         be.sync();
         signal_all_tile(PH_RS0, t);
-        wait_all_tile(PH_RS0, t);
-        out_tile<CU>(t);
-        be.sync();
+        if (j > 0) {
+          wait_all_tile(PH_RS0, t - G);
+          out_tile<CU>(t - G);
+        }
+      }
+      if (mine > 0) {
+        wait_all_tile(PH_RS0, cta + (mine - 1) * G);
+        out_tile<CU>(cta + (mine - 1) * G);
       }
     } else if (cta < Gc) {
       // copy role: tiles cta, cta + Gc, ...; stay up to kAhead tiles ahead with the copy-in

@@ -175,7 +175,7 @@ long long ft_host_comm_allreduce(ft_host_comm* c, const void* send, void* recv, 
   for (char v : vs) vec = vec && v;
   a.lonely = lonely;
   a.phases = phases;
-  a.nvls_reducers = ctas >= 4 ? ctas / 4 : (ctas > 1 ? 1 : 0);
+  a.nvls_reducers = ctas >= 4 ? ctas / 4 : 0;  // small CTA counts exercise the one-role (skewed) variant
   a.lay = make_layout(count, a.plan.nranks, es, tile_bytes, vec != 0);
   a.scale_plane_off = ((long long)a.lay.block * a.plan.nranks * es + 255) & ~255LL;
   if ((size_t)(a.scale_plane_off + (a.lay.block * a.plan.nranks) / 16 + 16) > c->win_bytes) return -4;

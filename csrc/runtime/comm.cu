@@ -349,21 +349,32 @@ Shape pick_shape(const ft_comm* c, int algo, int mode, bool tma, size_t msg_byte
       if (tile > kNvlsMaxTile) tile = kNvlsMaxTile;
       if (tile < 4096) tile = 4096;
     } else {
-      // Private buffers: role-split kernel (run_nvls_private). Up to 8 CTAs only reduce in the switch, the
-      // others copy user <-> window; tiles small enough that the pipeline fills quickly, large enough that the
-      // two fences per tile stay cheap.
-      tile = block_bytes / 64;
-      if (tile > (256 << 10)) tile = 256 << 10;
-      if (tile < (16 << 10)) tile = 16 << 10;
-      tile = env_ll("FT_NVLS_MAX_TILE_BYTES", tile);
-      const long long ntiles = (block_bytes + tile - 1) / tile;
-      int gr = (int)(ntiles / 4);
-      gr = gr < 1 ? 1 : (gr > 8 ? 8 : gr);
-      int cap2 = max_ctas < 64 ? max_ctas : 64;
-      int gc = (int)(ntiles < (long long)(cap2 - gr) ? ntiles : (long long)(cap2 - gr));
-      if (gc < 1) gc = 1;
-      ctas = gr + gc;
-      s.nvls_reducers = gr;
+      // Private buffers (run_nvls_private): user <-> window copies around the in-switch reduce.
+      if ((long long)msg_bytes >= env_ll("FT_NVLS_SPLIT_BYTES", 128ll << 20)) {
+        // large: role split - up to 8 CTAs only reduce in the switch, the others copy; tiles small enough that
+        // the pipeline fills quickly, large enough that the two fences per tile stay cheap
+        tile = block_bytes / 64;
+        if (tile > (256 << 10)) tile = 256 << 10;
+        if (tile < (16 << 10)) tile = 16 << 10;
+        const long long ntiles = (block_bytes + tile - 1) / tile;
+        int gr = (int)(ntiles / 4);
+        gr = gr < 1 ? 1 : (gr > 8 ? 8 : gr);
+        int cap2 = max_ctas < 64 ? max_ctas : 64;
+        int gc = (int)(ntiles < (long long)(cap2 - gr) ? ntiles : (long long)(cap2 - gr));
+        if (gc < 1) gc = 1;
+        ctas = gr + gc;
+        s.nvls_reducers = gr;
+      } else {
+        // mid-size: every CTA does copy-in / reduce / copy-out on its own tiles, skewed by one tile; several
+        // tiles per CTA so that the passes of different CTAs overlap
+        long long want = block_bytes / (32 << 10);
+        ctas = (int)(want < 2 ? 2 : (want > 64 ? 64 : want));
+        if (ctas > max_ctas) ctas = max_ctas;
+        tile = block_bytes / ((long long)ctas * 4);
+        if (tile > (256 << 10)) tile = 256 << 10;
+        if (tile < (16 << 10)) tile = 16 << 10;
+        s.nvls_reducers = 0;
+      }
     }
   } else {
     // P2P pull kernels: as many CTAs as there are minimum-size tiles, up to the whole GPU; then one tile per
@@ -377,7 +388,7 @@ Shape pick_shape(const ft_comm* c, int algo, int mode, bool tma, size_t msg_byte
   }
   ctas = c->ctas_override ? c->ctas_override : env_int("FT_CTAS", ctas);
   if (ctas < 1) ctas = 1;
-  if (s.nvls_reducers >= ctas) s.nvls_reducers = ctas > 1 ? (ctas >= 8 ? ctas / 4 : 1) : 0;
+  if (s.nvls_reducers >= ctas) s.nvls_reducers = ctas >= 8 ? ctas / 4 : 0;
   if (ctas > FT_MAX_CTAS) ctas = FT_MAX_CTAS;
   if (c->kind == COMM_EMULATED && ctas > max_ctas) ctas = max_ctas;
   s.ctas = ctas;
