@@ -4,6 +4,7 @@
 
   python bench.py --gpus N --steps K --warmup W            (N>1: launched by torch.distributed.run)
   python bench.py --impl reference --gpus N ...            (the unmodified reference on the box CPU)
+  python bench.py --impl nccl --gpus N ...                 (dist.all_reduce in the same timing loop, N >= 2)
 
 A "step" is ONE allreduce of --bytes (default 256 MiB, > L2) in place on a symmetric buffer through
 the public API (flextree.Communicator.allreduce). The buffer is re-filled from a pristine copy between
@@ -258,8 +259,15 @@ def main():
         for b_, p_ in zip(bufs, pristine):
             b_.copy_(p_)
 
+    use_nccl = args.impl == "nccl"
+    if use_nccl and emulated:
+        os.write(real_stdout, (json.dumps({"impl": "nccl", "unavailable": "NCCL has nothing to do on one GPU"}) + "\n").encode())
+        return 0
+
     def step(stream=None):
-        if emulated:
+        if use_nccl:
+            dist.all_reduce(bufs[0])          # the library baseline: same buffers, same timing loop
+        elif emulated:
             comm.allreduce_multi(bufs, stream=stream)
         else:
             comm.allreduce(bufs[0], stream=stream)
@@ -312,7 +320,7 @@ def main():
     if not emulated:
         dist.all_reduce(total_ms, op=dist.ReduceOp.MAX)
     ms_per_step = total_ms.item() / args.steps
-    info = comm.last_call()
+    info = {"algo": "nccl (torch.distributed.all_reduce)"} if use_nccl else comm.last_call()
     bb = busbw(nbytes, ms_per_step / 1e3, ranks)
 
     # ---- end to end through the public API: pinned host -> device, allreduce, result back to host ---------
@@ -399,8 +407,8 @@ def main():
             "e2e": {"value": e2e_bb * n, "unit": "GB/s", "ms_per_step": e2e_ms.item(), "steps": e2e_steps,
                     "h2d_bytes_per_step": nbytes * nloc, "d2h_bytes_per_step": 11 * esize,
                     "api": "Communicator.allreduce on a symmetric tensor; input copied from pinned host memory each step"},
-            "gpu_launches": args.steps,
-            "impl": "flextree",
+            "gpu_launches": 0 if use_nccl else args.steps,
+            "impl": args.impl,
         }
         if sweep:
             out["sweep"] = sweep
