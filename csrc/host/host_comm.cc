@@ -183,6 +183,7 @@ long long ft_host_comm_allreduce(ft_host_comm* c, const void* send, void* recv, 
     size_t region = (c->ll_bytes / (size_t)N) & ~(size_t)15;
     if ((size_t)((count * es + 7) / 8) * 16 > region) return -5;
   }
+  if (algo == ALGO_NVLS && mode == MODE_STAGING && a.lay.ntiles > FT_MAX_CTAS) return -12;  // per-tile flag slots
   if (ctas < 1 || ctas > FT_MAX_CTAS) return -6;
   a.nlocal = 1;
   a.ctas = ctas;

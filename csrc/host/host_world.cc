@@ -129,6 +129,7 @@ long long ft_host_allreduce(void* h, const void* const* send, void* const* recv,
     size_t lines = (size_t)((count * es + 7) / 8);
     if (lines * 16 > region) return -5;
   }
+  if (algo == ALGO_NVLS && mode == MODE_STAGING && a.lay.ntiles > FT_MAX_CTAS) return -12;  // per-tile flag slots
   if (ctas < 1 || ctas > FT_MAX_CTAS) return -6;
   a.nlocal = w->n;
   a.ctas = ctas;

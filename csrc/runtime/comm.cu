@@ -628,7 +628,16 @@ ft_result_t do_allreduce(ft_comm* c, const void* const* send, void* const* recv,
       per_cta = (a.lay.ntiles + sh.ctas - 1) / sh.ctas;
     }
   }
-  if (sh.ctas > a.lay.ntiles && algo != ALGO_ONESHOT) sh.ctas = a.lay.ntiles;
+  // NVLS with private buffers signals per TILE (slot = tile mod FT_MAX_CTAS): keep every tile in its own slot so
+  // that two CTAs can never write one slot out of order.
+  while (algo == ALGO_NVLS && mode == MODE_STAGING && a.lay.ntiles > FT_MAX_CTAS) {
+    sh.tile_bytes *= 2;
+    a.lay = make_layout((long long)count, T, es, sh.tile_bytes, vec);
+  }
+  if (sh.ctas > a.lay.ntiles && algo != ALGO_ONESHOT) {
+    sh.ctas = a.lay.ntiles;
+    if (sh.nvls_reducers >= sh.ctas) sh.nvls_reducers = 0;
+  }
 
   // ---- memory --------------------------------------------------------------------------------------------
   if (algo == ALGO_ONESHOT) {
