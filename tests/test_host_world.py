@@ -405,7 +405,7 @@ def test_reduce_scatter_and_all_gather_halves(n, widths, per_rank):
 def test_nvls_private_buffers_role_split(n, ctas):
     """NVLS with private buffers: copy CTAs and reduce CTAs meet through per-tile flags (incl. self flags)."""
     w = HostWorld(n, window_bytes=1 << 20)
-    for count, tile in ((40000, 256), (1001, 64), (3, 64), (65536, 4096)):
+    for count, tile in ((40000, 1024), (1001, 64), (3, 64), (65536, 4096)):
         xf = make_inputs(n, count, np.float32)
         send = [aligned_copy(x) for x in xf]
         recv = [aligned_empty(count, np.float32) for _ in range(n)]
