@@ -41,6 +41,13 @@ $(B)/%.o: %.cc
 	@mkdir -p $(dir $@)
 	$(CXX) $(CXXFLAGS) -MMD -MP -c $< -o $@
 
+# the CPU data plane: -O3 so that the bulk-tile loops (csrc/host/cpu_backend.h) are vectorised (at -O2 gcc's
+# "very-cheap" cost model skips every loop that needs an epilogue); baseline x86-64 ISA only - the library
+# travels to other machines
+$(B)/csrc/host/host_run_g%.o: csrc/host/host_run_g%.cc
+	@mkdir -p $(dir $@)
+	$(CXX) $(CXXFLAGS) -O3 -MMD -MP -c $< -o $@
+
 $(B)/%.cu.o: %.cu
 	@mkdir -p $(dir $@)
 	$(NVCC) $(NVFLAGS) -MMD -MP -c $< -o $@

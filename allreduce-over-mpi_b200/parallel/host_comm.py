@@ -74,7 +74,7 @@ class HostCommunicator:
         w = (C.c_int * len(widths))(*widths)
         rc = self._L.ft_host_comm_allreduce(
             self._h, send_ptr, recv_ptr, count, dcode, iocode, K.OPS[op] if isinstance(op, str) else op,
-            K.ALGOS[algo] if isinstance(algo, str) else algo, w, len(widths), ctas, tile_bytes, mode,
+            K.HOST_ALGOS[algo] if isinstance(algo, str) else algo, w, len(widths), ctas, tile_bytes, mode,
             1.0 if scale is None else float(scale), 0 if scale is None else 1, int(timeout_s * 1e9), lonely, phases)
         if rc:
             raise RuntimeError(f"host allreduce failed: code {rc}")
@@ -88,8 +88,14 @@ class HostCommunicator:
             return a, K.NUMPY_DTYPE[a.dtype]
         return x, K.NUMPY_DTYPE[x.dtype]
 
-    def allreduce(self, x, out=None, op="sum", algo="stages", widths=None, ctas=2, tile_bytes=16384, scale=None,
+    def allreduce(self, x, out=None, op="sum", algo="stages_bulk", widths=None, ctas=1, tile_bytes=262144, scale=None,
                   wire=None, registered=False, lonely=0, timeout_s=30.0):
+        """In-place (or into ``out``) allreduce of a numpy array / CPU tensor.
+
+        ``algo="stages_bulk"`` (default) runs the staged algorithm with the CPU's bulk tiles
+        (csrc/host/cpu_backend.h; falls back to the per-vector text where they do not apply), ``"stages"`` the exact
+        text of the GPU kernels; ``ctas`` is the number of threads this rank uses. Defaults are the best measured
+        shape for MB-sized messages with one rank per core (bench/cpu_compare.py)."""
         a, code = self._as_numpy(x)
         o, _ = self._as_numpy(out) if out is not None else (a, code)
         dcode = code if wire is None else wire

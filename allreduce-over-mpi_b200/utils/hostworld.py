@@ -60,7 +60,7 @@ class HostWorld:
         w = (C.c_int * len(widths))(*widths)
         rc = self._L.ft_host_allreduce(
             self._h, s, r, count, dtype_code, io_dtype_code, K.OPS[op] if isinstance(op, str) else op,
-            K.ALGOS[algo] if isinstance(algo, str) else algo, w, len(widths), ctas, tile_bytes, mode,
+            K.HOST_ALGOS[algo] if isinstance(algo, str) else algo, w, len(widths), ctas, tile_bytes, mode,
             1.0 if scale is None else float(scale), 0 if scale is None else 1,
             int(timeout_s * 1e9), skip_rank, lonely, phases)
         return rc

@@ -1165,6 +1165,7 @@ struct StagedCta {
     } else if (a.mode == MODE_STAGING) {
       for (int j = 0; j < mine; ++j) {
         if constexpr (kBlockScaled) q_copy_in_tile(cta + j * G);
+        else if constexpr (TMA && BE::kBulkCopyIn) be.template copy_in_tile_bulk<T, IO, Op, VE>(*this, cta + j * G);
         else copy_in_tile<CU>(cta + j * G);
         be.sync();
         signal_group(PH_IN, 0, E + j + 1);

@@ -13,9 +13,112 @@
 namespace ft {
 
 struct CpuBE {
-  static constexpr bool kTma = false;  // the TMA-staged tiles exist only on the GPU
-  template <typename T, typename IO, class Op, int VE, class Cta> void rs_tile_tma(Cta&, int, int) {}
-  template <typename T, typename IO, class Op, int VE, class Cta> void ag_tile_tma(Cta&, int, int) {}
+  static constexpr bool kTma = false;  // no cp.async.bulk here ...
+  // ... but the same hook (StagedCta::run<true>) has a CPU meaning: "bulk" tiles. The GPU text gives one
+  // 16-byte vector to one thread and pays an index computation per vector, which is free next to an NVLink
+  // load and very much not free on a CPU core. The bulk tiles walk each contiguous block-of-a-tile with plain
+  // loops over kBulk elements that the compiler vectorises: same flags, same groups, same summation order
+  // (own first, peers ascending), same rounding points - results are bit-identical to the per-vector text
+  // (tests/test_host_world.py::test_bulk_*). Selected by the host with algo 5, like the TMA kernel on the GPU.
+  static constexpr bool kBulkCopyIn = true;
+  static constexpr int kBulk = 1024;
+
+  template <typename T, typename IO, class Op, int VE, class Cta> void copy_in_tile_bulk(Cta& c, int t) {
+    using EL = Elem<T>;
+    using EU = Elem<IO>;
+    using A = typename EL::acc;
+    const int N = c.a.plan.nranks, g1 = c.a.plan.gap[1];
+    char* wr = c.rc.win[c.r] + c.woff;
+    for (int b = 0; b < N; ++b) {
+      if ((b % g1) == (c.r % g1)) continue;  // blocks I own after stage 0 are read straight from `send`
+      long long start;
+      const int n = c.tile_valid32(b, t, &start);
+      if (n <= 0) continue;
+      const IO* __restrict s = (const IO*)c.rc.send + start;
+      T* __restrict d = (T*)wr + start;
+      if constexpr (Cta::kRawIO) {
+        memcpy(d, s, (size_t)n * sizeof(T));
+      } else {
+        for (int i = 0; i < n; ++i) d[i] = EL::down((A)EU::up(s[i]));
+      }
+    }
+  }
+
+  template <typename T, typename IO, class Op, int VE, class Cta> void rs_tile_tma(Cta& c, int k, int t) {
+    using EL = Elem<T>;
+    using EU = Elem<IO>;
+    using A = typename EL::acc;
+    const Plan& P = c.a.plan;
+    const int w = P.width[k], gn = P.gap[k + 1], nb = P.nranks / gn, rmod = c.r % gn, npeers = w - 1;
+    const bool from_user = (k == 0) && (c.a.mode == MODE_STAGING);
+    const bool final_stage = (k == P.nstages - 1) && c.a.lonely == 0;
+    char* wr = c.rc.win[c.r] + c.woff;
+    const char* peer[FT_MAX_WIDTH];
+    for (int j = 0; j < npeers; ++j) peer[j] = c.rs_peer_ptr(k, j);
+    A acc[kBulk];
+    for (int bi = 0; bi < nb; ++bi) {
+      long long start;
+      const int n = c.tile_valid32(rmod + bi * gn, t, &start);
+      for (int o = 0; o < n; o += kBulk) {
+        const int len = n - o < kBulk ? n - o : kBulk;
+        const long long el = start + o;
+        if (from_user) {
+          const IO* __restrict s = (const IO*)c.rc.send + el;
+          if constexpr (Cta::kRawIO) {
+            for (int i = 0; i < len; ++i) acc[i] = EL::up(s[i]);
+          } else {  // the own contribution is rounded to the wire type first, exactly like io_to_wire
+            for (int i = 0; i < len; ++i) acc[i] = EL::up(EL::down((A)EU::up(s[i])));
+          }
+        } else {
+          const T* __restrict s = (const T*)wr + el;
+          for (int i = 0; i < len; ++i) acc[i] = EL::up(s[i]);
+        }
+        for (int j = 0; j < npeers; ++j) {
+          const T* __restrict s = (const T*)peer[j] + el;
+          for (int i = 0; i < len; ++i) acc[i] = Op::apply(acc[i], EL::up(s[i]));
+        }
+        if constexpr (EL::is_float) {
+          if (final_stage && c.a.apply_scale) {
+            const A sc = (A)c.a.scale;
+            for (int i = 0; i < len; ++i) acc[i] = (A)(acc[i] * sc);
+          }
+        }
+        T* __restrict d = (T*)wr + el;
+        for (int i = 0; i < len; ++i) d[i] = EL::down(acc[i]);
+      }
+    }
+  }
+
+  template <typename T, typename IO, class Op, int VE, class Cta> void ag_tile_tma(Cta& c, int k, int t) {
+    using EL = Elem<T>;
+    using EU = Elem<IO>;
+    const Plan& P = c.a.plan;
+    const int w = P.width[k], g = P.gap[k], gn = P.gap[k + 1], base = stage_base(P, c.r, k), nb = P.nranks / gn;
+    const bool last = (k == 0);
+    const bool self_needed = last && !(c.a.mode == MODE_REGISTERED && Cta::kRawIO);
+    const int rot = (c.r - base) / g + 1;  // start at my right-hand neighbour: spreads the readers over the sources
+    char* wr = c.rc.win[c.r] + c.woff;
+    for (int bi = 0; bi < nb; ++bi) {
+      for (int s_ = 0; s_ < w; ++s_) {
+        const int p = base + ((rot + s_) % w) * g;
+        if (p == c.r && !self_needed) continue;
+        long long start;
+        const int n = c.tile_valid32((p % gn) + bi * gn, t, &start);
+        if (n <= 0) continue;
+        const T* __restrict s = (const T*)(c.rc.win[p] + c.woff) + start;
+        if (!last) {
+          memcpy((T*)wr + start, s, (size_t)n * sizeof(T));
+        } else {
+          IO* __restrict y = (IO*)c.rc.recv + start;
+          if constexpr (Cta::kRawIO && !EL::is_float) {
+            memcpy(y, s, (size_t)n * sizeof(T));
+          } else {  // same conversions as wire_to_io (the scale was applied when the block became final)
+            for (int i = 0; i < n; ++i) y[i] = EU::down((typename EU::acc)EL::up(s[i]));
+          }
+        }
+      }
+    }
+  }
   int abort_ = 0;
   int tid() const { return 0; }
   int nthr() const { return 1; }

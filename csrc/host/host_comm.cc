@@ -8,9 +8,11 @@
 #include <stdio.h>
 #include <stdlib.h>
 #include <string.h>
+#include <sched.h>
 #include <sys/mman.h>
 #include <sys/stat.h>
 #include <sys/time.h>
+#include <time.h>
 #include <unistd.h>
 
 #include <string>
@@ -35,13 +37,48 @@ struct ft_host_comm {
   std::vector<char*> maps;       // whole shared mapping of every rank
   std::vector<char*> win_table;  // window segment base of every rank
   CommDev cd;
-  uint64_t epoch = 0;
+  uint64_t epoch = 0, calls = 0;
+  size_t board_off = 0;  // agreement board: FT_MAX_RANKS 64-bit slots in the spare page behind the windows
   unsigned done = 0, err = 0;
   bool allgather(const void* s, void* r, size_t n) const {
     if (nranks == 1) { memcpy(r, s, n); return true; }
     return ag && ag(ctx, s, r, n) == 0;
   }
 };
+
+// Per-call agreement on one bit (here: "all my buffers are 16-byte aligned") without leaving shared memory.
+// Every rank owns one 64-bit slot per rank in the spare page behind its windows; it publishes
+// (call number << 1 | bit) into its slot on EVERY rank and then waits until its own board shows this call's
+// number in every slot. A peer cannot be more than one call ahead (it cannot finish call n without my data
+// phase, which starts after my agreement), so ">= this call" is never satisfied by a stale value. Replaces a
+// bootstrap all-gather per call (a gloo round trip costs more than the whole collective for small messages).
+static bool agree(ft_host_comm* c, char* bit, unsigned long long timeout_ns) {
+  const int N = c->nranks;
+  const uint64_t seq = ++c->calls;
+  const uint64_t mine = (seq << 1) | (uint64_t)(*bit ? 1 : 0);
+  for (int p = 0; p < N; ++p)
+    __atomic_store_n((uint64_t*)(c->maps[(size_t)p] + c->board_off) + c->rank, mine, __ATOMIC_RELEASE);
+  const uint64_t* board = (const uint64_t*)(c->maps[(size_t)c->rank] + c->board_off);
+  timespec t0;
+  clock_gettime(CLOCK_MONOTONIC, &t0);
+  char all = 1;
+  for (int p = 0; p < N; ++p) {
+    uint64_t v;
+    unsigned it = 0;
+    while (((v = __atomic_load_n(board + p, __ATOMIC_ACQUIRE)) >> 1) < seq) {
+      if (((++it) & 0x3ff) == 0 && timeout_ns) {
+        timespec t1;
+        clock_gettime(CLOCK_MONOTONIC, &t1);
+        const unsigned long long dt = (unsigned long long)(t1.tv_sec - t0.tv_sec) * 1000000000ull + (unsigned long long)t1.tv_nsec - (unsigned long long)t0.tv_nsec;
+        if (dt > timeout_ns) return false;
+      }
+      sched_yield();
+    }
+    all = all && (v & 1);
+  }
+  *bit = all;
+  return true;
+}
 
 static std::string shm_name(unsigned long long token, int rank) {
   char buf[96];
@@ -65,6 +102,7 @@ ft_result_t ft_host_comm_create(ft_host_comm** out, int rank, int nranks, ft_all
   c->win_bytes = ((window_bytes ? window_bytes : (size_t)(4 << 20)) + 4095) & ~(size_t)4095;
   c->ll_bytes = ((ll_bytes ? ll_bytes : (size_t)(1 << 20)) + 4095) & ~(size_t)4095;
   c->seg_bytes = 3 * c->win_bytes + 4096;  // [parity 0 | parity 1 | registered]
+  c->board_off = 3 * c->win_bytes;
   const size_t pad_off = c->seg_bytes, ll_off = pad_off + ((FT_PAD_BYTES + 4095) & ~(size_t)4095);
   c->total_bytes = ll_off + 2 * c->ll_bytes + 4096;
 
@@ -149,6 +187,8 @@ long long ft_host_comm_allreduce(ft_host_comm* c, const void* send, void* recv, 
   StagedArgs a;
   memset(&a, 0, sizeof a);
   const int N = c->nranks;
+  const bool want_bulk = algo == ALGO_STAGED_TMA;  // staged stages with the CPU's bulk tiles (cpu_backend.h)
+  if (want_bulk) algo = ALGO_STAGED;
   if (send == FT_IN_PLACE || !send) send = recv;
   if (N == 1) {
     if (send != recv) memcpy(recv, send, (size_t)count * (size_t)dtype_size(io_dtype));
@@ -170,13 +210,12 @@ long long ft_host_comm_allreduce(ft_host_comm* c, const void* send, void* recv, 
   // every rank must take the same code path: alignment is agreed on collectively
   char vec = ((uintptr_t)send % 16 == 0) && ((uintptr_t)recv % 16 == 0);
   if (phases != PHASES_ALLREDUCE && ((count / N) * es) % 16) vec = 0;
-  std::vector<char> vs((size_t)N);
-  if (!c->allgather(&vec, vs.data(), 1)) return -11;
-  for (char v : vs) vec = vec && v;
+  if (!agree(c, &vec, timeout_ns)) return -11;
   a.lonely = lonely;
   a.phases = phases;
   a.nvls_reducers = ctas >= 4 ? ctas / 4 : 0;  // small CTA counts exercise the one-role (skewed) variant
   a.lay = make_layout(count, a.plan.nranks, es, tile_bytes, vec != 0);
+  a.use_tma = want_bulk && vec && lonely == 0 && dtype != DT_FP8_BLOCK && count % (16 / es) == 0;
   a.scale_plane_off = ((long long)a.lay.block * a.plan.nranks * es + 255) & ~255LL;
   if ((size_t)(a.scale_plane_off + (a.lay.block * a.plan.nranks) / 16 + 16) > c->win_bytes) return -4;
   if (algo == ALGO_ONESHOT) {
@@ -198,7 +237,7 @@ long long ft_host_comm_allreduce(ft_host_comm* c, const void* send, void* recv, 
   a.rc[0].recv = recv;
   a.rc[0].win = c->win_table.data();
   a.rc[0].mc = nullptr;
-  if (!host_run_group(dtype_group(dtype), dtype, io_dtype, op, vec != 0, &a, algo)) return -7;
+  if (!host_run_group(dtype_group(dtype), dtype, io_dtype, op, vec != 0, &a, a.use_tma ? (int)ALGO_STAGED_TMA : algo)) return -7;
   return c->err ? (long long)c->err : 0;
 }
 

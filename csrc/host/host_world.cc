@@ -102,6 +102,8 @@ long long ft_host_allreduce(void* h, const void* const* send, void* const* recv,
   auto* w = (HostWorld*)h;
   StagedArgs a;
   memset(&a, 0, sizeof a);
+  const bool want_bulk = algo == ALGO_STAGED_TMA;  // staged stages with the CPU's bulk tiles (cpu_backend.h)
+  if (want_bulk) algo = ALGO_STAGED;
   if (algo == ALGO_RING || algo == ALGO_NVLS || algo == ALGO_ONESHOT) {
     int flat = w->n;
     if (!make_plan(&flat, 1, &a.plan)) return -1;
@@ -122,6 +124,8 @@ long long ft_host_allreduce(void* h, const void* const* send, void* const* recv,
     vec = vec && ((uintptr_t)send[r] % 16 == 0) && ((uintptr_t)recv[r] % 16 == 0);
   if (phases != PHASES_ALLREDUCE && ((count / w->n) * es) % 16) vec = false;  // blocks must not be padded
   a.lay = make_layout(count, a.plan.nranks, es, tile_bytes, vec);
+  // same rule as the TMA kernel on the GPU: vector path, whole 16-byte vectors, plain wire, no lonely ranks
+  a.use_tma = want_bulk && vec && lonely == 0 && dtype != DT_FP8_BLOCK && count % (16 / es) == 0;
   a.scale_plane_off = ((long long)a.lay.block * a.plan.nranks * es + 255) & ~255LL;
   if ((size_t)(a.scale_plane_off + (a.lay.block * a.plan.nranks) / 16 + 16) > w->win_bytes) return -4;
   if (algo == ALGO_ONESHOT) {
@@ -155,7 +159,7 @@ long long ft_host_allreduce(void* h, const void* const* send, void* const* recv,
     b.nlocal = w->n - 1;
     a = b;
   }
-  bool ok = host_run_group(dtype_group(dtype), dtype, io_dtype, op, vec, &a, algo);
+  bool ok = host_run_group(dtype_group(dtype), dtype, io_dtype, op, vec, &a, a.use_tma ? (int)ALGO_STAGED_TMA : algo);
   if (!ok) return -7;
   for (int r = 0; r < w->n; ++r)
     if (w->err[r]) return (long long)w->err[r];

@@ -20,6 +20,7 @@ namespace ft {
 
 struct CudaBE {
   static constexpr bool kTma = true;
+  static constexpr bool kBulkCopyIn = false;  // CPU back end only (host/cpu_backend.h)
   int* abort_;
   TmaRing ring_;
   __device__ __forceinline__ CudaBE(int* abort_smem, const TmaRing& ring) : abort_(abort_smem), ring_(ring) {}

@@ -58,5 +58,9 @@ int main() {
   bad |= run(4, {4}, 1, 0, 999, 2, 256);
   bad |= run(7, {2, 3}, 2, 0, 5000, 2, 256, 1);
   bad |= run(5, {3}, 2, 0, 3001, 3, 128, 2);
+  // bulk tiles (algo 5, cpu_backend.h): private and registered buffers
+  bad |= run(6, {2, 3}, 5, 0, 7000, 2, 512);
+  bad |= run(8, {2, 2, 2}, 5, 1, 6000, 3, 256);
+  bad |= run(4, {4}, 5, 0, 40000, 1, 4096);
   return bad;
 }

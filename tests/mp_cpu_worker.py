@@ -37,6 +37,23 @@ def main():
             chk = y.clone()
             dist.broadcast(chk, 0)
             assert torch.equal(chk, y), "ranks differ"
+    # bulk tiles vs the per-vector text of the GPU kernels: same bits, private and registered buffers
+    for widths in ft.enumerate_widths(world):
+        x = torch.randn(40000, generator=g)
+        a, b = x.clone(), x.clone()
+        comm.allreduce(a, algo="stages", widths=widths, ctas=2, tile_bytes=4096)
+        comm.allreduce(b, algo="stages_bulk", widths=widths, ctas=2, tile_bytes=4096)
+        assert torch.equal(a, b), widths
+        comm.allreduce(x, widths=widths)  # defaults: bulk, one thread, 256 KiB tiles
+        assert torch.equal(a, x), widths
+    # the per-call agreement on the code path lives in shared memory: one rank with a misaligned buffer moves
+    # every rank to the scalar path (a disagreement would deadlock or corrupt, not just differ)
+    raw = torch.zeros(1001 + 4)
+    x = raw[1:1002] if rank == world - 1 else raw[4:1005] if raw.data_ptr() % 16 == 0 else raw[0:1001]
+    x.copy_(torch.randn(1001, generator=g))
+    ref = ref_sum(x.double()).float()
+    comm.allreduce(x)
+    assert torch.allclose(x, ref, rtol=1e-5, atol=1e-5)
     # other algorithms
     for algo in ("oneshot", "ring", "nvls"):
         x = torch.randn(3000, generator=g)

@@ -445,3 +445,123 @@ def test_conversions_match_numpy():
         f = L.ft_f16_to_float(bits)
         want = np.array([bits], np.uint16).view(np.float16).astype(np.float32)[0]
         assert (np.isnan(f) and np.isnan(want)) or f == want, hex(bits)
+
+
+# ---- bulk tiles (csrc/host/cpu_backend.h): the CPU counterpart of the TMA-staged tiles -------------------------
+# Same hook as the TMA kernel (StagedCta::run<true>), selected with algo 5. They must give the bits of the
+# per-vector text in every configuration they accept and fall back to it silently everywhere else.
+
+def _both(n, make, **kw):
+    """Run the same call with the per-vector text and with the bulk tiles; return the two result lists."""
+    out = []
+    for algo in ("stages", "stages_bulk"):
+        w = HostWorld(n, window_bytes=1 << 18)
+        send, recv = make()
+        assert w.allreduce(send, recv, algo=algo, **kw) == 0
+        out.append(recv if recv is not None else send)
+        w.close()
+    return out
+
+
+@pytest.mark.parametrize("dtype", [np.uint8, np.int16, np.int32, np.int64, np.float32, np.float64, np.float16, np.bool_])
+@pytest.mark.parametrize("op", ["sum", "max", "band"])
+def test_bulk_tiles_dtype_op_matrix_bit_identical(dtype, op):
+    dt = np.dtype(dtype)
+    if dt.kind == "f" and op == "band":
+        pytest.skip("no bitwise ops on floats")
+    n, widths = 6, [2, 3]
+    count = 6 * 1024 + 16 * 5  # a multiple of 16 elements: whole 16-byte vectors for every dtype
+    inputs = make_inputs(n, count, dtype)
+    a, b = _both(n, lambda: ([aligned_copy(x) for x in inputs], None), op=op, widths=widths, ctas=2, tile_bytes=512)
+    for r in range(n):
+        np.testing.assert_array_equal(a[r], b[r], err_msg=f"rank {r}")
+    if dt.kind != "f":  # and against numpy (floats: bit-exact model is covered by the per-vector tests)
+        if dt.kind == "b":
+            want = np.stack(inputs).any(0) if op in ("sum", "max") else np.stack(inputs).all(0)
+        else:
+            with np.errstate(over="ignore"):
+                want = inputs[0].copy()
+                for x in inputs[1:]:
+                    want = NP_OPS[op](want, x)
+        np.testing.assert_array_equal(b[0], want)
+
+
+@pytest.mark.parametrize("n,widths", [(2, [2]), (4, [2, 2]), (8, [8]), (8, [2, 2, 2]), (12, [3, 4]), (20, [20])])
+@pytest.mark.parametrize("ctas,tile", [(1, 1 << 20), (3, 256), (2, 4096)])
+def test_bulk_tiles_fp32_bit_exact_vs_model(n, widths, ctas, tile):
+    count = 4 * 1237  # not a multiple of n * 4: short and empty tail blocks
+    inputs = make_inputs(n, count, np.float32)
+    want = staged_allreduce(inputs, widths, block=block_size(count, n, 4))
+    w = HostWorld(n, window_bytes=1 << 18)
+    send = [aligned_copy(x) for x in inputs]
+    recv = [aligned_empty(count, np.float32) for _ in range(n)]
+    assert w.allreduce(send, recv, algo="stages_bulk", widths=widths, ctas=ctas, tile_bytes=tile) == 0
+    for r in range(n):
+        np.testing.assert_array_equal(recv[r], want[r], err_msg=f"rank {r}")
+        np.testing.assert_array_equal(send[r], inputs[r])  # sendbuf preserved
+    # back to back, in place, other parity of the window
+    assert w.allreduce(send, None, algo="stages_bulk", widths=widths, ctas=ctas, tile_bytes=tile) == 0
+    for r in range(n):
+        np.testing.assert_array_equal(send[r], want[r])
+
+
+@pytest.mark.parametrize("widths", [[8], [2, 4], [2, 2, 2]])
+def test_bulk_tiles_registered_zero_copy_and_scale(widths):
+    n, count = 8, 4096
+    inputs = make_inputs(n, count, np.float32)
+    res = []
+    for algo in ("stages", "stages_bulk"):
+        w = HostWorld(n, window_bytes=1 << 18)
+        bufs = [w.registered(r, count, np.float32) for r in range(n)]
+        for b, x in zip(bufs, inputs):
+            b[:] = x
+        assert w.allreduce(bufs, None, algo=algo, widths=widths, ctas=2, tile_bytes=512, mode=K.MODE_REGISTERED,
+                           scale=0.125) == 0
+        res.append([b.copy() for b in bufs])
+        w.close()
+    for r in range(n):
+        np.testing.assert_array_equal(res[0][r], res[1][r])
+    np.testing.assert_allclose(res[1][0], np.mean(np.stack(inputs), 0), rtol=1e-5, atol=1e-6)
+
+
+def test_bulk_tiles_fp32_io_bf16_wire_with_scale():
+    n, count, widths = 4, 2048, [2, 2]
+    xf = make_inputs(n, count, np.float32)
+    kw = dict(widths=widths, ctas=2, tile_bytes=256, dtype_code=K.BFLOAT16, io_dtype_code=K.FLOAT, scale=1.0 / n)
+    a, b = _both(n, lambda: ([aligned_copy(x) for x in xf], [aligned_empty(count, np.float32) for _ in range(n)]), **kw)
+    for r in range(n):
+        np.testing.assert_array_equal(a[r], b[r])
+    want = staged_allreduce([round_bf16(x) for x in xf], widths, block=block_size(count, n, 2), round_fn=round_bf16,
+                            final_scale=1.0 / n)[0]
+    np.testing.assert_array_equal(b[0], want)
+
+
+def test_bulk_tiles_fall_back_where_they_do_not_apply():
+    n, widths = 4, [2, 2]
+    # ragged message (not whole 16-byte vectors), unaligned buffers, lonely ranks: algo 5 silently runs the per-vector text
+    for count, misalign in [(1001, 0), (1024, 4)]:
+        inputs = make_inputs(n, count, np.float32)
+        a, b = _both(n, lambda: ([aligned_copy(x, misalign) for x in inputs], None), widths=widths, ctas=2, tile_bytes=256)
+        for r in range(n):
+            np.testing.assert_array_equal(a[r], b[r])
+    inputs = make_inputs(5, 1024, np.float32)
+    a, b = _both(5, lambda: ([aligned_copy(x) for x in inputs], None), widths=[2, 2], ctas=2, tile_bytes=256, lonely=1)
+    for r in range(5):
+        np.testing.assert_array_equal(a[r], b[r])
+
+
+@pytest.mark.parametrize("n,widths", [(4, [4]), (6, [2, 3])])
+def test_bulk_tiles_reduce_scatter_and_all_gather_halves(n, widths):
+    per_rank = 256
+    total = per_rank * n
+    xs = make_inputs(n, total, np.float32)
+    w = HostWorld(n, window_bytes=1 << 18)
+    part = [aligned_empty(per_rank, np.float32) for _ in range(n)]
+    assert w.allreduce([aligned_copy(x) for x in xs], part, algo="stages_bulk", widths=widths, ctas=2, tile_bytes=128,
+                       phases=1, count=total) == 0
+    full = [aligned_empty(total, np.float32) for _ in range(n)]
+    assert w.allreduce(part, full, algo="stages_bulk", widths=widths, ctas=2, tile_bytes=128, phases=2, count=total) == 0
+    ref = [aligned_copy(x) for x in xs]
+    assert w.allreduce(ref, None, widths=widths) == 0
+    for r in range(n):
+        np.testing.assert_array_equal(full[r], ref[r])
