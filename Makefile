@@ -31,7 +31,7 @@ HOST_OBJ := $(HOST_SRC:%.cc=$(B)/%.o)
 CUDA_OBJ := $(CUDA_SRC:%.cu=$(B)/%.cu.o)
 RT_CC_OBJ := $(RT_CC_SRC:%.cc=$(B)/%.o)
 
-.PHONY: all host cuda tools clean tsan fdtest memcheck racecheck
+.PHONY: all host cuda tools clean tsan fdtest memcheck racecheck dropin
 all: host cuda tools
 host: $(B)/libflextree_host.so
 cuda: $(LIBDIR)/libflextree.so
@@ -75,6 +75,10 @@ tsan:
 	  tests/cpp/tsan_world.cc csrc/host/host_world.cc csrc/host/host_run_all.cc csrc/host/host_run_g1.cc \
 	  csrc/planner/factorize.cc csrc/planner/cost_model.cc -lpthread
 	$(B)/tsan_world
+# The reference's unmodified benchmark.cpp (and a plain MPI test program) built against compat/mpi_mod.hpp +
+# libflextree_host.so + the in-repo MPI subset -> baseline/_ref/bin/{allreduce_over_mpi_dropin,dropin_user}
+dropin: host
+	bash baseline/build_ref.sh
 fdtest:
 	$(CXX) -std=c++17 -O1 -o $(B)/fd_channel_test tests/cpp/fd_channel_test.cc
 	$(B)/fd_channel_test 8

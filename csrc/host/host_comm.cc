@@ -19,6 +19,7 @@
 #include <vector>
 
 #include "../../include/flextree.h"
+#include "../../include/flextree_host.h"
 #include "../core/dispatch.h"
 #include "../core/staged_core.h"
 #include "../planner/cost_model.h"
