@@ -49,10 +49,30 @@ class HostCommunicator:
 
         self._cb = _AG_FN(_allgather)
         self._h = vp()
-        rc = L.ft_host_comm_create(C.byref(self._h), self.rank, world, C.cast(self._cb, vp), None, window_bytes, ll_bytes)
+        self._ll_bytes = ll_bytes
+        self._create(window_bytes)
+
+    def _create(self, window_bytes):
+        L, vp = self._L, C.c_void_p
+        rc = L.ft_host_comm_create(C.byref(self._h), self.rank, self.size, C.cast(self._cb, vp), None, window_bytes,
+                                   self._ll_bytes)
         if rc:
             raise RuntimeError(f"ft_host_comm_create failed ({rc}): {L.ft_last_error().decode()}")
         self.window_bytes = window_bytes
+
+    def reserve(self, nbytes):
+        """Grow-only staging, like the reference's flextree_register_the_buffer (mpi_mod.hpp:932-950): make room for
+        messages of ``nbytes`` (wire type). Collective when it has to grow (every rank sees the same sizes); views
+        returned by registered() before a growth are invalid afterwards. allreduce() calls this itself."""
+        need = nbytes + nbytes // 16 + 32 * self.size + 4096  # blocks padded to 16 B + the scale plane of the layout
+        if need <= self.window_bytes:
+            return
+        win = self.window_bytes
+        while win < need:
+            win *= 2
+        self._L.ft_host_comm_destroy(self._h)
+        self._h = C.c_void_p()
+        self._create(win)
 
     def close(self):
         if getattr(self, "_h", None) and self._h.value:
@@ -72,6 +92,8 @@ class HostCommunicator:
               timeout_s):
         widths = list(widths) if widths is not None else [self.size - lonely]
         w = (C.c_int * len(widths))(*widths)
+        if mode != K.MODE_REGISTERED:  # a registered call works on a view of the current window: it cannot move
+            self.reserve(count * K.DTYPE_SIZE[dcode])
         rc = self._L.ft_host_comm_allreduce(
             self._h, send_ptr, recv_ptr, count, dcode, iocode, K.OPS[op] if isinstance(op, str) else op,
             K.HOST_ALGOS[algo] if isinstance(algo, str) else algo, w, len(widths), ctas, tile_bytes, mode,

@@ -107,6 +107,15 @@ def main():
         ref = ref_sum(x.double()).float()
         comm.allreduce(x, widths=tree, lonely=lonely)
         assert torch.allclose(x, ref, rtol=1e-5, atol=1e-5)
+    # grow-only staging (mpi_mod.hpp:932-950): a communicator created small re-creates its windows collectively
+    small = ft.HostCommunicator(window_bytes=1 << 16)
+    for count in (1000, 200000, 5000):
+        x = torch.randn(count, generator=g)
+        ref = ref_sum(x.double()).float()
+        small.allreduce(x)
+        assert torch.allclose(x, ref, rtol=1e-5, atol=1e-5), count
+    assert small.window_bytes >= 800000 and small.error() == 0
+    small.close()
     assert comm.error() == 0
     dist.barrier()
     comm.close()
