@@ -11,7 +11,8 @@ from .parallel.api import init, allreduce, get_communicator, shutdown
 from .parallel.ddp import ddp_comm_hook, FlexTreeHookState
 from .parallel.data_parallel import FlexTreeDataParallel
 from .parallel.host_comm import HostCommunicator
+from .parallel.host_data_parallel import HostDataParallel
 
 __all__ = list(_planner_all) + list(_const_all) + [
     "HostWorld", "Timer", "Communicator", "FlexTreeError", "init", "allreduce", "get_communicator", "shutdown",
-    "ddp_comm_hook", "FlexTreeHookState", "FlexTreeDataParallel", "HostCommunicator"]
+    "ddp_comm_hook", "FlexTreeHookState", "FlexTreeDataParallel", "HostCommunicator", "HostDataParallel"]

@@ -67,6 +67,9 @@ class HostCommunicator:
         need = nbytes + nbytes // 16 + 32 * self.size + 4096  # blocks padded to 16 B + the scale plane of the layout
         if need <= self.window_bytes:
             return
+        if getattr(self, "_views_out", False):
+            raise RuntimeError(f"a {nbytes}-byte message needs a larger window, and growing it would invalidate the registered "
+                               "views handed out earlier: create the communicator with a larger window_bytes")
         win = self.window_bytes
         while win < need:
             win *= 2
@@ -79,11 +82,24 @@ class HostCommunicator:
             self._L.ft_host_comm_destroy(self._h)
             self._h = C.c_void_p()
 
-    def registered(self, count, dtype):
-        """numpy view of this rank's registered (zero-copy) region."""
+    def registered(self, count, dtype, offset_bytes=0):
+        """numpy view of (a piece of) this rank's registered (zero-copy) region. Pieces must start at a multiple of
+        16 bytes and at the same offset on every rank; allreduce(view, registered=True) works on them in place."""
+        if offset_bytes % 16:
+            raise ValueError("registered views start at multiples of 16 bytes")
         ptr = self._L.ft_host_comm_registered(self._h)
         nbytes = count * np.dtype(dtype).itemsize
-        return np.frombuffer((C.c_char * nbytes).from_address(ptr), dtype=dtype, count=count)
+        if offset_bytes + nbytes > self.window_bytes:
+            raise ValueError(f"registered region is {self.window_bytes} bytes (HostCommunicator(window_bytes=...))")
+        self._views_out = True
+        return np.frombuffer((C.c_char * nbytes).from_address(ptr + offset_bytes), dtype=dtype, count=count)
+
+    def registered_tensor(self, numel, dtype=torch.float32, offset_bytes=0):
+        """The same as a torch tensor sharing the memory (fp32/fp64/ints; bf16/fp16 through a uint16 view)."""
+        if dtype in (torch.bfloat16, torch.float16):
+            return torch.from_numpy(self.registered(numel, np.uint16, offset_bytes)).view(dtype)
+        npdt = torch.empty(0, dtype=dtype).numpy().dtype
+        return torch.from_numpy(self.registered(numel, npdt, offset_bytes))
 
     def error(self):
         return int(self._L.ft_host_comm_error(self._h))

@@ -47,38 +47,42 @@ struct ft_host_comm {
   }
 };
 
-// Per-call agreement on one bit (here: "all my buffers are 16-byte aligned") without leaving shared memory.
-// Every rank owns one 64-bit slot per rank in the spare page behind its windows; it publishes
-// (call number << 1 | bit) into its slot on EVERY rank and then waits until its own board shows this call's
-// number in every slot. A peer cannot be more than one call ahead (it cannot finish call n without my data
-// phase, which starts after my agreement), so ">= this call" is never satisfied by a stale value. Replaces a
-// bootstrap all-gather per call (a gloo round trip costs more than the whole collective for small messages).
-static bool agree(ft_host_comm* c, char* bit, unsigned long long timeout_ns) {
+// Per-call agreement without leaving shared memory: one bit that is AND-ed over the ranks (here: "all my buffers
+// are 16-byte aligned") and a 31-bit payload that must be the same on every rank (here: the offset of a registered
+// buffer inside the region, in 16-byte units). Every rank owns one 64-bit slot per rank in the spare page behind its
+// windows; it publishes (call number << 32 | payload << 1 | bit) into its slot on EVERY rank and then waits until
+// its own board shows this call's number in every slot. A peer cannot be more than one call ahead (it cannot
+// finish call n without my data phase, which starts after my agreement), so ">= this call" is never satisfied by a
+// stale value. Replaces a bootstrap all-gather per call (a gloo round trip costs more than the whole collective for
+// small messages). Returns 0 = timeout, 1 = agreed, 2 = payloads differ (every rank sees that).
+static int agree(ft_host_comm* c, char* bit, uint32_t payload, unsigned long long timeout_ns) {
   const int N = c->nranks;
   const uint64_t seq = ++c->calls;
-  const uint64_t mine = (seq << 1) | (uint64_t)(*bit ? 1 : 0);
+  const uint64_t mine = (seq << 32) | ((uint64_t)(payload & 0x7fffffffu) << 1) | (uint64_t)(*bit ? 1 : 0);
   for (int p = 0; p < N; ++p)
     __atomic_store_n((uint64_t*)(c->maps[(size_t)p] + c->board_off) + c->rank, mine, __ATOMIC_RELEASE);
   const uint64_t* board = (const uint64_t*)(c->maps[(size_t)c->rank] + c->board_off);
   timespec t0;
   clock_gettime(CLOCK_MONOTONIC, &t0);
   char all = 1;
+  bool same = true;
   for (int p = 0; p < N; ++p) {
     uint64_t v;
     unsigned it = 0;
-    while (((v = __atomic_load_n(board + p, __ATOMIC_ACQUIRE)) >> 1) < seq) {
+    while (((v = __atomic_load_n(board + p, __ATOMIC_ACQUIRE)) >> 32) < seq) {
       if (((++it) & 0x3ff) == 0 && timeout_ns) {
         timespec t1;
         clock_gettime(CLOCK_MONOTONIC, &t1);
         const unsigned long long dt = (unsigned long long)(t1.tv_sec - t0.tv_sec) * 1000000000ull + (unsigned long long)t1.tv_nsec - (unsigned long long)t0.tv_nsec;
-        if (dt > timeout_ns) return false;
+        if (dt > timeout_ns) return 0;
       }
       sched_yield();
     }
     all = all && (v & 1);
+    same = same && (((v >> 1) & 0x7fffffffu) == (payload & 0x7fffffffu));
   }
   *bit = all;
-  return true;
+  return same ? 1 : 2;
 }
 
 static std::string shm_name(unsigned long long token, int rank) {
@@ -211,7 +215,21 @@ long long ft_host_comm_allreduce(ft_host_comm* c, const void* send, void* recv, 
   // every rank must take the same code path: alignment is agreed on collectively
   char vec = ((uintptr_t)send % 16 == 0) && ((uintptr_t)recv % 16 == 0);
   if (phases != PHASES_ALLREDUCE && ((count / N) * es) % 16) vec = 0;
-  if (!agree(c, &vec, timeout_ns)) return -11;
+  // registered mode: the buffer is a 16-byte aligned piece of my registered region, at the same offset on every rank
+  // (a ragged last vector is written whole: up to 15 bytes behind the message, inside the same 16-byte slot)
+  long long reg_off = 0;
+  bool reg_bad = false;
+  if (mode == MODE_REGISTERED) {
+    const char* base = c->win_table[(size_t)c->rank] + 2 * c->win_bytes;
+    reg_off = (const char*)recv - base;
+    reg_bad = send != recv || reg_off < 0 || reg_off % 16 ||
+              (size_t)reg_off + (((size_t)count * (size_t)es + 15) & ~(size_t)15) > c->win_bytes;
+  }
+  // a rank with a bad buffer still takes part in the agreement (with a payload nobody else can have), so that
+  // every rank returns the error instead of some of them waiting for it
+  const int agreed = agree(c, &vec, reg_bad ? 0x7fffffffu : (uint32_t)(reg_off >> 4), timeout_ns);
+  if (agreed == 0) return -11;
+  if (agreed == 2 || reg_bad) return -13;
   a.lonely = lonely;
   a.phases = phases;
   a.nvls_reducers = ctas >= 4 ? ctas / 4 : 0;  // small CTA counts exercise the one-role (skewed) variant
@@ -230,7 +248,7 @@ long long ft_host_comm_allreduce(ft_host_comm* c, const void* send, void* recv, 
   a.mode = mode;
   a.apply_scale = apply_scale;
   a.scale = scale;
-  a.win_off0 = mode == MODE_REGISTERED ? 2 * (long long)c->win_bytes : 0;
+  a.win_off0 = mode == MODE_REGISTERED ? 2 * (long long)c->win_bytes + reg_off : 0;
   a.win_stride = mode == MODE_REGISTERED ? 0 : (long long)c->win_bytes;
   a.timeout_ns = timeout_ns;
   a.rc[0].comm = &c->cd;

@@ -89,6 +89,23 @@ def main():
         view[:] = src.numpy()
         comm.allreduce(view, registered=True, ctas=2, tile_bytes=1024)
         assert np.allclose(view, ref.numpy(), rtol=1e-5, atol=1e-5)
+    # pieces of the registered region: same offset on every rank works in place; different offsets (or a buffer
+    # outside the region) are refused on EVERY rank, and the communicator stays usable
+    piece = comm.registered(1000, np.float32, offset_bytes=8192)
+    src = torch.randn(1000, generator=g)
+    ref = ref_sum(src.double()).float()
+    piece[:] = src.numpy()
+    comm.allreduce(piece, registered=True)
+    assert np.allclose(piece, ref.numpy(), rtol=1e-5, atol=1e-5)
+    for bad in (comm.registered(256, np.float32, offset_bytes=16 * (1 + rank)), np.zeros(256, np.float32) if rank == 0 else piece[:256]):
+        try:
+            comm.allreduce(bad, registered=True)
+            raise AssertionError("mismatched registered buffers must be refused")
+        except RuntimeError as e:
+            assert "-13" in str(e), e
+    piece[:] = src.numpy()
+    comm.allreduce(piece, registered=True)
+    assert np.allclose(piece, ref.numpy(), rtol=1e-5, atol=1e-5)
     # the halves
     per = 257
     x = torch.randn(per * world, generator=g)
