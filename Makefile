@@ -71,8 +71,8 @@ $(B)/nccl_bench: csrc/tools/nccl_bench.cu
 # ThreadSanitizer run of the algorithm templates on the CPU world (the reference has no
 # sanitizer targets at all) and the SCM_RIGHTS fd-channel test.
 tsan:
-	$(CXX) -std=c++17 -O1 -g -fsanitize=thread -Wno-unknown-pragmas -Iinclude -DFT_ONLY_F32 -o $(B)/tsan_world \
-	  tests/cpp/tsan_world.cc csrc/host/host_world.cc csrc/host/host_run_all.cc csrc/host/host_run_g1.cc \
+	$(CXX) -std=c++17 -O1 -g -fsanitize=thread -Wno-unknown-pragmas -Wno-tsan -Iinclude -DFT_ONLY_F32 -DFT_WITH_F16 -o $(B)/tsan_world \
+	  tests/cpp/tsan_world.cc csrc/host/host_world.cc csrc/host/host_run_all.cc csrc/host/host_run_g1.cc csrc/host/host_run_g2.cc \
 	  csrc/planner/factorize.cc csrc/planner/cost_model.cc -lpthread
 	$(B)/tsan_world
 # The reference's unmodified benchmark.cpp (and a plain MPI test program) built against compat/mpi_mod.hpp +

@@ -2,8 +2,12 @@
 #include "../core/dispatch.h"
 namespace ft {
 bool host_run_g1(int, int, int, bool, const StagedArgs*, int);
-#ifdef FT_ONLY_F32  // sanitizer builds compile one slice of the type matrix
+#ifdef FT_ONLY_F32  // sanitizer builds compile one slice of the type matrix (+ the 16-bit / fp8 wire slice on request)
+#ifdef FT_WITH_F16
+bool host_run_g2(int, int, int, bool, const StagedArgs*, int);
+#else
 static bool host_run_g2(int, int, int, bool, const StagedArgs*, int) { return false; }
+#endif
 static bool host_run_g4(int, int, int, bool, const StagedArgs*, int) { return false; }
 static bool host_run_g8(int, int, int, bool, const StagedArgs*, int) { return false; }
 static bool host_run_g16(int, int, int, bool, const StagedArgs*, int) { return false; }

@@ -43,6 +43,65 @@ static int run(int n, std::vector<int> widths, int algo, int mode, long long cou
   return bad;
 }
 
+// The two halves as collectives of their own (phases 1 and 2), fp32, checked against each other.
+static int run_halves(int n, std::vector<int> widths, long long per_rank, int ctas, long long tile, int algo) {
+  void* w = ft_host_world_create(n, 1 << 18, 1 << 18);
+  const long long total = per_rank * n;
+  std::vector<std::vector<float>> in(n, std::vector<float>(total + 8)), part(n, std::vector<float>(per_rank + 8)),
+      full(n, std::vector<float>(total + 8));
+  auto al = [](std::vector<float>& v) { return (float*)(((uintptr_t)v.data() + 15) & ~(uintptr_t)15); };
+  std::vector<const void*> s(n);
+  std::vector<void*> r(n);
+  for (int i = 0; i < n; ++i) {
+    for (long long j = 0; j < total; ++j) al(in[i])[j] = (float)(i + 1) * (float)(j % 5);
+    s[i] = al(in[i]);
+    r[i] = al(part[i]);
+  }
+  int bad = 0;
+  long long rc = ft_host_allreduce(w, s.data(), r.data(), total, 6, 6, 0, algo, widths.data(), (int)widths.size(), ctas, tile, 0,
+                                   1.0, 0, 20000000000ull, -1, 0, /*phases=*/1);
+  if (rc) { printf("rs rc=%lld\n", rc); bad = 1; }
+  for (int i = 0; i < n; ++i) {
+    s[i] = al(part[i]);
+    r[i] = al(full[i]);
+  }
+  rc = ft_host_allreduce(w, s.data(), r.data(), total, 6, 6, 0, algo, widths.data(), (int)widths.size(), ctas, tile, 0, 1.0, 0,
+                         20000000000ull, -1, 0, /*phases=*/2);
+  if (rc) { printf("ag rc=%lld\n", rc); bad = 1; }
+  const float tot = (float)n * (n + 1) / 2;
+  for (int i = 0; i < n; ++i)
+    for (long long j = 0; j < total; ++j)
+      if (al(full[i])[j] != tot * (float)(j % 5)) bad = 1;
+  ft_host_world_destroy(w);
+  printf("halves n=%d stages=%zu algo=%d per_rank=%lld: %s\n", n, widths.size(), algo, per_rank, bad ? "FAIL" : "ok");
+  return bad;
+}
+
+// fp32 data with a narrower wire (13 = bf16, 14 = block-scaled fp8) and the fused 1/N scale; small integers, so
+// that the expected value is exact in both wire formats.
+static int run_wire(int n, std::vector<int> widths, int wire, long long count, int ctas, long long tile) {
+  void* w = ft_host_world_create(n, 1 << 18, 1 << 18);
+  std::vector<std::vector<float>> buf(n, std::vector<float>(count + 8));
+  std::vector<const void*> s(n);
+  std::vector<void*> r(n);
+  for (int i = 0; i < n; ++i) {
+    float* base = (float*)(((uintptr_t)buf[i].data() + 15) & ~(uintptr_t)15);
+    for (long long j = 0; j < count; ++j) base[j] = (float)((j % 3) * n);  // sum = (j%3)*n*n, scaled by 1/n
+    s[i] = base;
+    r[i] = base;
+  }
+  int bad = 0;
+  long long rc = ft_host_allreduce(w, s.data(), r.data(), count, wire, 6, 0, 2, widths.data(), (int)widths.size(), ctas, tile, 0,
+                                   1.0 / n, 1, 20000000000ull, -1, 0, 0);
+  if (rc) { printf("wire rc=%lld\n", rc); bad = 1; }
+  for (int i = 0; i < n; ++i)
+    for (long long j = 0; j < count; ++j)
+      if (((float*)r[i])[j] != (float)((j % 3) * n)) bad = 1;
+  ft_host_world_destroy(w);
+  printf("wire=%d n=%d stages=%zu count=%lld: %s\n", wire, n, widths.size(), count, bad ? "FAIL" : "ok");
+  return bad;
+}
+
 int main() {
   int bad = 0;
   bad |= run(4, {2, 2}, 2, 0, 5000, 3, 256);
@@ -62,5 +121,13 @@ int main() {
   bad |= run(6, {2, 3}, 5, 0, 7000, 2, 512);
   bad |= run(8, {2, 2, 2}, 5, 1, 6000, 3, 256);
   bad |= run(4, {4}, 5, 0, 40000, 1, 4096);
+  // the halves (reduce-scatter / all-gather as collectives), per-vector text and bulk tiles
+  bad |= run_halves(6, {2, 3}, 1024, 2, 256, 2);
+  bad |= run_halves(4, {4}, 512, 3, 128, 5);
+#ifdef FT_WITH_F16
+  // narrower wire formats under fp32 user buffers, fused scale
+  bad |= run_wire(4, {2, 2}, 13, 4096, 2, 256);
+  bad |= run_wire(8, {2, 4}, 14, 4096, 3, 256);
+#endif
   return bad;
 }
