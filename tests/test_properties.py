@@ -70,3 +70,39 @@ def test_enumeration_matches_count(n):
         for x in wl:
             p *= x
         assert p == n or (n == 1 and wl == [])
+
+
+@settings(max_examples=40, deadline=None, suppress_health_check=[HealthCheck.too_slow])
+@given(plans(), st.integers(0, 2**31 - 1), st.sampled_from([np.float32, np.float64, np.int16, np.uint8]),
+       st.booleans(), st.booleans())
+def test_bulk_tiles_equal_per_vector_text(plan, seed, dtype, registered, scaled):
+    """The CPU's bulk tiles (algo 5, the TMA hook) against the per-vector text of the GPU kernels: same bits for any
+    plan, count (ragged ones fall back), tiling, dtype, private or registered buffers, with or without the scale."""
+    n, widths, count, ctas, tile = plan
+    rng = np.random.default_rng(seed)
+    dt = np.dtype(dtype)
+    if dt.kind == "f":
+        xs = [rng.standard_normal(count).astype(dt) for _ in range(n)]
+    else:
+        info = np.iinfo(dt)
+        xs = [rng.integers(info.min, info.max, count, dtype=dt, endpoint=True) for _ in range(n)]
+    scale = 0.25 if (scaled and dt.kind == "f") else None
+    res = []
+    for algo in ("stages", "stages_bulk"):
+        w = HostWorld(n, window_bytes=1 << 16)
+        bufs = []
+        for r, x in enumerate(xs):
+            if registered:
+                v = w.registered(r, count, dt)
+            else:
+                raw = np.empty(x.nbytes + 64, dtype=np.uint8)
+                off = (-raw.ctypes.data) % 16
+                v = raw[off:off + x.nbytes].view(dt)
+            v[:] = x
+            bufs.append(v)
+        mode = ft.ops.constants.MODE_REGISTERED if registered else ft.ops.constants.MODE_STAGING
+        assert w.allreduce(bufs, None, algo=algo, widths=widths, ctas=ctas, tile_bytes=tile, mode=mode, scale=scale) == 0
+        res.append([b.copy() for b in bufs])
+        w.close()
+    for a, b in zip(*res):
+        np.testing.assert_array_equal(a, b)
