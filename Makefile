@@ -31,7 +31,7 @@ HOST_OBJ := $(HOST_SRC:%.cc=$(B)/%.o)
 CUDA_OBJ := $(CUDA_SRC:%.cu=$(B)/%.cu.o)
 RT_CC_OBJ := $(RT_CC_SRC:%.cc=$(B)/%.o)
 
-.PHONY: all host cuda tools clean tsan fdtest memcheck racecheck dropin
+.PHONY: all host cuda tools clean tsan asan fdtest memcheck racecheck dropin
 all: host cuda tools
 host: $(B)/libflextree_host.so
 cuda: $(LIBDIR)/libflextree.so
@@ -75,6 +75,20 @@ tsan:
 	  tests/cpp/tsan_world.cc csrc/host/host_world.cc csrc/host/host_run_all.cc csrc/host/host_run_g1.cc csrc/host/host_run_g2.cc \
 	  csrc/planner/factorize.cc csrc/planner/cost_model.cc -lpthread
 	$(B)/tsan_world
+# AddressSanitizer + UBSan over the same CPU world and over the planner CLI
+asan:
+	$(CXX) -std=c++17 -O1 -g -fsanitize=address,undefined -fno-sanitize-recover=undefined -Wno-unknown-pragmas -Iinclude -DFT_ONLY_F32 -DFT_WITH_F16 \
+	  -o $(B)/asan_world tests/cpp/tsan_world.cc csrc/host/host_world.cc csrc/host/host_run_all.cc csrc/host/host_run_g1.cc \
+	  csrc/host/host_run_g2.cc csrc/planner/factorize.cc csrc/planner/cost_model.cc -lpthread
+	$(B)/asan_world
+	$(CXX) -std=c++17 -O1 -g -fsanitize=address,undefined -fno-sanitize-recover=undefined -Iinclude $(VERDEFS) -o $(B)/asan_plan csrc/tools/ft_plan.cc $(PLANNER_SRC)
+	$(B)/asan_plan --sweep --max 300 --out /dev/null > /dev/null
+	$(B)/asan_plan --candidates 7 > /dev/null
+	$(B)/asan_plan --print-ops --widths 2,3,2 --rank 5 > /dev/null
+	$(B)/asan_plan --print-ops --widths 2,3 --rank 6 --lonely 1 > /dev/null
+	$(B)/asan_plan --legacy 24 --chunk 100 > /dev/null
+	$(B)/asan_plan --choose 8 --bytes 1048576 --nvls > /dev/null
+	$(B)/asan_plan --enumerate 64 --legacy-flat > /dev/null
 # The reference's unmodified benchmark.cpp (and a plain MPI test program) built against compat/mpi_mod.hpp +
 # libflextree_host.so + the in-repo MPI subset -> baseline/_ref/bin/{allreduce_over_mpi_dropin,dropin_user}
 dropin: host

@@ -47,3 +47,19 @@ def torch_dtype_code(dt):
 
 
 __all__ = [n for n in dir() if n.isupper()] + ["torch_dtype_code"]
+
+
+def default_wire(dt, op, env=None):
+    """Wire dtype code when the caller passes none: the environment variable FT_WIRE =
+    ``native`` (default: the tensor's own dtype), ``bf16`` (fp32 tensors travel as bf16) or ``fp8`` (fp32 and bf16
+    tensors travel as block-scaled e4m3). Narrow wires are lossy, so they only ever apply to floating-point SUM."""
+    import os
+    v = (os.environ if env is None else env).get("FT_WIRE", "native").strip().lower()
+    opc = OPS[op] if isinstance(op, str) else int(op)
+    if opc != OPS["sum"] or v in ("", "native"):
+        return dt
+    if v == "bf16":
+        return BFLOAT16 if dt == FLOAT else dt
+    if v in ("fp8", "fp8-block16", "fp8_block"):
+        return FP8_BLOCK if dt in (FLOAT, BFLOAT16) else dt
+    raise ValueError(f"FT_WIRE={v!r}: expected native, bf16 or fp8")

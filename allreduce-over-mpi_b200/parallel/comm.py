@@ -228,9 +228,9 @@ class Communicator:
         return C.c_void_p(s.cuda_stream)
 
     @staticmethod
-    def _wire_code(dt, wire_dtype):
+    def _wire_code(dt, wire_dtype, op="sum"):
         if wire_dtype is None:
-            return dt
+            return K.default_wire(dt, op)  # FT_WIRE, default native
         if isinstance(wire_dtype, str):
             if wire_dtype in ("fp8", "fp8-block16", "fp8_block"):
                 return K.FP8_BLOCK  # opt-in block-scaled e4m3 wire
@@ -250,7 +250,7 @@ class Communicator:
         if out.dtype != tensor.dtype or out.numel() != tensor.numel():
             raise ValueError("out must match the input dtype/size")
         dt = K.torch_dtype_code(tensor.dtype)
-        wt = self._wire_code(dt, wire_dtype)
+        wt = self._wire_code(dt, wire_dtype, op)
         opc = K.OPS[op] if isinstance(op, str) else int(op)
         # (the native call selects the communicator's device itself; no torch device context on the hot path)
         rc = self._L.ft_allreduce_ex(tensor.data_ptr(), out.data_ptr(), tensor.numel(),
@@ -266,7 +266,7 @@ class Communicator:
             raise ValueError("need one tensor per emulated rank")
         outs = tensors if outs is None else outs
         dt = K.torch_dtype_code(tensors[0].dtype)
-        wt = self._wire_code(dt, wire_dtype)
+        wt = self._wire_code(dt, wire_dtype, op)
         opc = K.OPS[op] if isinstance(op, str) else int(op)
         s = (C.c_void_p * n)(*[t.data_ptr() for t in tensors])
         r = (C.c_void_p * n)(*[t.data_ptr() for t in outs])

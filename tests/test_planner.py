@@ -210,3 +210,20 @@ def test_legacy_enumerator_getwidth2_sets():
     assert len(ft.enumerate_widths(12, True)) == 9
     # no 9-stage limit here (getWidth2 caps the depth at 9): 2^12 has a 12-stage tree
     assert [2] * 12 in ft.enumerate_widths(4096)
+
+
+def test_ft_wire_environment_default():
+    """FT_WIRE: default wire format of the torch path when the caller passes none."""
+    from flextree.ops import constants as K
+    assert K.default_wire(K.FLOAT, "sum", {}) == K.FLOAT
+    assert K.default_wire(K.FLOAT, "sum", {"FT_WIRE": "native"}) == K.FLOAT
+    assert K.default_wire(K.FLOAT, "sum", {"FT_WIRE": "bf16"}) == K.BFLOAT16
+    assert K.default_wire(K.BFLOAT16, "sum", {"FT_WIRE": "bf16"}) == K.BFLOAT16
+    assert K.default_wire(K.INT32, "sum", {"FT_WIRE": "bf16"}) == K.INT32          # integers are never narrowed
+    assert K.default_wire(K.FLOAT, "max", {"FT_WIRE": "bf16"}) == K.FLOAT          # only SUM
+    assert K.default_wire(K.FLOAT, "sum", {"FT_WIRE": "fp8"}) == K.FP8_BLOCK
+    assert K.default_wire(K.BFLOAT16, "sum", {"FT_WIRE": "fp8"}) == K.FP8_BLOCK
+    assert K.default_wire(K.DOUBLE, "sum", {"FT_WIRE": "fp8"}) == K.DOUBLE
+    import pytest
+    with pytest.raises(ValueError):
+        K.default_wire(K.FLOAT, "sum", {"FT_WIRE": "int4"})
