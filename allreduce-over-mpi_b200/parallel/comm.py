@@ -10,6 +10,7 @@ The reference's only "API" is MPI_Allreduce(sendbuf, recvbuf, count, datatype, o
 the fused scale/cast the DDP path needs.
 """
 import ctypes as C
+import os
 
 import torch
 
@@ -17,6 +18,7 @@ from .. import _lib
 from ..ops import constants as K
 
 _AG_FN = C.CFUNCTYPE(C.c_int, C.c_void_p, C.c_void_p, C.c_void_p, C.c_size_t)
+_NVTX = os.environ.get("FT_NVTX") == "1"
 
 
 class CommOptions(C.Structure):
@@ -253,8 +255,12 @@ class Communicator:
         wt = self._wire_code(dt, wire_dtype, op)
         opc = K.OPS[op] if isinstance(op, str) else int(op)
         # (the native call selects the communicator's device itself; no torch device context on the hot path)
+        if _NVTX:  # FT_NVTX=1: one range per call for nsys / ncu timelines
+            torch.cuda.nvtx.range_push(f"flextree.allreduce {tensor.numel() * tensor.element_size()} B")
         rc = self._L.ft_allreduce_ex(tensor.data_ptr(), out.data_ptr(), tensor.numel(),
                                      dt, wt, opc, float(scale), self._h, self._stream(stream))
+        if _NVTX:
+            torch.cuda.nvtx.range_pop()
         if rc:
             _check(self._L, rc, "ft_allreduce")
         return out
