@@ -19,6 +19,10 @@ class HostWorld:
             raise ValueError("bad world size")
         self.window_bytes = window_bytes
 
+    def set_jitter(self, permille):
+        """Tests: random 0-200 us sleeps at flag publications / acquisitions / syncs of every CPU "CTA" (process-wide)."""
+        self._L.ft_host_set_jitter(int(permille))
+
     def close(self):
         if self._h:
             self._L.ft_host_world_destroy(self._h)

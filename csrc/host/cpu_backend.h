@@ -12,6 +12,26 @@
 
 namespace ft {
 
+// Stress knob (tests only): with probability permille/1000 a thread sleeps 0-200 us before publishing a flag, after
+// acquiring one and at every CTA-wide sync - the schedule perturbation that exposes a missing wait, a buffer reused
+// too early or an exit barrier that lets a slow reader be overrun (SURVEY 5.2 "randomized delays").
+inline int& host_jitter_permille() {
+  static int v = 0;
+  return v;
+}
+inline void host_jitter() {
+  const int pm = host_jitter_permille();
+  if (pm <= 0) return;
+  static thread_local uint64_t x = 0x9E3779B97F4A7C15ull ^ (uint64_t)(uintptr_t)&x;
+  x ^= x << 13;
+  x ^= x >> 7;
+  x ^= x << 17;
+  if ((int)(x % 1000) < pm) {
+    timespec ts = {0, (long)((x >> 20) % 200000)};
+    nanosleep(&ts, nullptr);
+  }
+}
+
 struct CpuBE {
   static constexpr bool kTma = false;  // no cp.async.bulk here ...
   // ... but the same hook (StagedCta::run<true>) has a CPU meaning: "bulk" tiles. The GPU text gives one
@@ -122,13 +142,19 @@ struct CpuBE {
   int abort_ = 0;
   int tid() const { return 0; }
   int nthr() const { return 1; }
-  void sync() {}
+  void sync() { host_jitter(); }
   template <int B> static void ld(void* dst, const void* src, bool /*remote*/) { memcpy(dst, src, B); }
   template <int B> static void st(void* dst, const void* src) { memcpy(dst, src, B); }
   uint64_t flag_ld(const uint64_t* p) { return __atomic_load_n(p, __ATOMIC_ACQUIRE); }
-  void flag_st(uint64_t* p, uint64_t v) { __atomic_store_n(p, v, __ATOMIC_RELEASE); }
+  void flag_st(uint64_t* p, uint64_t v) {
+    host_jitter();
+    __atomic_store_n(p, v, __ATOMIC_RELEASE);
+  }
   void fence() { __atomic_thread_fence(__ATOMIC_SEQ_CST); }
-  void acquire(const uint64_t* p) { (void)__atomic_load_n(p, __ATOMIC_ACQUIRE); }
+  void acquire(const uint64_t* p) {
+    (void)__atomic_load_n(p, __ATOMIC_ACQUIRE);
+    host_jitter();
+  }
   uint64_t load_epoch(const uint64_t* p) { return __atomic_load_n(p, __ATOMIC_ACQUIRE); }
   unsigned err_ld(const unsigned* p) { return __atomic_load_n(p, __ATOMIC_RELAXED); }
   void err_set(unsigned* p, unsigned v) {

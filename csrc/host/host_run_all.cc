@@ -1,5 +1,6 @@
 #include "../core/comm_dev.h"
 #include "../core/dispatch.h"
+#include "cpu_backend.h"
 namespace ft {
 bool host_run_g1(int, int, int, bool, const StagedArgs*, int);
 #ifdef FT_ONLY_F32  // sanitizer builds compile one slice of the type matrix (+ the 16-bit / fp8 wire slice on request)
@@ -28,3 +29,7 @@ bool host_run_group(int group, int dtype, int io_dtype, int op, bool vec, const 
   return false;
 }
 }  // namespace ft
+
+// Tests only: probability (per mille) of a random 0-200 us sleep at every flag publication / acquisition / CTA sync
+// of the CPU back end. 0 = off (default).
+extern "C" void ft_host_set_jitter(int permille) { ft::host_jitter_permille() = permille < 0 ? 0 : permille; }

@@ -106,6 +106,19 @@ def main():
     piece[:] = src.numpy()
     comm.allreduce(piece, registered=True)
     assert np.allclose(piece, ref.numpy(), rtol=1e-5, atol=1e-5)
+    # randomized delays around back-to-back registered calls whose buffer is refilled right after each
+    # return: without the exit barrier of registered mode a slow peer would read the next iteration's input
+    ft._lib.load().ft_host_set_jitter(120)
+    for it in range(25):
+        src = torch.full((3000,), float(it + 1)) + rank
+        v = comm.registered(3000, np.float32)
+        v[:] = src.numpy()
+        comm.allreduce(v, registered=True, widths=ft.enumerate_widths(world)[it % len(ft.enumerate_widths(world))],
+                       ctas=1 + it % 2, tile_bytes=1024)
+        want = world * (it + 1) + world * (world - 1) / 2
+        assert np.all(v == want), (it, v[:4], want)
+        v[:] = -1e9  # the next input arrives immediately
+    ft._lib.load().ft_host_set_jitter(0)
     # the halves
     per = 257
     x = torch.randn(per * world, generator=g)

@@ -565,3 +565,36 @@ def test_bulk_tiles_reduce_scatter_and_all_gather_halves(n, widths):
     assert w.allreduce(ref, None, widths=widths) == 0
     for r in range(n):
         np.testing.assert_array_equal(full[r], ref[r])
+
+
+def test_randomized_delays_stress():
+    """random sleeps before every flag publication, after every acquisition and at every CTA sync, over
+    back-to-back calls that change size, plan, algorithm and buffer kind: a missing wait, a window reused too early
+    or a leaky exit barrier shows up as a wrong sum."""
+    n = 6
+    w = HostWorld(n, window_bytes=1 << 16, ll_bytes=1 << 16)
+    w.set_jitter(150)
+    try:
+        rng = np.random.default_rng(7)
+        plans = [("stages", [2, 3]), ("stages_bulk", [3, 2]), ("stages", [6]), ("ring", None), ("nvls", None),
+                 ("oneshot", None), ("stages_bulk", [6])]
+        for it in range(28):
+            algo, widths = plans[it % len(plans)]
+            count = int(rng.integers(1, 3000)) if algo != "oneshot" else int(rng.integers(1, 600))
+            registered = algo in ("stages", "stages_bulk", "ring") and it % 3 == 0
+            xs = [rng.integers(-1000, 1000, count).astype(np.int32) for _ in range(n)]
+            if registered:
+                bufs = [w.registered(r, count, np.int32) for r in range(n)]
+                for b, x in zip(bufs, xs):
+                    b[:] = x
+            else:
+                bufs = [aligned_copy(x) for x in xs]
+            rc = w.allreduce(bufs, None, algo=algo, widths=widths, ctas=1 + it % 3, tile_bytes=[64, 256, 1024][it % 3],
+                             mode=K.MODE_REGISTERED if registered else K.MODE_STAGING)
+            assert rc == 0, (it, algo, rc)
+            want = np.sum(np.stack(xs), 0, dtype=np.int32)
+            for r in range(n):
+                np.testing.assert_array_equal(bufs[r], want, err_msg=f"iteration {it} {algo} {widths} rank {r}")
+    finally:
+        w.set_jitter(0)
+        w.close()
