@@ -107,18 +107,27 @@ def main():
     comm.allreduce(piece, registered=True)
     assert np.allclose(piece, ref.numpy(), rtol=1e-5, atol=1e-5)
     # randomized delays around back-to-back registered calls whose buffer is refilled right after each
-    # return: without the exit barrier of registered mode a slow peer would read the next iteration's input
-    ft._lib.load().ft_host_set_jitter(120)
-    for it in range(25):
-        src = torch.full((3000,), float(it + 1)) + rank
+    # return, with ranks entering at different times: without the entry waits a fast rank would reduce a peer's
+    # stale buffer, without the exit barriers a slow peer would read the next iteration's input or a rank would
+    # return before its peers' stores have landed. (Mutation-checked against staged_core.h.)
+    import random
+    import time
+    lib = ft._lib.load()
+    lib.ft_host_set_jitter(120)
+    rnd = random.Random(1000 + rank)
+    all_widths = ft.enumerate_widths(world)
+    for it in range(36):
+        algo = ("stages", "nvls", "ring", "stages_bulk")[it % 4]
         v = comm.registered(3000, np.float32)
-        v[:] = src.numpy()
-        comm.allreduce(v, registered=True, widths=ft.enumerate_widths(world)[it % len(ft.enumerate_widths(world))],
-                       ctas=1 + it % 2, tile_bytes=1024)
+        if rnd.random() < 0.5:
+            time.sleep(rnd.random() * 2e-3)  # late to the call: my buffer still holds the poison below
+        v[:] = float(it + 1) + rank
+        comm.allreduce(v, algo=algo, registered=True, widths=all_widths[it % len(all_widths)], ctas=1 + it % 2,
+                       tile_bytes=1024)
         want = world * (it + 1) + world * (world - 1) / 2
-        assert np.all(v == want), (it, v[:4], want)
-        v[:] = -1e9  # the next input arrives immediately
-    ft._lib.load().ft_host_set_jitter(0)
+        assert np.all(v == want), (it, algo, v[:4], want)
+        v[:] = -1e9  # poison: the next input arrives immediately
+    lib.ft_host_set_jitter(0)
     # the halves
     per = 257
     x = torch.randn(per * world, generator=g)

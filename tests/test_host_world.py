@@ -570,18 +570,22 @@ def test_bulk_tiles_reduce_scatter_and_all_gather_halves(n, widths):
 def test_randomized_delays_stress():
     """random sleeps before every flag publication, after every acquisition and at every CTA sync, over
     back-to-back calls that change size, plan, algorithm and buffer kind: a missing wait, a window reused too early
-    or a leaky exit barrier shows up as a wrong sum."""
+    or a leaky exit barrier shows up as a wrong sum. (Mutation-checked: removing any single wait of staged_core.h
+    that an in-process world can observe makes this test fail.)"""
     n = 6
     w = HostWorld(n, window_bytes=1 << 16, ll_bytes=1 << 16)
     w.set_jitter(150)
     try:
         rng = np.random.default_rng(7)
-        plans = [("stages", [2, 3]), ("stages_bulk", [3, 2]), ("stages", [6]), ("ring", None), ("nvls", None),
-                 ("oneshot", None), ("stages_bulk", [6])]
-        for it in range(28):
-            algo, widths = plans[it % len(plans)]
+        # (algorithm, widths, lonely ranks, registered buffers?, threads per rank)
+        plans = [("stages", [2, 3], 0, False, 2), ("stages_bulk", [3, 2], 0, True, 1), ("stages", [6], 0, True, 3),
+                 ("ring", None, 0, False, 2), ("nvls", None, 0, False, 2), ("oneshot", None, 0, False, 1),
+                 ("stages_bulk", [6], 0, False, 3), ("nvls", None, 0, True, 2), ("nvls", None, 0, False, 5),
+                 ("stages", [5], 1, False, 2), ("ring", None, 0, True, 1), ("stages", [2, 2], 2, False, 3),
+                 ("nvls", None, 0, False, 8)]
+        for it in range(2 * len(plans)):
+            algo, widths, lonely, registered, ctas = plans[it % len(plans)]
             count = int(rng.integers(1, 3000)) if algo != "oneshot" else int(rng.integers(1, 600))
-            registered = algo in ("stages", "stages_bulk", "ring") and it % 3 == 0
             xs = [rng.integers(-1000, 1000, count).astype(np.int32) for _ in range(n)]
             if registered:
                 bufs = [w.registered(r, count, np.int32) for r in range(n)]
@@ -589,10 +593,22 @@ def test_randomized_delays_stress():
                     b[:] = x
             else:
                 bufs = [aligned_copy(x) for x in xs]
-            rc = w.allreduce(bufs, None, algo=algo, widths=widths, ctas=1 + it % 3, tile_bytes=[64, 256, 1024][it % 3],
-                             mode=K.MODE_REGISTERED if registered else K.MODE_STAGING)
+            dt_kw = {}
+            if algo == "nvls":  # the in-switch reduce exists for floats; small integers in fp32 are exact
+                xs = [x.astype(np.float32) for x in xs]
+                if registered:
+                    bufs = [w.registered(r, count, np.float32) for r in range(n)]
+                    for b, x in zip(bufs, xs):
+                        b[:] = x
+                else:
+                    bufs = [aligned_copy(x) for x in xs]
+            tile = [64, 256, 1024][it % 3]
+            if algo == "nvls" and not registered:
+                tile = 1024  # one flag slot per tile: keep ntiles <= FT_MAX_CTAS
+            rc = w.allreduce(bufs, None, algo=algo, widths=widths, ctas=ctas, tile_bytes=tile, lonely=lonely,
+                             mode=K.MODE_REGISTERED if registered else K.MODE_STAGING, **dt_kw)
             assert rc == 0, (it, algo, rc)
-            want = np.sum(np.stack(xs), 0, dtype=np.int32)
+            want = np.sum(np.stack(xs), 0, dtype=xs[0].dtype)
             for r in range(n):
                 np.testing.assert_array_equal(bufs[r], want, err_msg=f"iteration {it} {algo} {widths} rank {r}")
     finally:
