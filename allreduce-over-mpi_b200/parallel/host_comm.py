@@ -141,16 +141,16 @@ class HostCommunicator:
                    K.MODE_REGISTERED if registered else K.MODE_STAGING, scale, lonely, 0, timeout_s)
         return out if out is not None else x
 
-    def reduce_scatter(self, x, out, op="sum", widths=None, ctas=2, tile_bytes=16384):
+    def reduce_scatter(self, x, out, op="sum", widths=None, ctas=1, tile_bytes=262144):
         a, code = self._as_numpy(x)
         o, _ = self._as_numpy(out)
-        self._call(a.ctypes.data, o.ctypes.data, a.size, code, code, op, "stages", widths, ctas, tile_bytes,
+        self._call(a.ctypes.data, o.ctypes.data, a.size, code, code, op, "stages_bulk", widths, ctas, tile_bytes,
                    K.MODE_STAGING, None, 0, 1, 30.0)
         return out
 
-    def all_gather(self, x, out, widths=None, ctas=2, tile_bytes=16384):
+    def all_gather(self, x, out, widths=None, ctas=1, tile_bytes=262144):
         a, code = self._as_numpy(x)
         o, _ = self._as_numpy(out)
-        self._call(a.ctypes.data, o.ctypes.data, o.size, code, code, "sum", "stages", widths, ctas, tile_bytes,
+        self._call(a.ctypes.data, o.ctypes.data, o.size, code, code, "sum", "stages_bulk", widths, ctas, tile_bytes,
                    K.MODE_STAGING, None, 0, 2, 30.0)
         return out
