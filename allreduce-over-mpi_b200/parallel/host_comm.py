@@ -14,12 +14,16 @@ _AG_FN = C.CFUNCTYPE(C.c_int, C.c_void_p, C.c_void_p, C.c_void_p, C.c_size_t)
 
 
 class HostCommunicator:
-    def __init__(self, group=None, window_bytes=8 << 20, ll_bytes=1 << 20):
+    def __init__(self, group=None, window_bytes=8 << 20, ll_bytes=1 << 20, max_phantoms=0):
+        """``max_phantoms`` > 0 makes room for "-k" trees: ``allreduce(x, widths=[2, 2, 2], lonely=-1)`` on 7 ranks runs
+        the 8-position tree with one phantom rank (hosted by rank 0, contributing the identity) - the shapes
+        cost_model/ChooseWidth.h:16-22 proposes for prime world sizes."""
         import torch.distributed as dist
         self._L = L = _lib.load()
         vp, i32, i64 = C.c_void_p, C.c_int, C.c_longlong
-        L.ft_host_comm_create.restype = i32
-        L.ft_host_comm_create.argtypes = [C.POINTER(vp), i32, i32, vp, vp, C.c_size_t, C.c_size_t]
+        L.ft_host_comm_create_ex.restype = i32
+        L.ft_host_comm_create_ex.argtypes = [C.POINTER(vp), i32, i32, vp, vp, C.c_size_t, C.c_size_t, i32]
+        self.max_phantoms = int(max_phantoms)
         L.ft_host_comm_destroy.argtypes = [vp]
         L.ft_host_comm_registered.restype = vp
         L.ft_host_comm_registered.argtypes = [vp]
@@ -54,8 +58,8 @@ class HostCommunicator:
 
     def _create(self, window_bytes):
         L, vp = self._L, C.c_void_p
-        rc = L.ft_host_comm_create(C.byref(self._h), self.rank, self.size, C.cast(self._cb, vp), None, window_bytes,
-                                   self._ll_bytes)
+        rc = L.ft_host_comm_create_ex(C.byref(self._h), self.rank, self.size, C.cast(self._cb, vp), None, window_bytes,
+                                      self._ll_bytes, self.max_phantoms)
         if rc:
             raise RuntimeError(f"ft_host_comm_create failed ({rc}): {L.ft_last_error().decode()}")
         self.window_bytes = window_bytes

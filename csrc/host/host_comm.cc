@@ -15,6 +15,8 @@
 #include <time.h>
 #include <unistd.h>
 
+#include <limits>
+#include <memory>
 #include <string>
 #include <vector>
 
@@ -41,6 +43,22 @@ struct ft_host_comm {
   uint64_t epoch = 0, calls = 0;
   size_t board_off = 0;  // agreement board: FT_MAX_RANKS 64-bit slots in the spare page behind the windows
   unsigned done = 0, err = 0;
+  // "-k" trees (cost_model/ChooseWidth.h:16-22 lists the trees of N+1 as candidates for N ranks): a tree with k more
+  // positions than there are processes. Phantom j (logical rank N+j) is hosted by process j % N: it has its own
+  // windows / pad / LL in slot 1 + j / N of that process's segment, its own epoch, and runs as a second logical rank
+  // of the host's call with the operation's identity as input.
+  int phantoms = 0, slots = 1;
+  size_t slot_bytes = 0;
+  struct Phantom {
+    CommDev cd;
+    uint64_t epoch = 0;
+    unsigned done = 0, err = 0;
+  };
+  std::vector<std::unique_ptr<Phantom>> hosted;  // phantoms this process runs, ascending j
+  std::vector<int> hosted_id;                    // their j
+  std::vector<char> ident, sink;                 // identity input / discarded output of the hosted phantoms
+  long long ident_count = -1;
+  int ident_dtype = -1, ident_op = -1;
   bool allgather(const void* s, void* r, size_t n) const {
     if (nranks == 1) { memcpy(r, s, n); return true; }
     return ag && ag(ctx, s, r, n) == 0;
@@ -85,6 +103,35 @@ static int agree(ft_host_comm* c, char* bit, uint32_t payload, unsigned long lon
   return same ? 1 : 2;
 }
 
+// The operation's identity in the user's element type: what a phantom rank contributes.
+template <typename T> static void fill_n(void* buf, long long n, T v) {
+  T* p = (T*)buf;
+  for (long long i = 0; i < n; ++i) p[i] = v;
+}
+static bool fill_identity(void* buf, long long n, int dtype, int op) {
+  const size_t bytes = (size_t)n * (size_t)dtype_size(dtype);
+  if (op == OP_SUM || op == OP_BOR) { memset(buf, 0, bytes); return true; }
+  if (op == OP_BAND) { memset(buf, 0xFF, bytes); return true; }
+  if (op != OP_MAX && op != OP_MIN) return false;
+  const bool mx = op == OP_MAX;  // identity of MAX is the lowest value, of MIN the highest
+  switch (dtype) {
+    case DT_UINT8: fill_n<uint8_t>(buf, n, mx ? 0 : 0xFF); return true;
+    case DT_BOOL: fill_n<uint8_t>(buf, n, mx ? 0 : 1); return true;
+    case DT_INT8: fill_n<int8_t>(buf, n, mx ? INT8_MIN : INT8_MAX); return true;
+    case DT_UINT16: fill_n<uint16_t>(buf, n, mx ? 0 : 0xFFFF); return true;
+    case DT_INT16: fill_n<int16_t>(buf, n, mx ? INT16_MIN : INT16_MAX); return true;
+    case DT_INT32: fill_n<int32_t>(buf, n, mx ? INT32_MIN : INT32_MAX); return true;
+    case DT_UINT32: fill_n<uint32_t>(buf, n, mx ? 0u : 0xFFFFFFFFu); return true;
+    case DT_INT64: case DT_LONG_LONG: fill_n<int64_t>(buf, n, mx ? INT64_MIN : INT64_MAX); return true;
+    case DT_UINT64: fill_n<uint64_t>(buf, n, mx ? 0ull : ~0ull); return true;
+    case DT_FLOAT: fill_n<float>(buf, n, mx ? -std::numeric_limits<float>::infinity() : std::numeric_limits<float>::infinity()); return true;
+    case DT_DOUBLE: fill_n<double>(buf, n, mx ? -std::numeric_limits<double>::infinity() : std::numeric_limits<double>::infinity()); return true;
+    case DT_HALF: fill_n<uint16_t>(buf, n, mx ? 0xFC00 : 0x7C00); return true;      // -inf / +inf
+    case DT_BFLOAT16: fill_n<uint16_t>(buf, n, mx ? 0xFF80 : 0x7F80); return true;  // -inf / +inf
+  }
+  return false;
+}
+
 static std::string shm_name(unsigned long long token, int rank) {
   char buf[96];
   snprintf(buf, sizeof buf, "/flextree.%llx.%d", token, rank);
@@ -95,7 +142,13 @@ extern "C" {
 
 ft_result_t ft_host_comm_create(ft_host_comm** out, int rank, int nranks, ft_allgather_fn ag, void* ctx,
                                 size_t window_bytes, size_t ll_bytes) {
-  if (!out || nranks < 1 || nranks > FT_MAX_RANKS || rank < 0 || rank >= nranks || (nranks > 1 && !ag)) {
+  return ft_host_comm_create_ex(out, rank, nranks, ag, ctx, window_bytes, ll_bytes, 0);
+}
+
+ft_result_t ft_host_comm_create_ex(ft_host_comm** out, int rank, int nranks, ft_allgather_fn ag, void* ctx,
+                                   size_t window_bytes, size_t ll_bytes, int max_phantoms) {
+  if (!out || nranks < 1 || nranks > FT_MAX_RANKS || rank < 0 || rank >= nranks || (nranks > 1 && !ag) ||
+      max_phantoms < 0 || nranks + max_phantoms > FT_MAX_RANKS) {
     set_last_error("ft_host_comm_create: bad arguments");
     return FT_ERR_INVALID;
   }
@@ -109,7 +162,10 @@ ft_result_t ft_host_comm_create(ft_host_comm** out, int rank, int nranks, ft_all
   c->seg_bytes = 3 * c->win_bytes + 4096;  // [parity 0 | parity 1 | registered]
   c->board_off = 3 * c->win_bytes;
   const size_t pad_off = c->seg_bytes, ll_off = pad_off + ((FT_PAD_BYTES + 4095) & ~(size_t)4095);
-  c->total_bytes = ll_off + 2 * c->ll_bytes + 4096;
+  c->slot_bytes = ll_off + 2 * c->ll_bytes + 4096;
+  c->phantoms = max_phantoms;
+  c->slots = 1 + (max_phantoms + nranks - 1) / nranks;  // slot 0 = the process itself, then the phantoms it may host
+  c->total_bytes = c->slot_bytes * (size_t)c->slots;
 
   unsigned long long tok = 0;
   if (rank == 0) {
@@ -152,17 +208,36 @@ ft_result_t ft_host_comm_create(ft_host_comm** out, int rank, int nranks, ft_all
   memset(&c->cd, 0, sizeof c->cd);
   c->cd.rank = rank;
   c->cd.nranks = nranks;
-  c->win_table.resize((size_t)nranks);
-  for (int p = 0; p < nranks; ++p) {
-    c->win_table[(size_t)p] = c->maps[(size_t)p];
-    c->cd.pad[p] = (uint64_t*)(c->maps[(size_t)p] + pad_off);
-    c->cd.ll[p] = c->maps[(size_t)p] + ll_off;
+  // logical rank L: processes first, then phantom j = L - nranks in slot 1 + j / nranks of process j % nranks
+  const int logical = nranks + max_phantoms;
+  auto base_of = [&](int L) {
+    return L < nranks ? c->maps[(size_t)L] : c->maps[(size_t)((L - nranks) % nranks)] + c->slot_bytes * (size_t)(1 + (L - nranks) / nranks);
+  };
+  c->win_table.resize((size_t)logical);
+  for (int p = 0; p < logical; ++p) {
+    c->win_table[(size_t)p] = base_of(p);
+    c->cd.pad[p] = (uint64_t*)(base_of(p) + pad_off);
+    c->cd.ll[p] = base_of(p) + ll_off;
+  }
+  for (int j = rank; j < max_phantoms; j += nranks) {
+    std::unique_ptr<ft_host_comm::Phantom> ph(new ft_host_comm::Phantom);
+    ph->cd = c->cd;  // same tables (rank / counters patched below, after c->cd is complete)
+    c->hosted.push_back(std::move(ph));
+    c->hosted_id.push_back(j);
   }
   c->cd.epoch = &c->epoch;
   c->cd.done = &c->done;
   c->cd.err = &c->err;
   c->cd.ll_bytes = c->ll_bytes;
   c->cd.trace = nullptr;
+  for (size_t i = 0; i < c->hosted.size(); ++i) {
+    ft_host_comm::Phantom& ph = *c->hosted[i];
+    ph.cd = c->cd;
+    ph.cd.rank = nranks + c->hosted_id[i];
+    ph.cd.epoch = &ph.epoch;
+    ph.cd.done = &ph.done;
+    ph.cd.err = &ph.err;
+  }
   *out = c;
   return FT_SUCCESS;
 }
@@ -199,14 +274,21 @@ long long ft_host_comm_allreduce(ft_host_comm* c, const void* send, void* recv, 
     if (send != recv) memcpy(recv, send, (size_t)count * (size_t)dtype_size(io_dtype));
     return 0;
   }
+  int phant = 0;  // lonely < 0: a "-k" tree, k phantom positions beyond the processes
+  if (lonely < 0) {
+    phant = -lonely;
+    lonely = 0;
+  }
   if (algo == ALGO_RING || algo == ALGO_NVLS || algo == ALGO_ONESHOT) {
     int flat = N;
     if (!make_plan(&flat, 1, &a.plan)) return -1;
     lonely = 0;
+    if (phant) return -14;
   } else if (!make_plan(widths, nstages, &a.plan)) {
     return -1;
   }
-  if (lonely < 0 || a.plan.nranks + lonely != N) return -2;
+  if (a.plan.nranks + lonely - phant != N) return -2;
+  if (phant && (phant > c->phantoms || mode != MODE_STAGING || phases != PHASES_ALLREDUCE || dtype == DT_FP8_BLOCK)) return -14;
   if (lonely > 0 && (algo != ALGO_STAGED || mode != MODE_STAGING)) return -8;
   if (phases != PHASES_ALLREDUCE && (algo != ALGO_STAGED || lonely > 0 || mode != MODE_STAGING || count % N)) return -10;
   if (dtype == DT_FP8_BLOCK && (algo != ALGO_STAGED || lonely > 0 || mode != MODE_STAGING)) return -9;
@@ -256,7 +338,37 @@ long long ft_host_comm_allreduce(ft_host_comm* c, const void* send, void* recv, 
   a.rc[0].recv = recv;
   a.rc[0].win = c->win_table.data();
   a.rc[0].mc = nullptr;
+  // the phantoms this process hosts ride along as further logical ranks of the same call
+  if (phant) {
+    const size_t bytes = ((size_t)count * (size_t)ios + 15) & ~(size_t)15;
+    size_t live = 0;
+    for (int j : c->hosted_id) live += j < phant ? 1 : 0;
+    if (live && (c->ident_count != count || c->ident_dtype != io_dtype || c->ident_op != op)) {
+      c->ident.assign(bytes + 16, 0);
+      if (!fill_identity(c->ident.data() + ((16 - (uintptr_t)c->ident.data() % 16) % 16), count, io_dtype, op)) return -7;
+      c->ident_count = count;
+      c->ident_dtype = io_dtype;
+      c->ident_op = op;
+    }
+    if (live && c->sink.size() < live * bytes + 16) c->sink.resize(live * bytes + 16);
+    size_t k = 0;
+    for (size_t i = 0; i < c->hosted.size(); ++i) {
+      if (c->hosted_id[i] >= phant) continue;
+      RankCall& rc = a.rc[a.nlocal++];
+      rc.comm = &c->hosted[i]->cd;
+      rc.send = c->ident.data() + ((16 - (uintptr_t)c->ident.data() % 16) % 16);
+      rc.recv = c->sink.data() + ((16 - (uintptr_t)c->sink.data() % 16) % 16) + (k++) * bytes;
+      rc.win = c->win_table.data();
+      rc.mc = nullptr;
+    }
+  }
   if (!host_run_group(dtype_group(dtype), dtype, io_dtype, op, vec != 0, &a, a.use_tma ? (int)ALGO_STAGED_TMA : algo)) return -7;
+  // every logical rank counts every call (flag values and the window parity derive from the epoch): the phantoms
+  // that sat this one out keep step with the ranks that ran it
+  for (size_t i = 0; i < c->hosted.size(); ++i)
+    if (c->hosted_id[i] >= phant) c->hosted[i]->epoch++;
+  for (auto& ph : c->hosted)
+    if (ph->err) return (long long)ph->err;
   return c->err ? (long long)c->err : 0;
 }
 

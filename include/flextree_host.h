@@ -22,6 +22,11 @@ typedef struct ft_host_comm ft_host_comm_t;
  * (LL) buffer, 0 = 1 MiB. */
 ft_result_t ft_host_comm_create(ft_host_comm_t** out, int rank, int nranks, ft_allgather_fn ag, void* ag_ctx,
                                 size_t window_bytes, size_t ll_bytes);
+/* Same, with room for up to max_phantoms phantom ranks: "-k" trees (cost_model/ChooseWidth.h:16-22 proposes the trees
+ * of N+1 for N ranks), run with lonely = -k in ft_host_comm_allreduce. Phantom j is hosted by process j % nranks as a
+ * second logical rank that contributes the operation's identity. Costs one more window set per hosting process. */
+ft_result_t ft_host_comm_create_ex(ft_host_comm_t** out, int rank, int nranks, ft_allgather_fn ag, void* ag_ctx,
+                                   size_t window_bytes, size_t ll_bytes, int max_phantoms);
 ft_result_t ft_host_comm_destroy(ft_host_comm_t* comm); /* collective */
 int ft_host_comm_rank(const ft_host_comm_t*);
 int ft_host_comm_size(const ft_host_comm_t*);
@@ -35,7 +40,9 @@ void* ft_host_comm_registered(ft_host_comm_t*);
  * widths[nstages]: the tree (product + lonely = world size); ignored by ring / one-shot / nvls. ctas = threads used
  * by this rank; tile_bytes = pipelining grain. mode: 0 = private buffers, 1 = `send == recv ==` registered region.
  * apply_scale: multiply the result by `scale` when a block becomes final (fused average). timeout_ns: watchdog,
- * 0 = wait forever. phases: 0 allreduce, 1 reduce-scatter (recv = my count/N block), 2 all-gather.
+ * 0 = wait forever. lonely: k > 0 = the last k ranks are outside the tree ("+k"), k < 0 = the tree has -k phantom
+ * positions beyond the ranks ("-k", needs create_ex). phases: 0 allreduce, 1 reduce-scatter (recv = my count/N block),
+ * 2 all-gather.
  * Returns 0, a negative argument error, or the watchdog word. */
 long long ft_host_comm_allreduce(ft_host_comm_t* comm, const void* send, void* recv, long long count, int dtype,
                                  int io_dtype, int op, int algo, const int* widths, int nstages, int ctas,

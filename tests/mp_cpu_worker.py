@@ -146,6 +146,32 @@ def main():
         ref = ref_sum(x.double()).float()
         comm.allreduce(x, widths=tree, lonely=lonely)
         assert torch.allclose(x, ref, rtol=1e-5, atol=1e-5)
+    # "-k" trees: more tree positions than ranks, the extra ones are phantom ranks hosted by the first processes
+    ph = ft.HostCommunicator(window_bytes=1 << 20, max_phantoms=2)
+    for k in (1, 2):
+        for widths in ft.enumerate_widths(world + k):
+            for algo in ("stages", "stages_bulk"):
+                x = torch.randn(4099 if algo == "stages" else 4096, generator=g)
+                ref = ref_sum(x.double()).float()
+                y = x.clone()
+                ph.allreduce(y, algo=algo, widths=widths, lonely=-k, ctas=2, tile_bytes=1024)
+                assert torch.allclose(y, ref, rtol=1e-5, atol=1e-5), (k, widths, algo)
+    xi = torch.randint(-1000, 1000, (3000,), generator=g, dtype=torch.int32)
+    for op, rop in (("max", dist.ReduceOp.MAX), ("min", dist.ReduceOp.MIN), ("band", dist.ReduceOp.BAND)):
+        y = xi.clone()
+        ph.allreduce(y, op=op, widths=ft.enumerate_widths(world + 1)[-1], lonely=-1)
+        assert torch.equal(y, ref_sum(xi, rop)), op
+    xf = torch.randn(2048, generator=g)
+    y = xf.clone()
+    ph.allreduce(y, op="min", widths=[world + 1], lonely=-1, scale=None)
+    assert torch.equal(y, ref_sum(xf, dist.ReduceOp.MIN))
+    try:
+        ph.allreduce(xf.clone(), widths=[world + 3], lonely=-3)  # more phantoms than the communicator has room for
+        raise AssertionError("must be refused")
+    except RuntimeError as e:
+        assert "-14" in str(e)
+    assert ph.error() == 0
+    ph.close()
     # grow-only staging (mpi_mod.hpp:932-950): a communicator created small re-creates its windows collectively
     small = ft.HostCommunicator(window_bytes=1 << 16)
     for count in (1000, 200000, 5000):
