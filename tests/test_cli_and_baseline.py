@@ -90,3 +90,17 @@ def test_public_header_is_c99_and_cxx11(tmp_path):
         r = subprocess.run(["gcc", "-std=c99", f"-I{inc}", f"-I{cuda_inc}", "-fsyntax-only",
                             os.path.join(ROOT, "examples", "c_local_allreduce.c")], capture_output=True, text=True)
         assert r.returncode == 0, r.stderr
+
+
+def test_launcher_front_end(tmp_path):
+    """python -m flextree.launch: the single-host stand-in for mpirun + hostfile (allreduce_over_mpi/Makefile:8-24)."""
+    from flextree import launch
+    cmd = launch.build_command(3, "x.py", ["--a", "1"], port=12345)
+    assert cmd[1:4] == ["-m", "torch.distributed.run", "--nnodes=1"] and "--nproc-per-node=3" in cmd
+    assert cmd[cmd.index("--master-addr") + 1] == "127.0.0.1" and cmd[-3:] == ["x.py", "--a", "1"]
+    script = tmp_path / "w.py"
+    script.write_text("import os\nprint('RANK', os.environ['RANK'], os.environ['WORLD_SIZE'], os.environ.get('FT_TOPO'), flush=True)\n")
+    p = subprocess.run([sys.executable, "-m", "flextree.launch", "-np", "2", "--cpu", "--topo", "2", str(script)],
+                       capture_output=True, text=True, cwd=ROOT, timeout=300)
+    assert p.returncode == 0, p.stderr[-500:]
+    assert "RANK 0 2 2" in p.stdout and "RANK 1 2 2" in p.stdout
