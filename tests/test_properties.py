@@ -106,3 +106,87 @@ def test_bulk_tiles_equal_per_vector_text(plan, seed, dtype, registered, scaled)
         w.close()
     for a, b in zip(*res):
         np.testing.assert_array_equal(a, b)
+
+
+@st.composite
+def algo_calls(draw):
+    n = draw(st.integers(2, 9))
+    algo = draw(st.sampled_from(["ring", "nvls", "oneshot", "stages+lonely", "halves"]))
+    count = draw(st.integers(1, 2500))
+    ctas = draw(st.integers(1, 6))
+    tile = draw(st.sampled_from([64, 256, 1024, 4096]))
+    registered = draw(st.booleans())
+    return n, algo, count, ctas, tile, registered
+
+
+@settings(max_examples=60, deadline=None, suppress_health_check=[HealthCheck.too_slow])
+@given(algo_calls(), st.integers(0, 2**31 - 1))
+def test_other_algorithms_any_shape(call, seed):
+    """Ring, NVLS (emulated switch; one-role, role-split and registered variants), one-shot LL, lonely trees and the
+    reduce-scatter / all-gather halves for random world sizes, counts, thread counts and tilings (exact: integers,
+    or small integers carried in fp32 for the float-only NVLS path)."""
+    n, algo, count, ctas, tile, registered = call
+    rng = np.random.default_rng(seed)
+    K = ft.ops.constants
+    w = HostWorld(n, window_bytes=1 << 16, ll_bytes=1 << 16)
+    try:
+        dt = np.float32 if algo == "nvls" else np.int32
+        xs = [rng.integers(-500, 500, count).astype(dt) for _ in range(n)]
+
+        def buffers(src):
+            out = []
+            for r, x in enumerate(src):
+                if registered and algo in ("ring", "nvls"):
+                    v = w.registered(r, x.size, x.dtype)
+                else:
+                    raw = np.empty(x.nbytes + 64, dtype=np.uint8)
+                    off = (-raw.ctypes.data) % 16
+                    v = raw[off:off + x.nbytes].view(x.dtype)
+                v[:] = x
+                out.append(v)
+            return out
+
+        want = np.sum(np.stack(xs), 0, dtype=dt)
+        if algo in ("ring", "nvls"):
+            mode = K.MODE_REGISTERED if registered else K.MODE_STAGING
+            if algo == "nvls" and not registered:
+                tile = max(tile, 1024)  # one flag slot per tile
+            bufs = buffers(xs)
+            assert w.allreduce(bufs, None, algo=algo, ctas=ctas, tile_bytes=tile, mode=mode) == 0
+            for b in bufs:
+                np.testing.assert_array_equal(b, want)
+        elif algo == "oneshot":
+            xs = [x[:500] for x in xs]
+            bufs = buffers(xs)
+            assert w.allreduce(bufs, None, algo="oneshot", ctas=ctas, tile_bytes=tile) == 0
+            for b in bufs:
+                np.testing.assert_array_equal(b, np.sum(np.stack(xs), 0, dtype=dt))
+        elif algo == "stages+lonely":
+            lonely = 1 if n < 4 else int(rng.integers(1, 3))
+            tree = n - lonely
+            if tree < 1:
+                return
+            widths = ft.enumerate_widths(tree)[int(rng.integers(0, len(ft.enumerate_widths(tree))))] if tree > 1 else [1]
+            if tree == 1:
+                return
+            bufs = buffers(xs)
+            assert w.allreduce(bufs, None, widths=widths, lonely=lonely, ctas=ctas, tile_bytes=tile) == 0
+            for b in bufs:
+                np.testing.assert_array_equal(b, want)
+        else:  # halves
+            per = max(1, count // n)
+            total = per * n
+            xs = [x[:total] if x.size >= total else np.resize(x, total) for x in xs]
+            widths = ft.enumerate_widths(n)[int(rng.integers(0, len(ft.enumerate_widths(n))))]
+            send = buffers(xs)
+            part = buffers([np.zeros(per, dt) for _ in range(n)])
+            assert w.allreduce(send, part, widths=widths, ctas=ctas, tile_bytes=tile, phases=1, count=total) == 0
+            full = np.sum(np.stack(xs), 0, dtype=dt)
+            for r in range(n):
+                np.testing.assert_array_equal(part[r], full[r * per:(r + 1) * per])
+            out = buffers([np.zeros(total, dt) for _ in range(n)])
+            assert w.allreduce(part, out, widths=widths, ctas=ctas, tile_bytes=tile, phases=2, count=total) == 0
+            for r in range(n):
+                np.testing.assert_array_equal(out[r], full)
+    finally:
+        w.close()
