@@ -25,7 +25,7 @@ COLS = [("UBLKCP (TMA bulk copy)", r"\bUBLKCP"), ("SYNCS (mbarrier)", r"\bSYNCS"
         ("LDG.*STRONG.SYS (peer loads/flags)", r"\bLDG\.[A-Z0-9.]*STRONG\.SYS"),
         ("STG.*STRONG.SYS (flags, LL lines, multimem.st)", r"\bSTG\.[A-Z0-9.]*STRONG\.SYS"),
         ("MEMBAR.ALL.SYS", r"\bMEMBAR\.ALL\.SYS"), ("CCTL.IVALL", r"\bCCTL\.IVALL"), ("FENCE.VIEW.ASYNC", r"\bFENCE\.VIEW\.ASYNC"),
-        ("registers", None), ("stack bytes", "STACK")]
+        ("LDL+STL (local-memory accesses)", r"\b(?:LDL|STL)\b"), ("registers", None), ("stack bytes", "STACK")]
 
 
 def main():
