@@ -1,11 +1,12 @@
 #!/usr/bin/env python
 """BASELINE.json config #1 on the CPU: "allreduce_over_mpi benchmark: mpirun -np 6, 1M fp32 sum, widths 2x3".
 
-Runs (a) the UNMODIFIED reference through the in-repo MPI shim (its own benchmark binary, its own timing) and
-(b) this library's multi-process CPU communicator (same algorithm templates as the GPU kernels, shared-memory
-windows, gloo bootstrap) on the same machine, same world size, same widths, same message.
+Four arms on the same machine, same world size, same widths, same message, run round-robin --rounds times:
+(a) the UNMODIFIED reference through the in-repo MPI shim (its own benchmark binary, its own timing);
+(b) "dropin": the same unmodified benchmark.cpp built against compat/mpi_mod.hpp (this library's CPU data plane);
+(c) flextree.HostCommunicator on private numpy buffers; (d) the same on the registered (zero-copy) region.
 
-  python bench/cpu_compare.py [--np 6] [--widths 2,3] [--size 1000000] [--repeat 20]
+  python bench/cpu_compare.py [--np 6] [--widths 2,3] [--size 1000000] [--repeat 20] [--rounds 3]
 """
 import argparse
 import json
