@@ -10,7 +10,7 @@ OPS = {"sum": SUM, "band": BAND, "max": MAX, "min": MIN, "bor": BOR}
 ALGOS = {"auto": ALGO_AUTO, "oneshot": ALGO_ONESHOT, "stages": ALGO_STAGES, "nvls": ALGO_NVLS, "ring": ALGO_RING}
 ALGO_NAMES = {v: k for k, v in ALGOS.items()}
 # CPU communicators only: the staged algorithm with the bulk (vectorised chunk) tiles of csrc/host/cpu_backend.h
-HOST_ALGOS = dict(ALGOS, stages_bulk=5)
+HOST_ALGOS = dict(ALGOS, stages_bulk=5, twoshot=6)  # 6: two-shot LL (reduce-scatter + all-gather over LL lines)
 
 DTYPE_SIZE = {UINT8: 1, INT8: 1, BOOL: 1, UINT16: 2, INT16: 2, HALF: 2, BFLOAT16: 2, INT32: 4, UINT32: 4,
               FLOAT: 4, INT64: 8, UINT64: 8, DOUBLE: 8, LONG_LONG: 8, FP8_BLOCK: 1}

@@ -721,6 +721,102 @@ struct StagedCta {
     }
     be.finish(cd, a.ctas);
   }
+  // ---- two-shot LL -----------------------------------------------------------------------------------------
+  // The one-shot pushes the whole message to every peer: (N-1) * S * 2 bytes per rank on the wire (a 16-byte line
+  // carries 8 bytes of data), which is past its sweet spot around 1 MiB. Two shots over the same LL lines move
+  // 2 * (N-1)/N * S * 2 instead: shot 1 sends block p of my message to rank p only, every rank reduces its own block
+  // (ascending rank order, like the one-shot), shot 2 broadcasts the reduced block. Still no barrier and no flag
+  // words: a line is its own flag. Costs one more store hop of latency than the one-shot.
+  // LL area of a parity half: [shot 1: N regions by source | shot 2: N regions by source], region = ll_bytes/(2N).
+  // (No counterpart in the reference.)
+  FT_DEV void run_twoshot() {
+    const int N = a.plan.nranks, G = a.ctas;
+    const long long count = a.lay.count;
+    const long long nlines = (count + LE - 1) / LE;
+    const long long Bl = (nlines + N - 1) / N;  // lines per block; block b = lines [b*Bl, min((b+1)*Bl, nlines))
+    const uint32_t tag = (uint32_t)(E >> FT_EPOCH_SHIFT);
+    const size_t region = (cd.ll_bytes / (size_t)(2 * N)) & ~(size_t)15;
+    const size_t par_off = ((E >> FT_EPOCH_SHIFT) & 1) ? cd.ll_bytes : 0;
+    const size_t shot2 = par_off + (size_t)N * region;
+    IO* y = (IO*)rc.recv;
+    const long long stride = (long long)G * be.nthr();
+    const long long first_line = (long long)cta * be.nthr() + be.tid();
+    // shot 1: every line that is not in my block goes to the rank that owns its block
+    for (long long i = first_line; i < nlines; i += stride) {
+      const int p = (int)(i / Bl);
+      if (p == r) continue;
+      const long long e0 = i * LE;
+      const int nv = (count - e0) < LE ? (int)(count - e0) : LE;
+      const Pack<T, LE> own = ll_own(e0, nv);
+      uint32_t d[2] = {0, 0};
+      memcpy(d, &own, sizeof(own) < 8 ? sizeof(own) : 8);
+      be.ll_st(cd.ll[p] + par_off + (size_t)r * region + (size_t)(i - (long long)p * Bl) * 16, d[0], d[1], tag);
+    }
+    // my block: reduce the N copies in ascending rank order, round to the wire type (the block is final: the fused
+    // scale is applied here, once), keep it and push it to everybody
+    const long long b0 = (long long)r * Bl, b1 = (b0 + Bl < nlines) ? b0 + Bl : nlines;
+    for (long long i = b0 + first_line; i < b1; i += stride) {
+      const long long e0 = i * LE, li = i - b0;
+      const int nv = (count - e0) < LE ? (int)(count - e0) : LE;
+      const Pack<T, LE> own = ll_own(e0, nv);
+      A acc[LE] = {};
+      bool first = true;
+      for (int q = 0; q < N; ++q) {
+        Pack<T, LE> in;
+        if (q == r) {
+          in = own;
+        } else {
+          uint32_t g[2];
+          if (!ll_wait(cd.ll[r] + par_off + (size_t)q * region + (size_t)li * 16, tag, g, q)) { g[0] = g[1] = 0; }
+          memcpy(&in, g, sizeof(in) < 8 ? sizeof(in) : 8);
+        }
+#pragma unroll
+        for (int e = 0; e < LE; ++e) acc[e] = first ? EL::up(in.e[e]) : Op::apply(acc[e], EL::up(in.e[e]));
+        first = false;
+      }
+      Pack<T, LE> res;
+#pragma unroll
+      for (int e = 0; e < LE; ++e) {
+        if constexpr (EL::is_float) {
+          A v = acc[e];
+          if (a.apply_scale) v = (A)(v * (A)a.scale);
+          res.e[e] = EL::down(v);
+        } else {
+          res.e[e] = EL::down(acc[e]);
+        }
+      }
+      uint32_t d[2] = {0, 0};
+      memcpy(d, &res, sizeof(res) < 8 ? sizeof(res) : 8);
+      for (int p = 0; p < N; ++p) {
+        if (p == r) continue;
+        be.ll_st(cd.ll[p] + shot2 + (size_t)r * region + (size_t)li * 16, d[0], d[1], tag);
+      }
+      twoshot_out(y, e0, nv, res);
+    }
+    // shot 2: the other blocks arrive reduced
+    for (long long i = first_line; i < nlines; i += stride) {
+      const int q = (int)(i / Bl);
+      if (q == r) continue;
+      const long long e0 = i * LE;
+      const int nv = (count - e0) < LE ? (int)(count - e0) : LE;
+      uint32_t g[2];
+      if (!ll_wait(cd.ll[r] + shot2 + (size_t)q * region + (size_t)(i - (long long)q * Bl) * 16, tag, g, q)) { g[0] = g[1] = 0; }
+      Pack<T, LE> res;
+      memcpy(&res, g, sizeof(res) < 8 ? sizeof(res) : 8);
+      twoshot_out(y, e0, nv, res);
+    }
+    be.finish(cd, a.ctas);
+  }
+  FT_DEV static void twoshot_out(IO* y, long long e0, int nv, const Pack<T, LE>& res) {
+    Pack<IO, LE> out;
+#pragma unroll
+    for (int e = 0; e < LE; ++e) {
+      if constexpr (kRawIO) out.e[e] = res.e[e];
+      else out.e[e] = EU::down((typename EU::acc)EL::up(res.e[e]));
+    }
+    if (VE > 1 && nv == LE) BE::template st<(int)sizeof(Pack<IO, LE>)>(y + e0, &out);
+    else for (int q = 0; q < nv && q < LE; ++q) BE::template st<(int)sizeof(IO)>(y + e0 + q, &out.e[q]);
+  }
   FT_DEV bool ll_wait(const char* line, uint32_t tag, uint32_t* data, int src) {
     if (*abort_flag) return false;
     uint64_t t0 = 0;

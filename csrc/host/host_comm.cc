@@ -279,7 +279,7 @@ long long ft_host_comm_allreduce(ft_host_comm* c, const void* send, void* recv, 
     phant = -lonely;
     lonely = 0;
   }
-  if (algo == ALGO_RING || algo == ALGO_NVLS || algo == ALGO_ONESHOT) {
+  if (algo == ALGO_RING || algo == ALGO_NVLS || algo == ALGO_ONESHOT || algo == ALGO_TWOSHOT) {
     int flat = N;
     if (!make_plan(&flat, 1, &a.plan)) return -1;
     lonely = 0;
@@ -322,6 +322,11 @@ long long ft_host_comm_allreduce(ft_host_comm* c, const void* send, void* recv, 
   if (algo == ALGO_ONESHOT) {
     size_t region = (c->ll_bytes / (size_t)N) & ~(size_t)15;
     if ((size_t)((count * es + 7) / 8) * 16 > region) return -5;
+  }
+  if (algo == ALGO_TWOSHOT) {  // [shot 1 | shot 2] x N regions of ceil(lines / N) lines per parity half
+    const size_t region2 = (c->ll_bytes / (size_t)(2 * N)) & ~(size_t)15;
+    const size_t lines2 = (size_t)((count * es + 7) / 8), per_block = (lines2 + (size_t)N - 1) / (size_t)N;
+    if (per_block * 16 > region2) return -5;
   }
   if (algo == ALGO_NVLS && mode == MODE_STAGING && a.lay.ntiles > FT_MAX_CTAS) return -12;  // per-tile flag slots
   if (ctas < 1 || ctas > FT_MAX_CTAS) return -6;

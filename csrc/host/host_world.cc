@@ -104,7 +104,7 @@ long long ft_host_allreduce(void* h, const void* const* send, void* const* recv,
   memset(&a, 0, sizeof a);
   const bool want_bulk = algo == ALGO_STAGED_TMA;  // staged stages with the CPU's bulk tiles (cpu_backend.h)
   if (want_bulk) algo = ALGO_STAGED;
-  if (algo == ALGO_RING || algo == ALGO_NVLS || algo == ALGO_ONESHOT) {
+  if (algo == ALGO_RING || algo == ALGO_NVLS || algo == ALGO_ONESHOT || algo == ALGO_TWOSHOT) {
     int flat = w->n;
     if (!make_plan(&flat, 1, &a.plan)) return -1;
   } else {
@@ -132,6 +132,11 @@ long long ft_host_allreduce(void* h, const void* const* send, void* const* recv,
     size_t region = (w->ll_bytes / w->n) & ~(size_t)15;
     size_t lines = (size_t)((count * es + 7) / 8);
     if (lines * 16 > region) return -5;
+  }
+  if (algo == ALGO_TWOSHOT) {  // [shot 1 | shot 2] x N regions of ceil(lines / N) lines per parity half
+    const size_t region2 = (w->ll_bytes / (size_t)(2 * w->n)) & ~(size_t)15;
+    const size_t lines2 = (size_t)((count * es + 7) / 8), per_block = (lines2 + (size_t)w->n - 1) / (size_t)w->n;
+    if (per_block * 16 > region2) return -5;
   }
   if (algo == ALGO_NVLS && mode == MODE_STAGING && a.lay.ntiles > FT_MAX_CTAS) return -12;  // per-tile flag slots
   if (ctas < 1 || ctas > FT_MAX_CTAS) return -6;

@@ -45,7 +45,7 @@ int legacy_choose(const std::vector<Widths>& trees, int total_nodes, double chun
 // ---------------------------------------------------------------------------------------------
 enum Algo { ALGO_AUTO = 0, ALGO_ONESHOT = 1, ALGO_STAGED = 2, ALGO_NVLS = 3, ALGO_RING = 4 };
 // internal kernel selector (not a user-visible algorithm): the P2P stages with TMA-staged tiles
-enum { ALGO_STAGED_TMA = 5 };
+enum { ALGO_STAGED_TMA = 5, ALGO_TWOSHOT = 6 };  // 6: two-shot LL (CPU communicators this round; GPU kernel not instantiated yet)
 const char* algo_name(int a);
 int algo_from_name(const std::string& s);  // -1 if unknown
 

@@ -115,6 +115,8 @@ int main() {
   bad |= run(5, {1}, 4, 0, 3000, 2, 256);
   bad |= run(5, {1}, 4, 1, 3000, 2, 256);
   bad |= run(4, {4}, 1, 0, 999, 2, 256);
+  bad |= run(4, {4}, 6, 0, 3001, 3, 256);  // two-shot LL
+  bad |= run(7, {7}, 6, 0, 5, 2, 256);     // ... with empty blocks
   bad |= run(7, {2, 3}, 2, 0, 5000, 2, 256, 1);
   bad |= run(5, {3}, 2, 0, 3001, 3, 128, 2);
   // bulk tiles (algo 5, cpu_backend.h): private and registered buffers

@@ -55,7 +55,7 @@ def main():
     comm.allreduce(x)
     assert torch.allclose(x, ref, rtol=1e-5, atol=1e-5)
     # other algorithms
-    for algo in ("oneshot", "ring", "nvls"):
+    for algo in ("oneshot", "twoshot", "ring", "nvls"):
         x = torch.randn(3000, generator=g)
         ref = ref_sum(x.double()).float()
         comm.allreduce(x, algo=algo, ctas=2, tile_bytes=2048)

@@ -316,6 +316,58 @@ def test_oneshot_ll(n, dtype):
     assert w.allreduce([aligned_copy(a) for a in make_inputs(n, 1 << 16, np.float32)], None, algo="oneshot") == -5
 
 
+@pytest.mark.parametrize("n", [2, 3, 4, 8])
+@pytest.mark.parametrize("dtype", [np.float32, np.float16, np.int32, np.uint8, np.float64])
+def test_twoshot_ll_equals_oneshot(n, dtype):
+    """Two-shot LL (block p of every message to rank p, reduce, broadcast) against the one-shot: same ascending
+    summation order, so the same bits - for ragged counts, counts smaller than N (empty blocks), in place, and
+    several CTAs."""
+    LL = 1 << 20
+    w = HostWorld(n, window_bytes=8 << 20, ll_bytes=LL)
+    for count in (1, 5, 1023, 4096):
+        x = make_inputs(n, count, dtype)
+        one = [aligned_empty(count, dtype) for _ in range(n)]
+        assert w.allreduce([aligned_copy(a) for a in x], one, algo="oneshot", ctas=2) == 0
+        two = [aligned_copy(a) for a in x]  # in place
+        assert w.allreduce(two, None, algo="twoshot", ctas=3) == 0
+        for r in range(n):
+            np.testing.assert_array_equal(two[r], one[r], err_msg=f"count {count} rank {r}")
+    # the two-shot holds ~N/2 times the one-shot's message in the same LL buffer
+    big = LL // 16 // n * 8 // 4 + 64  # fp32 elements: a little more than one one-shot region
+    xs = make_inputs(n, big, np.float32)
+    assert w.allreduce([aligned_copy(a) for a in xs], None, algo="oneshot") == -5
+    if n > 2:
+        bufs = [aligned_copy(a) for a in xs]
+        assert w.allreduce(bufs, None, algo="twoshot", ctas=2) == 0
+        acc = xs[0].copy()
+        for a in xs[1:]:
+            acc = acc + a
+        np.testing.assert_array_equal(bufs[0], acc)
+    assert w.allreduce([aligned_copy(a) for a in make_inputs(n, LL, np.float32)], None, algo="twoshot") == -5
+
+
+def test_twoshot_ll_fused_scale_and_bf16_wire():
+    n, count = 4, 2000
+    xf = make_inputs(n, count, np.float32)
+    w = HostWorld(n, ll_bytes=1 << 18)
+    bufs = [aligned_copy(x) for x in xf]
+    assert w.allreduce(bufs, None, algo="twoshot", ctas=2, scale=0.25) == 0
+    acc = xf[0].copy()
+    for a in xf[1:]:
+        acc = acc + a
+    for b in bufs:
+        np.testing.assert_array_equal(b, acc * np.float32(0.25))
+    # fp32 data on a bf16 wire: inputs and the reduced block are rounded to bf16, every rank gets the same bits
+    bufs = [aligned_copy(x) for x in xf]
+    assert w.allreduce(bufs, None, algo="twoshot", ctas=2, dtype_code=K.BFLOAT16, io_dtype_code=K.FLOAT, scale=0.25) == 0
+    acc = round_bf16(xf[0]).astype(np.float32)
+    for a in xf[1:]:
+        acc = acc + round_bf16(a)
+    want = round_bf16(acc * np.float32(0.25))
+    for b in bufs:
+        np.testing.assert_array_equal(b, want)
+
+
 @pytest.mark.parametrize("mode", [K.MODE_STAGING, K.MODE_REGISTERED])
 def test_nvls_protocol_with_emulated_switch(mode):
     n, count = 8, 3001
@@ -582,10 +634,10 @@ def test_randomized_delays_stress():
                  ("ring", None, 0, False, 2), ("nvls", None, 0, False, 2), ("oneshot", None, 0, False, 1),
                  ("stages_bulk", [6], 0, False, 3), ("nvls", None, 0, True, 2), ("nvls", None, 0, False, 5),
                  ("stages", [5], 1, False, 2), ("ring", None, 0, True, 1), ("stages", [2, 2], 2, False, 3),
-                 ("nvls", None, 0, False, 8)]
+                 ("nvls", None, 0, False, 8), ("twoshot", None, 0, False, 2)]
         for it in range(2 * len(plans)):
             algo, widths, lonely, registered, ctas = plans[it % len(plans)]
-            count = int(rng.integers(1, 3000)) if algo != "oneshot" else int(rng.integers(1, 600))
+            count = int(rng.integers(1, 3000)) if algo not in ("oneshot", "twoshot") else int(rng.integers(1, 600))
             xs = [rng.integers(-1000, 1000, count).astype(np.int32) for _ in range(n)]
             if registered:
                 bufs = [w.registered(r, count, np.int32) for r in range(n)]
