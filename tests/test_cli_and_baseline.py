@@ -99,7 +99,9 @@ def test_launcher_front_end(tmp_path):
     assert cmd[1:4] == ["-m", "torch.distributed.run", "--nnodes=1"] and "--nproc-per-node=3" in cmd
     assert cmd[cmd.index("--master-addr") + 1] == "127.0.0.1" and cmd[-3:] == ["x.py", "--a", "1"]
     script = tmp_path / "w.py"
-    script.write_text("import os\nprint('RANK', os.environ['RANK'], os.environ['WORLD_SIZE'], os.environ.get('FT_TOPO'), flush=True)\n")
+    # one os.write per rank: two ranks share the pipe, and print() would emit its fields in separate writes
+    script.write_text("import os\nos.write(1, ('RANK %s %s %s\\n' % (os.environ['RANK'], os.environ['WORLD_SIZE'], "
+                      "os.environ.get('FT_TOPO'))).encode())\n")
     p = subprocess.run([sys.executable, "-m", "flextree.launch", "-np", "2", "--cpu", "--topo", "2", str(script)],
                        capture_output=True, text=True, cwd=ROOT, timeout=300)
     assert p.returncode == 0, p.stderr[-500:]
