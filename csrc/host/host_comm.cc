@@ -87,7 +87,8 @@ static int agree(ft_host_comm* c, char* bit, uint32_t payload, unsigned long lon
   for (int p = 0; p < N; ++p) {
     uint64_t v;
     unsigned it = 0;
-    while (((v = __atomic_load_n(board + p, __ATOMIC_ACQUIRE)) >> 32) < seq) {
+    // (32-bit call numbers compared modulo 2^32: a peer is never more than one call away from me)
+    while ((int32_t)((uint32_t)((v = __atomic_load_n(board + p, __ATOMIC_ACQUIRE)) >> 32) - (uint32_t)seq) < 0) {
       if (((++it) & 0x3ff) == 0 && timeout_ns) {
         timespec t1;
         clock_gettime(CLOCK_MONOTONIC, &t1);
@@ -253,6 +254,8 @@ ft_result_t ft_host_comm_destroy(ft_host_comm* c) {
   return FT_SUCCESS;
 }
 
+// Tests only: jump the per-call agreement counter (same value on every rank), e.g. to just below 2^32.
+void ft_host_comm_debug_set_calls(ft_host_comm* c, unsigned long long calls) { c->calls = calls; }
 int ft_host_comm_rank(const ft_host_comm* c) { return c->rank; }
 int ft_host_comm_size(const ft_host_comm* c) { return c->nranks; }
 unsigned ft_host_comm_error(const ft_host_comm* c) { return c->err; }

@@ -128,6 +128,16 @@ def main():
         assert np.all(v == want), (it, algo, v[:4], want)
         v[:] = -1e9  # poison: the next input arrives immediately
     lib.ft_host_set_jitter(0)
+    # the per-call agreement numbers its calls modulo 2^32: run across the wrap
+    import ctypes
+    lib.ft_host_comm_debug_set_calls.argtypes = [ctypes.c_void_p, ctypes.c_ulonglong]
+    dist.barrier()
+    lib.ft_host_comm_debug_set_calls(comm._h, (1 << 32) - 3)
+    for it in range(6):
+        x = torch.randn(777, generator=g)
+        ref = ref_sum(x.double()).float()
+        comm.allreduce(x)
+        assert torch.allclose(x, ref, rtol=1e-5, atol=1e-5), it
     # the halves
     per = 257
     x = torch.randn(per * world, generator=g)
