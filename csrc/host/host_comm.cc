@@ -41,7 +41,7 @@ struct ft_host_comm {
   std::vector<char*> win_table;  // window segment base of every rank
   CommDev cd;
   uint64_t epoch = 0, calls = 0;
-  size_t board_off = 0;  // agreement board: FT_MAX_RANKS 64-bit slots in the spare page behind the windows
+  size_t board_off = 0;  // agreement board: 2 parities x FT_MAX_RANKS 64-bit slots in the spare page behind the windows
   unsigned done = 0, err = 0;
   // "-k" trees (cost_model/ChooseWidth.h:16-22 lists the trees of N+1 as candidates for N ranks): a tree with k more
   // positions than there are processes. Phantom j (logical rank N+j) is hosted by process j % N: it has its own
@@ -67,19 +67,23 @@ struct ft_host_comm {
 
 // Per-call agreement without leaving shared memory: one bit that is AND-ed over the ranks (here: "all my buffers
 // are 16-byte aligned") and a 31-bit payload that must be the same on every rank (here: the offset of a registered
-// buffer inside the region, in 16-byte units). Every rank owns one 64-bit slot per rank in the spare page behind its
-// windows; it publishes (call number << 32 | payload << 1 | bit) into its slot on EVERY rank and then waits until
-// its own board shows this call's number in every slot. A peer cannot be more than one call ahead (it cannot
-// finish call n without my data phase, which starts after my agreement), so ">= this call" is never satisfied by a
-// stale value. Replaces a bootstrap all-gather per call (a gloo round trip costs more than the whole collective for
-// small messages). Returns 0 = timeout, 1 = agreed, 2 = payloads differ (every rank sees that).
+// buffer inside the region, in 16-byte units). Every rank owns two 64-bit slots per rank (one per call parity) in
+// the spare page behind its windows; it publishes (call number << 32 | payload << 1 | bit) into this call's slot on
+// EVERY rank and then waits until its own board shows exactly this call's number in every slot of that parity.
+// Why two parities: a call that ends right after the agreement (an argument error every rank sees, e.g. mismatched
+// registered offsets) has no data phase to hold a fast rank back, so that rank may already be publishing its NEXT
+// call while a slow rank still reads this one - into the other parity. It cannot get two calls ahead: finishing the
+// next agreement needs the slow rank's next publication. Replaces a bootstrap all-gather per call (a gloo round trip
+// costs more than the whole collective for small messages). Call numbers are compared modulo 2^32.
+// Returns 0 = timeout, 1 = agreed, 2 = payloads differ (every rank sees that).
 static int agree(ft_host_comm* c, char* bit, uint32_t payload, unsigned long long timeout_ns) {
   const int N = c->nranks;
   const uint64_t seq = ++c->calls;
+  const size_t par = (size_t)(seq & 1) * FT_MAX_RANKS;
   const uint64_t mine = (seq << 32) | ((uint64_t)(payload & 0x7fffffffu) << 1) | (uint64_t)(*bit ? 1 : 0);
   for (int p = 0; p < N; ++p)
-    __atomic_store_n((uint64_t*)(c->maps[(size_t)p] + c->board_off) + c->rank, mine, __ATOMIC_RELEASE);
-  const uint64_t* board = (const uint64_t*)(c->maps[(size_t)c->rank] + c->board_off);
+    __atomic_store_n((uint64_t*)(c->maps[(size_t)p] + c->board_off) + par + c->rank, mine, __ATOMIC_RELEASE);
+  const uint64_t* board = (const uint64_t*)(c->maps[(size_t)c->rank] + c->board_off) + par;
   timespec t0;
   clock_gettime(CLOCK_MONOTONIC, &t0);
   char all = 1;
@@ -87,8 +91,7 @@ static int agree(ft_host_comm* c, char* bit, uint32_t payload, unsigned long lon
   for (int p = 0; p < N; ++p) {
     uint64_t v;
     unsigned it = 0;
-    // (32-bit call numbers compared modulo 2^32: a peer is never more than one call away from me)
-    while ((int32_t)((uint32_t)((v = __atomic_load_n(board + p, __ATOMIC_ACQUIRE)) >> 32) - (uint32_t)seq) < 0) {
+    while ((uint32_t)((v = __atomic_load_n(board + p, __ATOMIC_ACQUIRE)) >> 32) != (uint32_t)seq) {
       if (((++it) & 0x3ff) == 0 && timeout_ns) {
         timespec t1;
         clock_gettime(CLOCK_MONOTONIC, &t1);
