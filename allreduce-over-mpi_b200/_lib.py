@@ -112,6 +112,8 @@ def _declare(L):
     sig("ft_comm_has_multicast", i32, [vp])
     sig("ft_comm_error", C.c_uint, [vp])
     sig("ft_comm_clear_error", i32, [vp])
+    sig("ft_comm_error_peek", C.c_uint, [vp])
+    sig("ft_comm_inject_fault", i32, [vp, i32])
     sig("ft_comm_set_widths", i32, [vp, pi32, i32])
     sig("ft_comm_set_algo", i32, [vp, i32])
     sig("ft_comm_set_link_model", i32, [vp, vp])
@@ -132,3 +134,4 @@ def _declare(L):
     sig("ft_reduce_scatter_multi", i32, [C.POINTER(vp), C.POINTER(vp), C.c_size_t, i32, i32, vp, vp])
     sig("ft_all_gather_multi", i32, [C.POINTER(vp), C.POINTER(vp), C.c_size_t, i32, vp, vp])
     sig("ft_allreduce_emulated_noalloc", i32, [C.POINTER(vp), C.POINTER(vp), i32, C.c_size_t, i32, i32, vp])
+    sig("ft_noalloc_error", C.c_uint, [i32])

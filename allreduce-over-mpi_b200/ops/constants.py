@@ -7,7 +7,9 @@ ALGO_AUTO, ALGO_ONESHOT, ALGO_STAGES, ALGO_NVLS, ALGO_RING = range(5)
 MODE_STAGING, MODE_REGISTERED = 0, 1
 
 OPS = {"sum": SUM, "band": BAND, "max": MAX, "min": MIN, "bor": BOR}
-ALGOS = {"auto": ALGO_AUTO, "oneshot": ALGO_ONESHOT, "stages": ALGO_STAGES, "nvls": ALGO_NVLS, "ring": ALGO_RING}
+ALGO_TWOSHOT = 6
+ALGOS = {"auto": ALGO_AUTO, "oneshot": ALGO_ONESHOT, "stages": ALGO_STAGES, "nvls": ALGO_NVLS, "ring": ALGO_RING,
+         "twoshot": ALGO_TWOSHOT}
 ALGO_NAMES = {v: k for k, v in ALGOS.items()}
 # CPU communicators only: the staged algorithm with the bulk (vectorised chunk) tiles of csrc/host/cpu_backend.h
 HOST_ALGOS = dict(ALGOS, stages_bulk=5, twoshot=6)  # 6: two-shot LL (reduce-scatter + all-gather over LL lines)

@@ -146,6 +146,21 @@ class Communicator:
         torch.cuda.synchronize(self.device)
         return int(self._L.ft_comm_error(self._h))
 
+    def poll_error(self):
+        """The same word without any synchronisation (mapped host mirror written by the failing kernel)."""
+        return int(self._L.ft_comm_error_peek(self._h))
+
+    def raise_if_failed(self):
+        """Raise FlexTreeError if a device watchdog has fired on this communicator (non-blocking)."""
+        e = self.poll_error()
+        if e:
+            raise FlexTreeError(f"flextree: device watchdog fired (error word {e:#x}: code {e & 0xff}, phase {(e >> 8) & 0xff}, "
+                                f"waiting for rank {(e >> 16) & 0xff}, on rank {e >> 24}); the results of that collective are invalid")
+
+    def inject_fault(self, rank):
+        """Tests/drills: logical rank `rank` plays dead in the following collectives (None = off)."""
+        _check(self._L, self._L.ft_comm_inject_fault(self._h, -1 if rank is None else int(rank)), "ft_comm_inject_fault")
+
     def clear_error(self):
         _check(self._L, self._L.ft_comm_clear_error(self._h), "ft_comm_clear_error")
 

@@ -41,6 +41,7 @@ class FlexTreeDataParallel(torch.nn.Module):
         if max_ctas:
             comm.set_max_ctas(max_ctas)
         self.buckets = []
+        self._next = 0  # index of the first bucket not launched in this iteration
         self._bucket_of = {}
         params = [p for p in module.parameters() if p.requires_grad]
         if broadcast and comm.size > 1:
@@ -98,7 +99,16 @@ class FlexTreeDataParallel(torch.nn.Module):
         b = self._bucket_of[p]
         b.pending -= 1
         if b.pending == 0:
-            self._launch(b)
+            self._launch_ready()
+
+    def _launch_ready(self):
+        """Collectives are matched across ranks by ISSUE ORDER (flags and epochs carry no bucket id), so buckets are
+        launched strictly in index order: bucket i goes out only after buckets 0..i-1 have. A bucket that becomes
+        ready early (data-dependent control flow can reorder gradient production between ranks) waits here for
+        its predecessors; synchronize() flushes whatever is left, again in index order."""
+        while self._next < len(self.buckets) and self.buckets[self._next].pending == 0:
+            self._launch(self.buckets[self._next])
+            self._next += 1
 
     def _launch(self, b):
         cur = torch.cuda.current_stream(self.comm.device)
@@ -118,6 +128,10 @@ class FlexTreeDataParallel(torch.nn.Module):
             cur.wait_event(b.event)
             b.pending = len(b.params)
             b.launched = False
+        self._next = 0
+        # a watchdog that fired in one of this (or an earlier) iteration's collectives means wrong gradients: the
+        # kernel mirrors its error word into mapped host memory, so this check costs no synchronisation
+        self.comm.raise_if_failed()
 
     def zero_grad(self, set_to_none=False):
         for b in self.buckets:

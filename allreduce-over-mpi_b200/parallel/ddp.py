@@ -27,6 +27,8 @@ class FlexTreeHookState:
 def ddp_comm_hook(state, bucket):
     buf = bucket.buffer()
     comm = state.comm
+    # (comm.allreduce itself raises once an earlier bucket's collective has tripped the device watchdog: the
+    # kernel mirrors its error word into mapped host memory and every call peeks it first)
     scale = 1.0 / comm.size if state.average else 1.0
     wire = None
     if state.wire_dtype is not None:

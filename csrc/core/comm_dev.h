@@ -46,6 +46,7 @@ struct CommDev {
   uint64_t* epoch;              // local: number of collectives completed on this communicator
   unsigned* done;               // local: CTAs of the current kernel that have finished
   unsigned* err;                // local: sticky error word
+  unsigned* err_host;           // mirror of `err` in mapped host memory (the host peeks it without a sync), or null
   size_t ll_bytes;              // capacity of one parity half of an LL buffer
   uint64_t* trace;              // local, optional: FT_TRACE_SLOTS phase timestamps of CTA 0 (ns), null = off
 };
@@ -87,6 +88,7 @@ struct StagedArgs {
   long long scale_plane_off;  // fp8 block-scaled wire: byte offset of the scale plane inside the window
   int phases;   // 0 = allreduce, 1 = reduce-scatter only (recv gets my block), 2 = all-gather only (send is my block)
   int nvls_reducers;  // NVLS with private buffers: CTAs per rank that only run the in-switch reduce (rest copy)
+  int fault_rank_plus1;  // fault injection (tests): rank + 1 of a rank that plays dead in this call, 0 = none
   RankCall rc[FT_MAX_LOCAL];
 };
 

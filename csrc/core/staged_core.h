@@ -94,7 +94,7 @@ struct StagedCta {
           uint64_t now = be.now_ns();
           if (!t0) t0 = now;
           else if (now - t0 > a.timeout_ns) {
-            be.err_set(cd.err, (unsigned)ERR_TIMEOUT | ((unsigned)phase << 8) | ((unsigned)src << 16) |
+            be.err_set(cd, (unsigned)ERR_TIMEOUT | ((unsigned)phase << 8) | ((unsigned)src << 16) |
                                    ((unsigned)r << 24));
             *abort_flag = 1;
             return;
@@ -828,7 +828,7 @@ struct StagedCta {
           uint64_t now = be.now_ns();
           if (!t0) t0 = now;
           else if (now - t0 > a.timeout_ns) {
-            be.err_set(cd.err, (unsigned)ERR_TIMEOUT | (0xfeu << 8) | ((unsigned)src << 16) | ((unsigned)r << 24));
+            be.err_set(cd, (unsigned)ERR_TIMEOUT | (0xfeu << 8) | ((unsigned)src << 16) | ((unsigned)r << 24));
             *abort_flag = 1;
             return false;
           }

@@ -157,9 +157,10 @@ struct CpuBE {
   }
   uint64_t load_epoch(const uint64_t* p) { return __atomic_load_n(p, __ATOMIC_ACQUIRE); }
   unsigned err_ld(const unsigned* p) { return __atomic_load_n(p, __ATOMIC_RELAXED); }
-  void err_set(unsigned* p, unsigned v) {
+  void err_set(const CommDev& cd, unsigned v) {
     unsigned expect = 0;
-    __atomic_compare_exchange_n(p, &expect, v, false, __ATOMIC_RELAXED, __ATOMIC_RELAXED);
+    if (__atomic_compare_exchange_n(cd.err, &expect, v, false, __ATOMIC_RELAXED, __ATOMIC_RELAXED) && cd.err_host)
+      __atomic_store_n(cd.err_host, v, __ATOMIC_RELEASE);
   }
   uint64_t now_ns() {
     timespec ts;

@@ -122,7 +122,14 @@ struct CudaBE {
     asm volatile("ld.relaxed.gpu.global.u32 %0, [%1];" : "=r"(v) : "l"(p) : "memory");
     return v;
   }
-  __device__ __forceinline__ void err_set(unsigned* p, unsigned v) { atomicCAS(p, 0u, v); }
+  // First error wins. The winner also writes the mirror in mapped host memory, which the host checks at the
+  // start of the next call without synchronising anything.
+  __device__ __forceinline__ void err_set(const CommDev& cd, unsigned v) {
+    if (atomicCAS(cd.err, 0u, v) == 0u && cd.err_host) {
+      *(volatile unsigned*)cd.err_host = v;
+      __threadfence_system();
+    }
+  }
   __device__ __forceinline__ uint64_t now_ns() {
     uint64_t t;
     asm volatile("mov.u64 %0, %%globaltimer;" : "=l"(t));

@@ -28,11 +28,18 @@ __global__ void __launch_bounds__(FT_MAX_THREADS, 1) ft_allreduce_kernel(const _
   ring.empty = ring.full + kTmaStages;
   if constexpr (ALGO == ALGO_STAGED_TMA) tma_ring_init(ring, ((int)blockDim.x >> 5) - 1);
   CudaBE be(&s_abort, ring);
+  if (a.fault_rank_plus1 && a.rc[lr].comm->rank + 1 == a.fault_rank_plus1) {
+    // fault injection (ft_comm_inject_fault): this rank plays dead - it touches no buffer and signals nobody, so
+    // its peers run into the watchdog. The epoch still advances, which keeps the communicator usable afterwards.
+    be.finish(*a.rc[lr].comm, a.ctas);
+    return;
+  }
   StagedCta<CudaBE, T, IO, Op, VE> k(be, a, a.rc[lr], cta);
   if constexpr (ALGO == ALGO_STAGED) k.template run<false>();
   else if constexpr (ALGO == ALGO_STAGED_TMA) k.template run<true>();
   else if constexpr (ALGO == ALGO_NVLS) k.run_nvls();
   else if constexpr (ALGO == ALGO_ONESHOT) k.run_oneshot();
+  else if constexpr (ALGO == ALGO_TWOSHOT) k.run_twoshot();
   else k.run_ring();
 }
 
@@ -74,6 +81,7 @@ struct CudaLaunch {
           else c->supported = false;
           break;
         case ALGO_ONESHOT: c->err = go<ALGO_ONESHOT>(c); break;
+        case ALGO_TWOSHOT: c->err = go<ALGO_TWOSHOT>(c); break;
         case ALGO_RING: c->err = go<ALGO_RING>(c); break;
         case ALGO_NVLS:
           if constexpr (NvlsOk<T, Op>::value && VE > 1) c->err = go<ALGO_NVLS>(c);

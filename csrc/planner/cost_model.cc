@@ -50,6 +50,7 @@ const char* algo_name(int a) {
     case ALGO_STAGED: return "stages";
     case ALGO_NVLS: return "nvls";
     case ALGO_RING: return "ring";
+    case ALGO_TWOSHOT: return "twoshot";
   }
   return "?";
 }
@@ -60,6 +61,7 @@ int algo_from_name(const std::string& s) {
   if (s == "stages" || s == "staged" || s == "tree" || s == "flextree") return ALGO_STAGED;
   if (s == "nvls" || s == "multicast") return ALGO_NVLS;
   if (s == "ring") return ALGO_RING;
+  if (s == "twoshot" || s == "ll2") return ALGO_TWOSHOT;
   return -1;
 }
 
@@ -98,7 +100,7 @@ bool load_link_model(const std::string& path, LinkModel* m, std::string* err) {
     FT_KEY(alpha_peer_us, double) FT_KEY(alpha_nvls_us, double) FT_KEY(beta_ll_self_GBps, double)
     FT_KEY(beta_p2p_GBps, double) FT_KEY(beta_p2p_1peer_GBps, double) FT_KEY(fanin_knee, int)
     FT_KEY(beta_nvls_GBps, double) FT_KEY(beta_ll_GBps, double) FT_KEY(gamma_hbm_GBps, double)
-    FT_KEY(half_bw_bytes, double) FT_KEY(has_nvls, bool) FT_KEY(max_oneshot_bytes, int)
+    FT_KEY(half_bw_bytes, double) FT_KEY(has_nvls, bool) FT_KEY(max_oneshot_bytes, int) FT_KEY(max_twoshot_bytes, int)
 #undef FT_KEY
   }
   if (!found && err) *err = "no known keys in " + path;
@@ -111,10 +113,10 @@ std::string dump_link_model(const LinkModel& m) {
                 "{\"alpha_launch_us\": %.4g, \"alpha_sync_us\": %.4g, \"alpha_peer_us\": %.4g, \"alpha_ll_us\": %.4g, "
                 "\"alpha_nvls_us\": %.4g, \"beta_p2p_GBps\": %.5g, \"beta_p2p_1peer_GBps\": %.5g, \"fanin_knee\": %d, "
                 "\"beta_nvls_GBps\": %.5g, \"beta_ll_GBps\": %.5g, \"beta_ll_self_GBps\": %.5g, \"gamma_hbm_GBps\": %.5g, "
-                "\"half_bw_bytes\": %.6g, \"has_nvls\": %s, \"max_oneshot_bytes\": %d}",
+                "\"half_bw_bytes\": %.6g, \"has_nvls\": %s, \"max_oneshot_bytes\": %d, \"max_twoshot_bytes\": %d}",
                 m.alpha_launch_us, m.alpha_sync_us, m.alpha_peer_us, m.alpha_ll_us, m.alpha_nvls_us, m.beta_p2p_GBps,
                 m.beta_p2p_1peer_GBps, m.fanin_knee, m.beta_nvls_GBps, m.beta_ll_GBps, m.beta_ll_self_GBps,
-                m.gamma_hbm_GBps, m.half_bw_bytes, m.has_nvls ? "true" : "false", m.max_oneshot_bytes);
+                m.gamma_hbm_GBps, m.half_bw_bytes, m.has_nvls ? "true" : "false", m.max_oneshot_bytes, m.max_twoshot_bytes);
   return buf;
 }
 
@@ -144,6 +146,12 @@ double predict_us(const LinkModel& m, int algo, const Widths& widths, int n, dou
       // every rank pushes its whole message to N-1 peers as LL lines, then polls and reduces them
       return m.alpha_launch_us + m.alpha_ll_us + S / (m.beta_ll_self_GBps * 1e3) +
              (N - 1) * S / (m.beta_ll_GBps * 1e3);
+    }
+    case ALGO_TWOSHOT: {
+      // shot 1: block p of my message to rank p; reduce my block; shot 2: my reduced block to everybody. Two LL
+      // hops of latency, 2 (N-1)/N S of payload pushed per rank instead of the one-shot's (N-1) S.
+      return m.alpha_launch_us + 2.0 * m.alpha_ll_us + S / (m.beta_ll_self_GBps * 1e3) +
+             2.0 * (N - 1) / N * S / (m.beta_ll_GBps * 1e3);
     }
     case ALGO_STAGED: {
       double t = m.alpha_launch_us;
@@ -199,6 +207,7 @@ Choice choose(const LinkModel& m, int n, double S, bool registered, int max_widt
     }
   };
   if (S <= m.max_oneshot_bytes) consider(ALGO_ONESHOT, {n});
+  if (S <= m.max_twoshot_bytes) consider(ALGO_TWOSHOT, {n});
   for (auto& w : enumerate_widths(n, false)) {
     bool ok = true;
     for (int x : w) ok = ok && x <= max_width;

@@ -45,7 +45,7 @@ int legacy_choose(const std::vector<Widths>& trees, int total_nodes, double chun
 // ---------------------------------------------------------------------------------------------
 enum Algo { ALGO_AUTO = 0, ALGO_ONESHOT = 1, ALGO_STAGED = 2, ALGO_NVLS = 3, ALGO_RING = 4 };
 // internal kernel selector (not a user-visible algorithm): the P2P stages with TMA-staged tiles
-enum { ALGO_STAGED_TMA = 5, ALGO_TWOSHOT = 6 };  // 6: two-shot LL (CPU communicators this round; GPU kernel not instantiated yet)
+enum { ALGO_STAGED_TMA = 5, ALGO_TWOSHOT = 6 };  // 6: two-shot LL (user-visible as FT_ALGO_TWOSHOT / "twoshot")
 const char* algo_name(int a);
 int algo_from_name(const std::string& s);  // -1 if unknown
 
@@ -68,6 +68,7 @@ struct LinkModel {
   double half_bw_bytes = 4.0e6;   // per-stage bytes at which a P2P stage reaches half its peak rate
   bool has_nvls = false;
   int max_oneshot_bytes = 4 << 20;  // further limited by the LL buffer of the communicator
+  int max_twoshot_bytes = 0;        // two-shot LL as an automatic candidate up to this size (0 = only on request)
 };
 
 bool load_link_model(const std::string& json_path, LinkModel* m, std::string* err = nullptr);

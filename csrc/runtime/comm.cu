@@ -121,6 +121,8 @@ struct ft_comm {
   unsigned* d_done = nullptr;      // [nlocal]
   unsigned* d_err = nullptr;       // [nlocal]
   uint64_t* d_trace = nullptr;     // [nlocal][FT_TRACE_SLOTS], allocated by ft_comm_trace_enable
+  unsigned* h_err = nullptr;       // [nlocal] mapped pinned host mirror of d_err (written by the kernel that sets d_err)
+  int fault_rank = -1;             // ft_comm_inject_fault: this rank plays dead in the next calls (-1 = off)
 
   // policy
   std::vector<int> widths_override;
@@ -195,6 +197,16 @@ ft_result_t upload_comm_dev(ft_comm* c) {
   FT_CHECK_RT(cudaMemset(c->d_epoch, 0, sizeof(uint64_t) * (size_t)L));
   FT_CHECK_RT(cudaMemset(c->d_done, 0, sizeof(unsigned) * (size_t)L));
   FT_CHECK_RT(cudaMemset(c->d_err, 0, sizeof(unsigned) * (size_t)L));
+  unsigned* h_err_dev = nullptr;
+  if (cudaHostAlloc((void**)&c->h_err, sizeof(unsigned) * (size_t)L, cudaHostAllocMapped | cudaHostAllocPortable) == cudaSuccess &&
+      cudaHostGetDevicePointer((void**)&h_err_dev, c->h_err, 0) == cudaSuccess) {
+    memset(c->h_err, 0, sizeof(unsigned) * (size_t)L);
+  } else {  // no mapped host memory: errors are then only visible through ft_comm_error()
+    (void)cudaGetLastError();
+    if (c->h_err) cudaFreeHost(c->h_err);
+    c->h_err = nullptr;
+    h_err_dev = nullptr;
+  }
   std::vector<CommDev> h((size_t)L);
   for (int l = 0; l < L; ++l) {
     CommDev& d = h[(size_t)l];
@@ -208,6 +220,7 @@ ft_result_t upload_comm_dev(ft_comm* c) {
     d.epoch = c->d_epoch + l;
     d.done = c->d_done + l;
     d.err = c->d_err + l;
+    d.err_host = h_err_dev ? h_err_dev + l : nullptr;
     d.ll_bytes = c->ll_bytes;
   }
   FT_CHECK_RT(cudaMemcpy(c->d_comm, h.data(), sizeof(CommDev) * (size_t)L, cudaMemcpyHostToDevice));
@@ -331,10 +344,12 @@ Shape pick_shape(const ft_comm* c, int algo, int mode, bool tma, size_t msg_byte
   if (kMaxTile < kMinTile) kMaxTile = kMinTile;
   int ctas;
   long long tile;
-  if (algo == ALGO_ONESHOT) {
+  if (algo == ALGO_ONESHOT || algo == ALGO_TWOSHOT) {
     long long lines = ((long long)msg_bytes + 7) / 8;  // one LL line (8 payload bytes) per thread
+    if (algo == ALGO_TWOSHOT) lines = (lines + nranks - 1) / nranks;  // threads stride over the N blocks
     ctas = (int)((lines + s.threads - 1) / s.threads);
-    if (ctas > 64) ctas = 64;
+    const int cap_ll = algo == ALGO_TWOSHOT ? 128 : 64;
+    if (ctas > cap_ll) ctas = cap_ll;
     tile = kMinTile;
   } else if (algo == ALGO_NVLS) {
     // multimem.ld_reduce/st saturate the switch path from very few SMs (8 CTAs reach 796 GB/s busbw at
@@ -400,9 +415,23 @@ Shape pick_shape(const ft_comm* c, int algo, int mode, bool tma, size_t msg_byte
   return s;
 }
 
+// A device watchdog that fired during an EARLIER call left its error word in the mapped host mirror: refuse to
+// queue more work on a communicator whose flags are in an unknown state (the results of that call are garbage).
+// Costs a few host loads, synchronises nothing. ft_comm_clear_error() re-arms the communicator.
 ft_result_t check_device_error(ft_comm* c) {
-  // non-blocking peek is impossible without a sync; callers use ft_comm_error() explicitly
-  (void)c;
+  if (!c->h_err) return FT_SUCCESS;
+  for (int l = 0; l < c->nlocal; ++l) {
+    const unsigned e = *(volatile unsigned*)(c->h_err + l);
+    if (e) {
+      char buf[200];
+      snprintf(buf, sizeof buf,
+               "device watchdog fired in an earlier call on this communicator: error word %#x (code %u, phase %u, "
+               "waiting for rank %u, on rank %u); its results are invalid - ft_comm_clear_error() to continue",
+               e, e & 0xffu, (e >> 8) & 0xffu, (e >> 16) & 0xffu, e >> 24);
+      set_last_error(buf);
+      return (e & 0xffu) == ERR_TIMEOUT ? FT_ERR_TIMEOUT : FT_ERR_INTERNAL;
+    }
+  }
   return FT_SUCCESS;
 }
 
@@ -434,6 +463,10 @@ ft_result_t do_allreduce(ft_comm* c, const void* const* send, void* const* recv,
     return FT_ERR_UNSUPPORTED;
   }
   if (count == 0) return FT_SUCCESS;
+  {
+    ft_result_t er = check_device_error(c);
+    if (er != FT_SUCCESS) return er;
+  }
   {
     int cur = -1;
     if (cudaGetDevice(&cur) != cudaSuccess || cur != c->device) FT_CHECK_RT(cudaSetDevice(c->device));
@@ -497,13 +530,14 @@ ft_result_t do_allreduce(ft_comm* c, const void* const* send, void* const* recv,
   for (PlanEntry& e : c->plans) {
     if (!(e.key == key)) continue;
     StagedArgs a2 = e.args;
+    a2.fault_rank_plus1 = c->fault_rank + 1;
     for (int l = 0; l < L; ++l) {
       RankCall& rc = a2.rc[l];
       rc.comm = c->d_comm + l;
       rc.send = s[l];
       rc.recv = r[l];
       const Segment* seg = nullptr;
-      if (e.info.algo != ALGO_ONESHOT) seg = e.mode == MODE_REGISTERED ? &c->user[(size_t)useg].seg[(size_t)l] : &c->win[(size_t)l];
+      if (e.info.algo != ALGO_ONESHOT && e.info.algo != ALGO_TWOSHOT) seg = e.mode == MODE_REGISTERED ? &c->user[(size_t)useg].seg[(size_t)l] : &c->win[(size_t)l];
       rc.win = seg ? seg->d_table : nullptr;
       rc.mc = seg ? seg->mc_base : nullptr;
     }
@@ -560,6 +594,7 @@ ft_result_t do_allreduce(ft_comm* c, const void* const* send, void* const* recv,
       LinkModel m = c->model;
       m.has_nvls = m.has_nvls && has_mc && nvls_supported(wire_dtype, op) && vec;
       if (N > 1 && (size_t)((msg_bytes + 7) / 8 * 16) > ((c->ll_bytes / (size_t)N) & ~(size_t)15)) m.max_oneshot_bytes = 0;
+      if (N > 1 && (((msg_bytes + 7) / 8 + (size_t)N - 1) / (size_t)N) * 16 > ((c->ll_bytes / (size_t)(2 * N)) & ~(size_t)15)) m.max_twoshot_bytes = 0;
       Choice ch = choose(m, N, (double)msg_bytes, mode == MODE_REGISTERED, FT_MAX_WIDTH);
       algo = ch.algo;
       widths = ch.widths;
@@ -634,7 +669,7 @@ ft_result_t do_allreduce(ft_comm* c, const void* const* send, void* const* recv,
     sh.tile_bytes *= 2;
     a.lay = make_layout((long long)count, T, es, sh.tile_bytes, vec);
   }
-  if (sh.ctas > a.lay.ntiles && algo != ALGO_ONESHOT) {
+  if (sh.ctas > a.lay.ntiles && algo != ALGO_ONESHOT && algo != ALGO_TWOSHOT) {
     sh.ctas = a.lay.ntiles;
     if (sh.nvls_reducers >= sh.ctas) sh.nvls_reducers = 0;
   }
@@ -645,6 +680,14 @@ ft_result_t do_allreduce(ft_comm* c, const void* const* send, void* const* recv,
     size_t lines = (msg_bytes + 7) / 8;
     if (N > 1 && lines * 16 > region) {
       set_last_error("message too large for the one-shot (LL) buffer; raise ll_bytes / FT_LL_BYTES");
+      return FT_ERR_INVALID;
+    }
+  } else if (algo == ALGO_TWOSHOT) {
+    // LL area of a parity half: [shot 1 | shot 2], each N regions by source; a region holds one block of lines
+    size_t region = (c->ll_bytes / (size_t)(2 * N)) & ~(size_t)15;
+    size_t lines = (msg_bytes + 7) / 8, per_block = (lines + (size_t)N - 1) / (size_t)N;
+    if (per_block * 16 > region) {
+      set_last_error("message too large for the two-shot (LL) buffer; raise ll_bytes / FT_LL_BYTES");
       return FT_ERR_INVALID;
     }
   } else if (mode == MODE_STAGING) {
@@ -696,12 +739,13 @@ ft_result_t do_allreduce(ft_comm* c, const void* const* send, void* const* recv,
     rc.send = s[l];
     rc.recv = r[l];
     const Segment* seg = nullptr;
-    if (algo != ALGO_ONESHOT) seg = mode == MODE_REGISTERED ? &c->user[(size_t)useg].seg[(size_t)l] : &c->win[(size_t)l];
+    if (algo != ALGO_ONESHOT && algo != ALGO_TWOSHOT) seg = mode == MODE_REGISTERED ? &c->user[(size_t)useg].seg[(size_t)l] : &c->win[(size_t)l];
     rc.win = seg ? seg->d_table : nullptr;
     rc.mc = seg ? seg->mc_base : nullptr;
   }
 
   a.use_tma = tma ? 1 : 0;
+  a.fault_rank_plus1 = c->fault_rank + 1;
 
   LaunchCtx ctx;
   ctx.args = &a;
@@ -751,7 +795,7 @@ ft_result_t do_allreduce(ft_comm* c, const void* const* send, void* const* recv,
       c->plans[victim] = e;
     }
   }
-  return check_device_error(c);
+  return FT_SUCCESS;
 }
 
 ft_result_t finish_create(ft_comm* c) {
@@ -895,6 +939,7 @@ ft_result_t ft_comm_destroy(ft_comm_t* c) {
   if (c->d_done) cudaFree(c->d_done);
   if (c->d_err) cudaFree(c->d_err);
   if (c->d_trace) cudaFree(c->d_trace);
+  if (c->h_err) cudaFreeHost(c->h_err);
   (void)cudaGetLastError();
   if (c->group) {
     std::lock_guard<std::mutex> lk(c->group->mu);
@@ -924,9 +969,24 @@ unsigned ft_comm_error(ft_comm_t* c) {
     if (e) return e;
   return 0;
 }
+unsigned ft_comm_error_peek(const ft_comm_t* c) {
+  if (!c || !c->h_err) return 0;
+  for (int l = 0; l < c->nlocal; ++l) {
+    const unsigned e = *(volatile unsigned*)(c->h_err + l);
+    if (e) return e;
+  }
+  return 0;
+}
 ft_result_t ft_comm_clear_error(ft_comm_t* c) {
   FT_CHECK_RT(cudaSetDevice(c->device));
+  FT_CHECK_RT(cudaDeviceSynchronize());  // a kernel that is still spinning would set the words again
   FT_CHECK_RT(cudaMemset(c->d_err, 0, sizeof(unsigned) * (size_t)c->nlocal));
+  if (c->h_err) memset(c->h_err, 0, sizeof(unsigned) * (size_t)c->nlocal);
+  return FT_SUCCESS;
+}
+ft_result_t ft_comm_inject_fault(ft_comm_t* c, int rank) {
+  if (!c || rank >= c->nranks) return FT_ERR_INVALID;
+  c->fault_rank = rank < 0 ? -1 : rank;
   return FT_SUCCESS;
 }
 
@@ -958,7 +1018,7 @@ ft_result_t ft_comm_set_widths(ft_comm_t* c, const int* widths, int nstages) {
 }
 ft_result_t ft_comm_set_algo(ft_comm_t* c, ft_algo_t algo) {
   c->policy_gen++;
-  if ((int)algo < 0 || (int)algo > ALGO_RING) return FT_ERR_INVALID;
+  if ((int)algo < 0 || ((int)algo > ALGO_RING && (int)algo != ALGO_TWOSHOT)) return FT_ERR_INVALID;
   c->algo_override = (int)algo;
   return FT_SUCCESS;
 }

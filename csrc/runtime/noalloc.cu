@@ -39,11 +39,31 @@ constexpr size_t kCommOff = 0;                                            // Com
 constexpr size_t kEpochOff = (kCommOff + sizeof(CommDev) * kMaxRanks + 255) & ~(size_t)255;
 constexpr size_t kDoneOff = kEpochOff + 256;                              // unsigned[kMaxRanks]
 constexpr size_t kErrOff = kDoneOff + 256;                                // unsigned[kMaxRanks]
-constexpr size_t kLlOff = kErrOff + 256;
+constexpr size_t kStickyOff = kErrOff + 256;                             // unsigned: first error of any call, kept until read
+constexpr size_t kLlOff = kStickyOff + 256;
 constexpr size_t kScratchBytes = kLlOff + (size_t)kMaxRanks * 2 * kLlBytes;  // ~4.02 MiB
 
 // Zero-filled when the module is loaded on a device; lives until the process exits.
 static __device__ __align__(256) unsigned char g_noalloc_scratch[kScratchBytes];
+
+// Runs in stream order right behind the collective kernel (one warp, one thread works).
+//  * Epochs: the collective advances only the epoch words of the logical ranks that took part, and the LL line
+//    tag / parity half of a call are derived from a rank's own epoch. A call with fewer ranks would therefore leave
+//    the idle ranks one epoch behind and the next larger call would pair lines with different tags. All
+//    kMaxRanks words are brought to the same (largest) value here, whatever the call's world size was.
+//  * Errors: the per-rank error words are cleared at the start of every call; the first nonzero one is copied
+//    to a sticky word that only ft_noalloc_error(clear=1) resets.
+__global__ void noalloc_epilogue(unsigned char* base) {
+  if (threadIdx.x != 0) return;
+  uint64_t* epoch = (uint64_t*)(base + kEpochOff);
+  unsigned* err = (unsigned*)(base + kErrOff);
+  unsigned* sticky = (unsigned*)(base + kStickyOff);
+  uint64_t top = 0;
+  for (int l = 0; l < kMaxRanks; ++l) top = epoch[l] > top ? epoch[l] : top;
+  for (int l = 0; l < kMaxRanks; ++l) epoch[l] = top;
+  for (int l = 0; l < kMaxRanks; ++l)
+    if (err[l] && !*sticky) *sticky = err[l];
+}
 
 struct DeviceSetup {
   bool ready = false;
@@ -132,6 +152,7 @@ extern "C" ft_result_t ft_allreduce_emulated_noalloc(const void* const* sendbufs
   // completion counters (a call that was cut short leaves them mid-count) and the sticky error words.
   // The epochs must NOT be cleared: LL lines are validated by an epoch-derived tag, which is what makes
   // stale lines from earlier calls harmless.
+  static_assert(kErrOff == kDoneOff + 256 && kStickyOff == kErrOff + 256, "done and err words are cleared together");
   if (cudaMemsetAsync(st.base + kDoneOff, 0, 512, s) != cudaSuccess) {
     (void)cudaGetLastError();
     bad(&rc, FT_ERR_CUDA, "ft_allreduce_emulated_noalloc: cudaMemsetAsync failed");
@@ -183,5 +204,30 @@ extern "C" ft_result_t ft_allreduce_emulated_noalloc(const void* const* sendbufs
     (void)cudaGetLastError();
     return FT_ERR_CUDA;
   }
+  noalloc_epilogue<<<1, 32, 0, s>>>(st.base);
+  if (cudaGetLastError() != cudaSuccess) {
+    bad(&rc, FT_ERR_CUDA, "ft_allreduce_emulated_noalloc: epilogue launch failed");
+    return rc;
+  }
   return FT_SUCCESS;
+}
+
+extern "C" unsigned ft_noalloc_error(int clear) {
+  int device = 0;
+  if (cudaGetDevice(&device) != cudaSuccess || device < 0 || device >= kMaxDevices) {
+    (void)cudaGetLastError();
+    return 0xffffffffu;
+  }
+  std::lock_guard<std::mutex> lk(g_mu);
+  DeviceSetup& st = g_setup[device];
+  if (!st.ready) return 0;  // never used on this device: nothing can have failed
+  unsigned v = 0;
+  if (cudaMemcpy(&v, st.base + kStickyOff, sizeof v, cudaMemcpyDeviceToHost) != cudaSuccess) {
+    (void)cudaGetLastError();
+    return 0xffffffffu;
+  }
+  if (clear && v) {
+    if (cudaMemset(st.base + kStickyOff, 0, sizeof v) != cudaSuccess) (void)cudaGetLastError();
+  }
+  return v;
 }

@@ -45,7 +45,10 @@ typedef enum {
 
 typedef enum { FT_SUM = 0, FT_BAND = 1, FT_MAX = 2, FT_MIN = 3, FT_BOR = 4 } ft_op_t;
 
-typedef enum { FT_ALGO_AUTO = 0, FT_ALGO_ONESHOT = 1, FT_ALGO_STAGES = 2, FT_ALGO_NVLS = 3, FT_ALGO_RING = 4 } ft_algo_t;
+/* TWOSHOT: reduce-scatter + all-gather over LL lines (no flags, no barrier) for the sizes between the one-shot's
+ * sweet spot and the bandwidth kernels; value 5 is internal (the TMA flavour of STAGES). */
+typedef enum { FT_ALGO_AUTO = 0, FT_ALGO_ONESHOT = 1, FT_ALGO_STAGES = 2, FT_ALGO_NVLS = 3, FT_ALGO_RING = 4,
+               FT_ALGO_TWOSHOT = 6 } ft_algo_t;
 
 #define FT_IN_PLACE ((const void*)(intptr_t)-1)
 
@@ -134,9 +137,20 @@ ft_result_t ft_comm_destroy(ft_comm_t*);
 int ft_comm_rank(const ft_comm_t*);
 int ft_comm_size(const ft_comm_t*);
 int ft_comm_has_multicast(const ft_comm_t*);
-/* Sticky device error word (0 = healthy): code | phase<<8 | src<<16 | rank<<24. Synchronizes nothing. */
+/* Sticky device error word (0 = healthy): code | phase<<8 | src<<16 | rank<<24.
+ * ft_comm_error copies it from the device: it BLOCKS until the work queued on the device has drained, so after it
+ * returns 0 every collective issued so far has completed cleanly. ft_comm_error_peek reads the kernel-written
+ * mirror in mapped host memory instead: no synchronisation, may lag a running kernel. Every collective call
+ * peeks first and returns FT_ERR_TIMEOUT (with the decoded word in ft_last_error()) once an EARLIER call on the
+ * communicator has tripped the watchdog - the output of that earlier call is garbage - until
+ * ft_comm_clear_error() (which waits for the device) re-arms it.
+ * (The reference has no failure path at all: an absent peer hangs MPI_Waitall, mpi_mod.hpp:1003.) */
 unsigned ft_comm_error(ft_comm_t*);
+unsigned ft_comm_error_peek(const ft_comm_t*);
 ft_result_t ft_comm_clear_error(ft_comm_t*);
+/* Fault injection for tests and drills: logical rank `rank` plays dead in every following collective (its kernel
+ * exits without touching a buffer or signalling anybody), so its peers run into the watchdog. rank < 0 = off. */
+ft_result_t ft_comm_inject_fault(ft_comm_t*, int rank);
 
 /* Overrides (NULL/0 restores automatic choice). Same meaning as env FT_TOPO / FT_ALGO. */
 ft_result_t ft_comm_set_widths(ft_comm_t*, const int* widths, int nstages);
@@ -238,11 +252,20 @@ ft_result_t ft_comm_last_call(const ft_comm_t*, ft_call_info_t*);
  * Sharing: every call on a device uses the same array, and the array keeps the previous call's contents.
  * The call clears what has to start from zero (completion counters, error words) in stream order before
  * the kernel; everything else is protected by per-call tags. Two calls whose kernels overlap on the GPU
- * (different streams, or different host threads without ordering) race on the array: serialise them. */
+ * (different streams, or different host threads without ordering) race on the array: serialise them.
+ * World sizes may change freely from call to call (4 ranks, then 8, then 2 ...): a one-thread kernel queued
+ * behind every collective keeps the epoch words of all FT_NOALLOC_MAX_RANKS logical ranks in step.
+ * Failure: the return code only covers the launch. If the device watchdog fires (20 s without a peer's
+ * line, e.g. because two calls overlapped) the recvbufs of that call hold garbage; the error word of the
+ * first such call on the device is kept until ft_noalloc_error(1) reads and clears it. */
 #define FT_NOALLOC_MAX_RANKS 8
 #define FT_NOALLOC_MAX_BYTES 16384
 ft_result_t ft_allreduce_emulated_noalloc(const void* const* sendbufs, void* const* recvbufs, int nranks,
                                           size_t count, ft_dtype_t dtype, ft_op_t op, void* stream);
+/* Sticky error word of the allocation-free entry point on the CURRENT device (0 = every call so far completed;
+ * layout as ft_comm_error). Waits for the device (one 4-byte copy), allocates nothing; clear != 0 resets it.
+ * No counterpart in the reference. */
+unsigned ft_noalloc_error(int clear);
 
 #ifdef STANDALONE_TEST
 /* Source-level alias for code written against the reference benchmark (benchmark.cpp:153). */

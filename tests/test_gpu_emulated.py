@@ -440,3 +440,78 @@ def test_native_library_is_loaded():
     assert ft._lib.has_cuda_lib()
     maps = open("/proc/self/maps").read()
     assert "libflextree.so" in maps
+
+
+def test_fired_watchdog_is_visible_on_the_next_call():
+    """A dead rank (fault injection) makes its peers time out; the kernel mirrors the error word into mapped host
+    memory, so the NEXT collective call fails loudly instead of queueing onto a broken communicator, and
+    clear_error() re-arms it."""
+    n, count = 4, 4096
+    c = ft.Communicator.emulated(n, 0, window_bytes=1 << 20, timeout_s=0.05)
+    try:
+        ts = [torch.ones(count, device="cuda") for _ in range(n)]
+        for algo in ("stages", "oneshot"):
+            c.set_algo(algo)
+            c.allreduce_multi(ts)
+            torch.cuda.synchronize()
+            assert c.poll_error() == 0 and c.error() == 0
+            c.inject_fault(2)
+            c.allreduce_multi(ts)            # rank 2 plays dead: launch succeeds, peers hit the watchdog
+            torch.cuda.synchronize()
+            e = c.poll_error()               # host-mapped mirror: no device round trip
+            assert e != 0 and (e & 0xff) == 1 and ((e >> 16) & 0xff) == 2, hex(e)
+            assert c.error() == e or c.error() != 0
+            c.inject_fault(None)
+            with pytest.raises(ft.FlexTreeError, match="watchdog"):
+                c.allreduce_multi(ts)        # refused: an earlier call failed
+            with pytest.raises(ft.FlexTreeError, match="watchdog"):
+                c.raise_if_failed()
+            c.clear_error()
+            ts = [torch.full((count,), float(r + 1), device="cuda") for r in range(n)]
+            c.allreduce_multi(ts)            # healthy again (epochs stayed aligned)
+            torch.cuda.synchronize()
+            assert c.error() == 0 and torch.all(ts[0] == 10.0) and torch.all(ts[3] == 10.0)
+    finally:
+        c.close()
+
+
+@pytest.mark.parametrize("algo,registered,tma", [("oneshot", False, None), ("stages", True, True), ("stages", True, False),
+                                                 ("stages", False, True), ("ring", True, None), ("twoshot", False, None)])
+def test_cuda_graph_replay_every_path(comms, algo, registered, tma):
+    """Capture + 20 replays for the paths with their own replay hazards: the one-shot / two-shot LL lines alternate
+    parity halves by epoch, registered mode ends in an exit barrier, the TMA ring's mbarrier phases restart in
+    every launch."""
+    n = 4
+    count = 2048 if algo in ("oneshot", "twoshot") else 60000
+    c = comms(n)
+    if algo == "twoshot" and "twoshot" not in ft.ops.constants.ALGOS:
+        pytest.skip("two-shot kernel not built")
+    c.set_algo(algo)
+    c.set_widths([2, 2] if algo == "stages" else None)
+    if tma is not None:
+        c.set_tma(tma)
+    c.reserve(count * 4)
+    ts = c.symm_empty(count, torch.float32) if registered else [torch.empty(count, device="cuda") for _ in range(n)]
+    for r in range(n):
+        ts[r].fill_(1.0)
+    c.allreduce_multi(ts)  # warm-up outside capture: resolves the plan
+    torch.cuda.synchronize()
+    assert c.last_call()["mode"] == ("registered" if registered else "staging")
+    g = torch.cuda.CUDAGraph()
+    s = torch.cuda.Stream()
+    with torch.cuda.stream(s):
+        g.capture_begin()
+        c.allreduce_multi(ts, stream=s)
+        g.capture_end()
+    for it in range(20):
+        for r in range(n):
+            ts[r].fill_(float(r + 1 + it))
+        g.replay()
+        torch.cuda.synchronize()
+        want = float(sum(r + 1 + it for r in range(n)))
+        for r in range(n):
+            assert torch.all(ts[r] == want), (algo, it, r)
+    assert c.error() == 0
+    c.set_algo("auto")
+    c.set_widths(None)
+    c.set_tma(None)

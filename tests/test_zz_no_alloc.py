@@ -58,6 +58,31 @@ def test_noalloc_matches_regular_entry_point_twice():
     comm.close()
 
 
+def test_noalloc_world_size_may_change_between_calls():
+    """A call with fewer ranks must not leave the idle ranks' epoch words behind: 4 -> 8 -> 2 -> 8 -> 3 ranks,
+    every result bit-identical to the regular entry point, and no watchdog error recorded."""
+    L = ft._lib.load()
+    torch.cuda.set_device(0)
+    stream = C.c_void_p(torch.cuda.current_stream().cuda_stream)
+    g = torch.Generator(device="cuda").manual_seed(77)
+    L.ft_noalloc_error(1)
+    for n, count in [(4, 1000), (8, 4096), (2, 33), (8, 777), (3, 2048), (8, 4096)]:
+        comm = ft.Communicator.emulated(n, 0)
+        comm.set_algo("oneshot")
+        xs = [torch.randn(count, device="cuda", generator=g) for _ in range(n)]
+        want = [torch.empty_like(x) for x in xs]
+        comm.allreduce_multi(xs, outs=want)
+        got = [torch.full_like(x, float("nan")) for x in xs]
+        torch.cuda.synchronize()
+        rc = L.ft_allreduce_emulated_noalloc(_ptrs(xs), _ptrs(got), n, count, K.FLOAT, K.SUM, stream)
+        assert rc == 0, L.ft_last_error().decode()
+        torch.cuda.synchronize()
+        for r in range(n):
+            assert torch.equal(got[r], want[r]), f"n={n} rank {r}"
+        comm.close()
+    assert L.ft_noalloc_error(0) == 0
+
+
 def test_noalloc_rejects_what_the_static_scratch_cannot_hold():
     L = ft._lib.load()
     torch.cuda.set_device(0)
