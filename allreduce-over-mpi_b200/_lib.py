@@ -129,6 +129,8 @@ def _declare(L):
     sig("ft_allreduce_ex", i32, [vp, vp, C.c_size_t, i32, i32, i32, dbl, vp, vp])
     sig("ft_allreduce_multi", i32, [C.POINTER(vp), C.POINTER(vp), C.c_size_t, i32, i32, i32, dbl, vp, vp])
     sig("ft_comm_last_call", i32, [vp, vp])
+    sig("ft_allreduce_host", i32, [vp, vp, C.c_size_t, i32, i32, vp])
+    sig("ft_allreduce_host_multi", i32, [C.POINTER(vp), C.POINTER(vp), C.c_size_t, i32, i32, dbl, vp, C.c_size_t])
     sig("ft_reduce_scatter", i32, [vp, vp, C.c_size_t, i32, i32, vp, vp])
     sig("ft_all_gather", i32, [vp, vp, C.c_size_t, i32, vp, vp])
     sig("ft_reduce_scatter_multi", i32, [C.POINTER(vp), C.POINTER(vp), C.c_size_t, i32, i32, vp, vp])

@@ -297,6 +297,31 @@ class Communicator:
             _check(self._L, rc, "ft_allreduce_multi")
         return outs
 
+    def allreduce_host(self, tensors, outs=None, op="sum", scale=1.0, chunk_bytes=0):
+        """Allreduce of HOST tensors (pinned for full speed): ``outs`` (default: in place) hold the result when the
+        call returns. Chunks of the message are pipelined H2D -> in-place zero-copy allreduce -> D2H over three
+        streams (csrc/runtime/host_pipe.cu). One tensor per logical rank for an emulated communicator, else a single
+        tensor. This is the reference's calling convention: MPI_Allreduce on host vectors (benchmark.cpp:149-159)."""
+        single = isinstance(tensors, torch.Tensor)
+        ts = [tensors] if single else list(tensors)
+        os_ = ts if outs is None else ([outs] if isinstance(outs, torch.Tensor) else list(outs))
+        n = max(1, self.emulated_ranks)
+        if len(ts) != n or len(os_) != n:
+            raise ValueError("need one host tensor per logical rank")
+        for t, o in zip(ts, os_):
+            if t.is_cuda or o.is_cuda or not (t.is_contiguous() and o.is_contiguous()):
+                raise ValueError("allreduce_host takes contiguous CPU tensors")
+            if o.dtype != t.dtype or o.numel() != t.numel():
+                raise ValueError("out must match the input dtype/size")
+        dt = K.torch_dtype_code(ts[0].dtype)
+        opc = K.OPS[op] if isinstance(op, str) else int(op)
+        s = (C.c_void_p * n)(*[t.data_ptr() for t in ts])
+        r = (C.c_void_p * n)(*[t.data_ptr() for t in os_])
+        rc = self._L.ft_allreduce_host_multi(s, r, ts[0].numel(), dt, opc, float(scale), self._h, int(chunk_bytes))
+        if rc:
+            _check(self._L, rc, "ft_allreduce_host")
+        return os_[0] if single else os_
+
     # ---- the halves ------------------------------------------------------------------------------------------------
     def reduce_scatter(self, tensor, out, op="sum", stream=None):
         """out (numel/size elements) = this rank's block of the reduction of `tensor` across ranks."""

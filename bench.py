@@ -12,6 +12,13 @@ steps, outside the timed events (the re-fill writes 256 MiB, which also flushes 
 step comes from CUDA events on the launching stream; the job time is the MAX over ranks of the summed
 step times.
 
+Also in the JSON line, all measured in this process under the same clock record:
+  vs_nccl   dist.all_reduce on the same buffers in the same timing loop (N >= 2)
+  also      the same step on private (non-symmetric) buffers and in bf16
+  e2e       Communicator.allreduce_host: the message starts and ends in pinned HOST memory (the reference's calling
+            convention), chunk-pipelined H2D / allreduce / D2H; the WHOLE result is copied back every step
+  roofline  fraction of the ceiling of the path that actually ran (NVLS: 2(N-1)/(N+1) x link rate; P2P: link rate)
+
 N == 1: there is no peer, so the same kernels are run for R=8 logical ranks emulated on the one GPU
 (one cooperative launch, every "peer" in local HBM) - this measures the kernel path against HBM instead
 of NVLink and is labelled as such in `config`.
@@ -51,93 +58,11 @@ def parse():
     ap.add_argument("--staging", action="store_true", help="private buffers (copy-in path) instead of registered")
     ap.add_argument("--sweep", action="store_true", help="also print a size sweep table to stderr")
     ap.add_argument("--e2e-steps", type=int, default=5)
+    ap.add_argument("--no-also", action="store_true", help="skip the extra rows (private buffers, bf16, NCCL)")
     return ap.parse_args()
 
 
-class ClockSampler:
-    """SM clock + throttle reasons DURING the measured region (B200_PROFILING.md). NVML is polled in-process
-    every ~2 ms from a background thread (an `nvidia-smi -lms` child cannot deliver several samples inside a
-    timed loop that lasts a few tens of milliseconds); samples are time-stamped and the ones that fall inside
-    the timed loop are the ones reported. Falls back to one-shot nvidia-smi queries without pynvml."""
-    REASONS = (("hw_slowdown", 0x8), ("hw_thermal_slowdown", 0x40), ("sw_thermal_slowdown", 0x20),
-               ("sw_power_cap", 0x4), ("hw_power_brake", 0x80))
-
-    def __init__(self, gpu_index):
-        self.idx = gpu_index
-        self.samples = []   # (t, sm_mhz, max_mhz, power_w, reasons_bitmask)
-        self._stop = threading.Event()
-        self._t = None
-        self._nvml = None
-        self._h = None
-
-    def _run(self):
-        nv, h = self._nvml, self._h
-        try:
-            mx = nv.nvmlDeviceGetMaxClockInfo(h, nv.NVML_CLOCK_SM)
-        except Exception:
-            mx = None
-        while not self._stop.is_set():
-            try:
-                sm = nv.nvmlDeviceGetClockInfo(h, nv.NVML_CLOCK_SM)
-                try:
-                    rs = nv.nvmlDeviceGetCurrentClocksEventReasons(h)
-                except Exception:
-                    rs = nv.nvmlDeviceGetCurrentClocksThrottleReasons(h)
-                try:
-                    pw = nv.nvmlDeviceGetPowerUsage(h) / 1000.0
-                except Exception:
-                    pw = None
-                self.samples.append((time.perf_counter(), float(sm), float(mx) if mx else None, pw, int(rs)))
-            except Exception:
-                pass
-            self._stop.wait(0.002)
-
-    def start(self):
-        try:
-            import pynvml as nv
-            nv.nvmlInit()
-            # map the CUDA ordinal to NVML through the PCI bus id (CUDA_VISIBLE_DEVICES may reorder)
-            import torch
-            bus = torch.cuda.get_device_properties(self.idx).pci_bus_id if hasattr(torch.cuda.get_device_properties(self.idx), "pci_bus_id") else None
-            self._h = None
-            if bus is not None:
-                for i in range(nv.nvmlDeviceGetCount()):
-                    hh = nv.nvmlDeviceGetHandleByIndex(i)
-                    if nv.nvmlDeviceGetPciInfo(hh).bus == bus:
-                        self._h = hh
-                        break
-            if self._h is None:
-                self._h = nv.nvmlDeviceGetHandleByIndex(self.idx)
-            self._nvml = nv
-            self._t = threading.Thread(target=self._run, daemon=True)
-            self._t.start()
-        except Exception:
-            self._nvml = None
-
-    def stop(self, t_begin=None, t_end=None):
-        self._stop.set()
-        if self._t:
-            self._t.join(timeout=2)
-        if self._nvml is None:   # fallback: one nvidia-smi query (not "during", flagged as such)
-            try:
-                out = subprocess.run(["nvidia-smi", "--query-gpu=clocks.sm,clocks.max.sm", "--format=csv,noheader,nounits",
-                                      "-i", str(self.idx)], capture_output=True, text=True, timeout=5).stdout.split(",")
-                return {"sm_mhz": float(out[0]), "sm_max_mhz": float(out[1]), "reasons": [], "samples": 1,
-                        "samples_in_timed_loop": 0, "window": "after the run (pynvml unavailable)"}
-            except Exception:
-                return {"sm_mhz": None, "sm_max_mhz": None, "reasons": [], "samples": 0}
-        timed = [x for x in self.samples if t_begin is not None and t_begin <= x[0] <= t_end]
-        use = timed if len(timed) >= 3 else self.samples
-        sm = sorted(x[1] for x in use)
-        mx = [x[2] for x in use if x[2]]
-        pw = [x[3] for x in use if x[3] is not None]
-        mask = 0
-        for x in use:
-            mask |= x[4]
-        return {"sm_mhz": sm[len(sm) // 2] if sm else None, "sm_max_mhz": max(mx) if mx else None,
-                "power_w_max": round(max(pw), 1) if pw else None,
-                "reasons": [name for name, bit in self.REASONS if mask & bit], "samples": len(use),
-                "samples_in_timed_loop": len(timed), "window": "timed loop" if len(timed) >= 3 else "warm-up + timed loop"}
+from flextree.utils.clocks import ClockSampler  # noqa: E402
 
 
 def busbw(nbytes, seconds, ranks):
@@ -204,6 +129,22 @@ def run_reference(args):
 
 
 # ---------------------------------------------------------------------------------------------------
+LINK_GBPS = 770.0   # measured one-directional peer copy rate of one B200 over NVLink 5 (B200_PROFILING.md)
+
+
+def path_ceiling(algo, ranks):
+    """busbw ceiling (NCCL definition, 2(N-1)/N x algbw) of the path that ran, at LINK_GBPS per direction:
+    two-phase P2P (stages, ring) moves 2(N-1)/N S per direction -> LINK; NVLS moves (1+1/N) S -> 2(N-1)/(N+1) LINK;
+    one-shot moves (N-1) S -> 2/N LINK; two-shot LL doubles the bytes of the two-phase exchange -> LINK/2."""
+    if algo == "nvls":
+        return 2.0 * (ranks - 1) / (ranks + 1) * LINK_GBPS, "NVLS: (1+1/N) S per direction"
+    if algo == "oneshot":
+        return 2.0 / ranks * LINK_GBPS, "one-shot: (N-1) S per direction"
+    if algo == "twoshot":
+        return LINK_GBPS / 2.0, "two-shot LL: 2 x 2(N-1)/N S per direction (16-byte lines carry 8)"
+    return LINK_GBPS, "two-phase P2P: 2(N-1)/N S per direction"
+
+
 def main():
     args = parse()
     if args.impl == "reference":
@@ -227,12 +168,10 @@ def main():
         return 2
     torch.cuda.set_device(local_rank)
     dev = torch.device("cuda", local_rank)
-    tdt = torch.float32 if args.dtype == "fp32" else torch.bfloat16
-    esize = 4 if args.dtype == "fp32" else 2
-    count = args.bytes // esize
-    nbytes = count * esize
     emulated = n == 1
     ranks = EMULATED_RANKS if emulated else n
+    nloc = ranks if emulated else 1
+    nbytes = args.bytes // 16 * 16
 
     if not emulated:
         dist.init_process_group("nccl", device_id=dev)
@@ -244,33 +183,10 @@ def main():
     if args.widths:
         comm.set_widths([int(x) for x in args.widths.replace("x", ",").split(",")])
 
-    nloc = ranks if emulated else 1
-    gen = torch.Generator(device=dev).manual_seed(1234 + rank)
-    pristine = [torch.randn(count, device=dev, dtype=torch.float32, generator=gen).to(tdt) for _ in range(nloc)]
-    if args.staging:
-        bufs = [torch.empty(count, device=dev, dtype=tdt) for _ in range(nloc)]
-    else:
-        b = comm.symm_empty(count, tdt)
-        bufs = b if emulated else [b]
-    if args.staging:
-        comm.reserve(nbytes)
-
-    def refill():
-        for b_, p_ in zip(bufs, pristine):
-            b_.copy_(p_)
-
     use_nccl = args.impl == "nccl"
     if use_nccl and emulated:
         os.write(real_stdout, (json.dumps({"impl": "nccl", "unavailable": "NCCL has nothing to do on one GPU"}) + "\n").encode())
         return 0
-
-    def step(stream=None):
-        if use_nccl:
-            dist.all_reduce(bufs[0])          # the library baseline: same buffers, same timing loop
-        elif emulated:
-            comm.allreduce_multi(bufs, stream=stream)
-        else:
-            comm.allreduce(bufs[0], stream=stream)
 
     def barrier():
         torch.cuda.synchronize()
@@ -278,82 +194,205 @@ def main():
             dist.barrier()
             torch.cuda.synchronize()
 
-    # correctness gate on the first step (against fp64 torch math)
-    refill()
-    step()
-    torch.cuda.synchronize()
-    if comm.error():
-        print(f"bench.py: device error {comm.error():#x}", file=sys.stderr)
-        return 3
-    if emulated:
-        want = torch.stack([p.double() for p in pristine]).sum(0)
-    else:
-        want = pristine[0].double().clone()
-        dist.all_reduce(want)
-    tol = 1e-4 if tdt == torch.float32 else 0.25
-    err = (bufs[0].double() - want).abs().max().item()
-    if not err <= tol * max(1.0, want.abs().max().item()):
-        print(f"bench.py: WRONG RESULT max abs err {err}", file=sys.stderr)
-        return 4
-    del want
+    class Arm:
+        """One measured configuration: dtype x buffer kind x implementation, same timing loop for all."""
+
+        def __init__(self, dtype, staging, nccl):
+            self.tdt = torch.float32 if dtype == "fp32" else torch.bfloat16
+            self.dtype, self.staging, self.nccl = dtype, staging, nccl
+            esize = 4 if dtype == "fp32" else 2
+            self.count = nbytes // esize
+            gen = torch.Generator(device=dev).manual_seed(1234 + rank)
+            self.pristine = [torch.randn(self.count, device=dev, dtype=torch.float32, generator=gen).to(self.tdt) for _ in range(nloc)]
+            if staging or nccl:
+                self.bufs = [torch.empty(self.count, device=dev, dtype=self.tdt) for _ in range(nloc)]
+                if not nccl:
+                    comm.reserve(nbytes)
+            else:
+                b = comm.symm_empty(self.count, self.tdt)
+                self.bufs = b if emulated else [b]
+
+        def refill(self):
+            for b_, p_ in zip(self.bufs, self.pristine):
+                b_.copy_(p_)
+
+        def step(self):
+            if self.nccl:
+                dist.all_reduce(self.bufs[0])      # the library baseline: same buffers, same timing loop
+            elif emulated:
+                comm.allreduce_multi(self.bufs)
+            else:
+                comm.allreduce(self.bufs[0])
+
+        def check(self):
+            """Correctness gate on one step, against fp64 torch math (NCCL fp64 sum across ranks)."""
+            self.refill()
+            self.step()
+            torch.cuda.synchronize()
+            if not self.nccl and comm.error():
+                raise RuntimeError(f"device error {comm.error():#x}")
+            if emulated:
+                want = torch.stack([p.double() for p in self.pristine]).sum(0)
+            else:
+                want = self.pristine[0].double().clone()
+                dist.all_reduce(want)
+            tol = 1e-4 if self.tdt == torch.float32 else 0.25
+            err = (self.bufs[0].double() - want).abs().max().item()
+            if not err <= tol * max(1.0, want.abs().max().item()):
+                raise RuntimeError(f"WRONG RESULT max abs err {err}")
+
+        def time(self, steps, warmup):
+            """(ms per step = max over ranks of the summed CUDA-event times / steps, wall window of the loop)"""
+            for _ in range(warmup):
+                self.refill()
+                self.step()
+            barrier()
+            ev = [(torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)) for _ in range(steps)]
+            barrier()
+            t0 = time.perf_counter()
+            for i in range(steps):
+                self.refill()          # untimed: restores the input and evicts the previous result from L2
+                ev[i][0].record()
+                self.step()
+                ev[i][1].record()
+            barrier()
+            t1 = time.perf_counter()
+            total = torch.tensor([sum(a.elapsed_time(b) for a, b in ev)], device=dev, dtype=torch.float64)
+            if not emulated:
+                dist.all_reduce(total, op=dist.ReduceOp.MAX)
+            return total.item() / steps, (t0, t1)
+
+        def free(self):
+            self.bufs = self.pristine = None
 
     sampler = ClockSampler(local_rank)
     if rank == 0:
         sampler.start()
-    for _ in range(args.warmup):
-        refill()
-        step()
-    barrier()
-    ev = [(torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)) for _ in range(args.steps)]
-    barrier()
-    t_wall0 = time.perf_counter()
-    for i in range(args.steps):
-        refill()          # untimed: restores the input and evicts the previous result from L2
-        ev[i][0].record()
-        step()
-        ev[i][1].record()
-    barrier()
-    t_wall = time.perf_counter() - t_wall0
-    clocks = sampler.stop(t_wall0, t_wall0 + t_wall) if rank == 0 else None
-    ms = [a.elapsed_time(b) for a, b in ev]
-    total_ms = torch.tensor([sum(ms)], device=dev, dtype=torch.float64)
-    if not emulated:
-        dist.all_reduce(total_ms, op=dist.ReduceOp.MAX)
-    ms_per_step = total_ms.item() / args.steps
+    windows = []
+
+    main_arm = Arm(args.dtype, args.staging, use_nccl)
+    try:
+        main_arm.check()
+    except RuntimeError as e:
+        print(f"bench.py: {e}", file=sys.stderr)
+        return 4
+    ms_per_step, win = main_arm.time(args.steps, args.warmup)
+    windows.append(win)
+    t_wall = win[1] - win[0]
     info = {"algo": "nccl (torch.distributed.all_reduce)"} if use_nccl else comm.last_call()
     bb = busbw(nbytes, ms_per_step / 1e3, ranks)
 
-    # ---- end to end through the public API: pinned host -> device, allreduce, result back to host ---------
-    e2e_steps = max(1, min(args.steps, args.e2e_steps))
-    host_in = [torch.randn(count, dtype=torch.float32).to(tdt).pin_memory() for _ in range(nloc)]
-    host_out = torch.empty(11, dtype=tdt).pin_memory()
-    for _ in range(2):
-        for b_, h_ in zip(bufs, host_in):
-            b_.copy_(h_, non_blocking=True)
-        step()
-        host_out.copy_(bufs[0][9:20], non_blocking=True)
-    barrier()
-    e0, e1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
-    e0.record()
-    for _ in range(e2e_steps):
-        for b_, h_ in zip(bufs, host_in):
-            b_.copy_(h_, non_blocking=True)                       # H2D of this step's input
-        step()
-        host_out.copy_(bufs[0][9:20], non_blocking=True)          # D2H of the result check (reference CHECK 9..19)
-        torch.cuda.current_stream().synchronize()
-    e1.record()
-    barrier()
-    e2e_ms = torch.tensor([e0.elapsed_time(e1) / e2e_steps], device=dev, dtype=torch.float64)
-    if not emulated:
-        dist.all_reduce(e2e_ms, op=dist.ReduceOp.MAX)
-    e2e_bb = busbw(nbytes, e2e_ms.item() / 1e3, ranks)
+    # ---- the same step in the other configurations, same process, same clock record -------------------------
+    also, vs_nccl = [], None
+    if not args.no_also and not use_nccl:
+        extra = [(args.dtype, not args.staging, False), ("bf16" if args.dtype == "fp32" else "fp32", args.staging, False)]
+        for dtype, staging, nccl in extra:
+            try:
+                arm = Arm(dtype, staging, nccl)
+                arm.check()
+                ms, w = arm.time(args.steps, args.warmup)
+                windows.append(w)
+                call = comm.last_call()
+                ceil, what = path_ceiling(call["algo"], ranks)
+                row = {"dtype": dtype, "buffers": "private (copy-in)" if staging else "symmetric (zero-copy)", "ms_per_step": ms,
+                       "busbw_per_rank_GBps": busbw(nbytes, ms / 1e3, ranks), "algo": call["algo"], "widths": call["widths"],
+                       "ctas": call["ctas"]}
+                if not emulated:
+                    row["roofline_fraction"] = round(row["busbw_per_rank_GBps"] / ceil, 4)
+                also.append(row)
+                arm.free()
+            except Exception as e:  # an extra row must never cost the headline number
+                also.append({"dtype": dtype, "buffers": "private" if staging else "symmetric", "error": str(e)[:200]})
+        if not emulated:
+            nccl_rows = []
+            for dtype in (args.dtype, "bf16" if args.dtype == "fp32" else "fp32"):
+                arm = Arm(dtype, True, True)
+                arm.check()
+                ms, w = arm.time(args.steps, args.warmup)
+                windows.append(w)
+                nccl_rows.append({"dtype": dtype, "ms_per_step": ms, "busbw_per_rank_GBps": busbw(nbytes, ms / 1e3, ranks)})
+                arm.free()
+            ours = {args.dtype: ms_per_step}
+            for r_ in also:
+                if "ms_per_step" in r_ and r_["buffers"].startswith("symmetric" if not args.staging else "private"):
+                    ours.setdefault(r_["dtype"], r_["ms_per_step"])
+            vs_nccl = {"impl": "torch.distributed.all_reduce (NCCL %s), same buffers size, same loop" % ".".join(map(str, torch.cuda.nccl.version())),
+                       "ms_per_step": nccl_rows[0]["ms_per_step"], "busbw_per_rank_GBps": nccl_rows[0]["busbw_per_rank_GBps"],
+                       "ratio": nccl_rows[0]["ms_per_step"] / ms_per_step, "rows": nccl_rows,
+                       "ratio_private_buffers": next((nccl_rows[0]["ms_per_step"] / r_["ms_per_step"] for r_ in also
+                                                      if r_.get("dtype") == args.dtype and str(r_.get("buffers", "")).startswith("private") and "ms_per_step" in r_), None),
+                       "ratio_bf16": (nccl_rows[1]["ms_per_step"] / ours["bf16"]) if "bf16" in ours and nccl_rows[1]["dtype"] == "bf16" else None}
+
+    clocks = None
+    if rank == 0:
+        lo = min(w[0] for w in windows)
+        hi = max(w[1] for w in windows)
+        clocks = sampler.stop(lo, hi)
+
+    # ---- end to end through the public API: the message starts and ends in pinned HOST memory ----------------
+    # Communicator.allreduce_host = ft_allreduce_host_multi: chunked H2D -> in-place allreduce -> D2H over three
+    # streams; every step copies the whole input up and the WHOLE result back. Timed on the host clock around K
+    # synchronous calls (the API returns when the result is in host memory), barrier + synchronize on both sides,
+    # max over ranks.
+    e2e = None
+    if not use_nccl:
+        e2e_steps = max(1, min(args.steps, args.e2e_steps))
+        tdt = main_arm.tdt
+        host_in = [torch.randn(main_arm.count, dtype=torch.float32).to(tdt).pin_memory() for _ in range(nloc)]
+        host_out = [torch.empty(main_arm.count, dtype=tdt).pin_memory() for _ in range(nloc)]
+
+        def e2e_step():
+            if emulated:
+                comm.allreduce_host(host_in, outs=host_out)
+            else:
+                comm.allreduce_host(host_in[0], outs=host_out[0])
+
+        for _ in range(2):
+            e2e_step()
+        # gate: the host result equals the fp64 sum of the host inputs
+        if emulated:
+            want = torch.stack([h.double() for h in host_in]).sum(0)
+        else:
+            want = host_in[0].double().to(dev)
+            dist.all_reduce(want)
+            want = want.cpu()
+        err = (host_out[0].double() - want).abs().max().item()
+        tol = 1e-4 if tdt == torch.float32 else 0.25
+        if not err <= tol * max(1.0, want.abs().max().item()):
+            print(f"bench.py: WRONG e2e RESULT max abs err {err}", file=sys.stderr)
+            return 5
+        del want
+        barrier()
+        # device clock: each call returns only when its last D2H chunk has landed (it synchronises its output stream), so
+        # two events recorded on the idle current stream before and after the K calls bracket all of their device work
+        ea, eb = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+        t0 = time.perf_counter()
+        ea.record()
+        for _ in range(e2e_steps):
+            e2e_step()
+        eb.record()
+        torch.cuda.synchronize()
+        dt_wall = time.perf_counter() - t0
+        barrier()
+        e2e_ms = torch.tensor([ea.elapsed_time(eb) / e2e_steps], device=dev, dtype=torch.float64)
+        if not emulated:
+            dist.all_reduce(e2e_ms, op=dist.ReduceOp.MAX)
+        e2e_bb = busbw(nbytes, e2e_ms.item() / 1e3, ranks)
+        e2e = {"value": e2e_bb * n, "unit": "GB/s", "ms_per_step": e2e_ms.item(), "steps": e2e_steps,
+               "h2d_bytes_per_step": nbytes * nloc, "d2h_bytes_per_step": nbytes * nloc,
+               "pcie_GBps_per_direction": nbytes * nloc / (e2e_ms.item() / 1e3) / 1e9,
+               "api": "Communicator.allreduce_host(pinned_in, pinned_out): 16 MiB chunks pipelined H2D / zero-copy allreduce / D2H "
+                      "over three streams; whole result copied back; CUDA events around K synchronous calls, max over ranks",
+               "wall_ms_per_step_rank0": round(dt_wall * 1e3 / e2e_steps, 3)}
+        del host_in, host_out
 
     sweep = None
     if args.sweep:
         sweep = []
+        esize = 4 if args.dtype == "fp32" else 2
         for sz in [1 << 10, 8 << 10, 64 << 10, 512 << 10, 4 << 20, 32 << 20, nbytes]:
             cnt = sz // esize
-            views = [b_[:cnt] for b_ in bufs]
+            views = [b_[:cnt] for b_ in main_arm.bufs]
             def one():
                 if emulated:
                     comm.allreduce_multi(views)
@@ -382,20 +421,27 @@ def main():
         except Exception:
             pass
         if emulated:
-            # HBM roofline of the emulation: copy-in none (registered) ; RS reads R*S/R.. total traffic below
-            roof = "HBM (single GPU emulation)"
-            # bytes moved per GPU-wide step: RS reads R*S, writes S ; AG reads S*(R... ) writes R*S  ~ (2R+1..2)S
-            hbm_bytes = (2 * ranks + 2) * nbytes if not args.staging else (2 * ranks + 4) * nbytes
-            frac = (hbm_bytes / (ms_per_step / 1e3) / 1e9) / peaks.get("hbm_gbs", 6650.0)
+            # One GPU: every "link" is HBM. The floor is the compulsory traffic - each logical rank's input is read once
+            # and its output written once, 2 R S - at the measured copy rate. (The kernels issue (3R-1) S of loads and
+            # stores for a flat plan on registered buffers; the all-gather re-reads largely hit in L2: ncu counts ~21 S
+            # of DRAM traffic at 64 MiB, profiles/ncu_staged_tma_emulated.md.)
+            roof = "HBM, single-GPU emulation: compulsory bytes 2*R*S at the measured copy rate (MEASURED_PEAKS.json hbm_gbs)"
+            frac = (2 * ranks * nbytes / (ms_per_step / 1e3) / 1e9) / peaks.get("hbm_gbs", 6553.9)
+            ceiling = None
         else:
-            roof = "NVLink 770 GB/s per direction (measured peer copy, B200_PROFILING.md)"
-            frac = bb / 770.0
+            ceiling, what = path_ceiling(info.get("algo"), ranks)
+            roof = f"NVLink {LINK_GBPS:.0f} GB/s per direction (measured peer copy); path ceiling {ceiling:.0f} GB/s busbw ({what})"
+            frac = bb / ceiling
         out = {
             "metric": METRIC, "value": bb * n, "unit": "GB/s", "n_gpus": n, "steps": args.steps,
             "warmup": args.warmup, "ms_per_step": ms_per_step, "higher_is_better": True, "scaling": "weak",
             "vs_baseline": None, "dtype": args.dtype, "data": "synthetic (randn, fixed seed)",
             "busbw_per_rank_GBps": bb, "algbw_GBps": nbytes / (ms_per_step / 1e3) / 1e9,
-            "roofline": {"against": roof, "fraction": round(frac, 4)},
+            "roofline": {"against": roof, "fraction": round(frac, 4), "ceiling_busbw_GBps": ceiling,
+                         "link_bytes_per_direction": None if emulated else (
+                             (1 + 1.0 / ranks) * nbytes if info.get("algo") == "nvls" else 2.0 * (ranks - 1) / ranks * nbytes),
+                         "link_GBps_per_direction": None if emulated else round(
+                             ((1 + 1.0 / ranks) if info.get("algo") == "nvls" else 2.0 * (ranks - 1) / ranks) * nbytes / (ms_per_step / 1e3) / 1e9, 1)},
             "config": {"model": f"allreduce {args.dtype} SUM in place", "message_bytes": nbytes, "ranks": ranks,
                        "global_batch": None, "seq_len": None,
                        "parallelism": (f"{ranks} logical ranks emulated on 1 GPU (one cooperative launch, HBM-bound, no NVLink)"
@@ -404,12 +450,14 @@ def main():
                        "l2": "message > L2 and re-filled (256 MiB written) between timed steps",
                        "call": info, "wall_s_timed_loop": round(t_wall, 3)},
             "clocks": clocks,
-            "e2e": {"value": e2e_bb * n, "unit": "GB/s", "ms_per_step": e2e_ms.item(), "steps": e2e_steps,
-                    "h2d_bytes_per_step": nbytes * nloc, "d2h_bytes_per_step": 11 * esize,
-                    "api": "Communicator.allreduce on a symmetric tensor; input copied from pinned host memory each step"},
+            "e2e": e2e,
             "gpu_launches": 0 if use_nccl else args.steps,
             "impl": args.impl,
         }
+        if vs_nccl:
+            out["vs_nccl"] = vs_nccl
+        if also:
+            out["also"] = also
         if sweep:
             out["sweep"] = sweep
         os.write(real_stdout, (json.dumps(out) + "\n").encode())

@@ -16,7 +16,15 @@ def load(name):
     path = os.path.join(G, name)
     if not os.path.exists(path):
         return []
-    return [json.loads(l) for l in open(path) if l.strip().startswith("{")]
+    rows = [json.loads(l) for l in open(path) if l.strip().startswith("{")]
+    # a timing without a clock record is not admissible (B200_PROFILING.md): such rows are dropped, loudly
+    bad = [r for r in rows if "us" in r and not (r.get("clocks") or {}).get("sm_mhz")]
+    if bad:
+        print(f"make_profiles: {name}: REFUSING {len(bad)} of {len(rows)} rows that carry no clock record")
+    hot = [r for r in rows if set((r.get("clocks") or {}).get("reasons", [])) & {"hw_slowdown", "hw_thermal_slowdown", "sw_thermal_slowdown"}]
+    if hot:
+        print(f"make_profiles: {name}: REFUSING {len(hot)} rows measured under a thermal / hardware slowdown")
+    return [r for r in rows if r not in bad and r not in hot]
 
 
 def sweep_table(n, fname, note=""):

@@ -18,7 +18,10 @@ import torch
 import torch.distributed as dist
 
 sys.path.insert(0, os.path.dirname(os.path.dirname(os.path.abspath(__file__))))
+import time  # noqa: E402
+
 import flextree as ft  # noqa: E402
+from flextree.utils.clocks import ClockSampler  # noqa: E402
 
 
 def main():
@@ -51,6 +54,10 @@ def main():
     priv.zero_()
     comm.reserve(args.max)
     fout = open(args.out, "a") if rank == 0 else None
+    sampler = ClockSampler(local)   # one NVML poller for the whole sweep; every row gets the samples of its own loop
+    if rank == 0:
+        sampler.start()
+    last_window = [0.0, 0.0]
 
     def timed(fn, nbytes):
         reps = 50 if nbytes <= (1 << 20) else (20 if nbytes <= (64 << 20) else 8)
@@ -60,23 +67,27 @@ def main():
         dist.barrier()
         torch.cuda.synchronize()
         a, b = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+        last_window[0] = time.perf_counter()
         a.record()
         for _ in range(reps):
             fn()
         b.record()
         torch.cuda.synchronize()
+        last_window[1] = time.perf_counter()
         t = torch.tensor([a.elapsed_time(b) / reps], device=dev, dtype=torch.float64)
         dist.all_reduce(t, op=dist.ReduceOp.MAX)
         return t.item() * 1e3  # us
 
     def emit(rec):
         if rank == 0:
+            if "us" in rec:
+                rec["clocks"] = sampler.window(last_window[0], last_window[1])
             fout.write(json.dumps(rec) + "\n")
             fout.flush()
             print(json.dumps(rec), flush=True)
 
     impls = [("auto", None)]
-    impls += [("oneshot", None), ("stages", [world]), ("ring", None)]
+    impls += [("oneshot", None), ("twoshot", None), ("stages", [world]), ("ring", None)]
     if comm.has_multicast:
         impls.append(("nvls", None))
     if args.all_widths:
@@ -156,6 +167,8 @@ def main():
         for algo, widths in impls:
             for buf, mode in ((symm, "registered"),) + (((priv, "staging"),) if args.staging else ()):
                 if algo == "oneshot" and nbytes > (256 << 10):
+                    continue
+                if algo == "twoshot" and nbytes > (4 << 20):
                     continue
                 if algo == "ring" and nbytes > (64 << 20):
                     continue

@@ -26,6 +26,7 @@
 
 namespace ft {
 void set_last_error(const std::string& s);  // planner/c_api.cc
+void host_pipe_release(const ft_comm_t* c);  // runtime/host_pipe.cu
 }
 using namespace ft;
 
@@ -423,7 +424,7 @@ ft_result_t check_device_error(ft_comm* c) {
   for (int l = 0; l < c->nlocal; ++l) {
     const unsigned e = *(volatile unsigned*)(c->h_err + l);
     if (e) {
-      char buf[200];
+      char buf[320];
       snprintf(buf, sizeof buf,
                "device watchdog fired in an earlier call on this communicator: error word %#x (code %u, phase %u, "
                "waiting for rank %u, on rank %u); its results are invalid - ft_comm_clear_error() to continue",
@@ -805,6 +806,11 @@ ft_result_t finish_create(ft_comm* c) {
 
 }  // namespace
 
+namespace ft {
+int comm_nlocal(const ft_comm_t* c) { return c->nlocal; }
+int comm_device(const ft_comm_t* c) { return c->device; }
+}  // namespace ft
+
 extern "C" {
 
 void ft_comm_options_default(ft_comm_options_t* o) {
@@ -929,6 +935,7 @@ ft_result_t ft_comm_destroy(ft_comm_t* c) {
   if (!c) return FT_SUCCESS;
   cudaSetDevice(c->device);
   cudaDeviceSynchronize();
+  host_pipe_release(c);
   if (c->kind == COMM_PROCESS) c->bs.barrier();
   destroy_segments(&c->win);
   destroy_segments(&c->pad);

@@ -200,6 +200,20 @@ ft_result_t ft_allreduce_multi(const void* const* sendbufs, void* const* recvbuf
                                ft_dtype_t dtype, ft_dtype_t wire_dtype, ft_op_t op, double scale,
                                ft_comm_t* comm, void* stream);
 
+/* Host-resident data (what the reference's MPI_Allreduce takes: benchmark.cpp:119-159 allreduces a malloc'ed
+ * vector). Synchronous like MPI_Allreduce: when the call returns, recvbuf (host memory) holds the result.
+ * The message is cut into chunks (env FT_HOST_CHUNK_BYTES, default 16 MiB) that are pipelined over three streams -
+ * H2D of chunk i+1, in-place zero-copy allreduce of chunk i, D2H of chunk i-1 - so the call costs about
+ * max(H2D, D2H), not their sum plus the collective. Pass page-locked memory (cudaHostAlloc / cudaHostRegister /
+ * torch pin_memory) for full PCIe speed; pageable memory works but copies synchronously.
+ * Collective: the first call (and any call with a larger chunk size) allocates symmetric chunk slots.
+ * sendbuf may be FT_IN_PLACE. `_multi`: one pointer per logical rank (emulated communicators), fused scale,
+ * explicit chunk size (0 = default). */
+ft_result_t ft_allreduce_host(const void* sendbuf, void* recvbuf, size_t count, ft_dtype_t dtype, ft_op_t op,
+                              ft_comm_t* comm);
+ft_result_t ft_allreduce_host_multi(const void* const* sendbufs, void* const* recvbufs, size_t count,
+                                    ft_dtype_t dtype, ft_op_t op, double scale, ft_comm_t* comm, size_t chunk_bytes);
+
 /* The two halves of the algorithm as collectives of their own (the reference's tree_allreduce is a
  * reduce-scatter loop followed by an all-gather loop, mpi_mod.hpp:988-1029 / :1050-1060).
  * ft_reduce_scatter: sendbuf holds nranks*recvcount elements, recvbuf receives this rank's reduced block.

@@ -515,3 +515,23 @@ def test_cuda_graph_replay_every_path(comms, algo, registered, tma):
     c.set_algo("auto")
     c.set_widths(None)
     c.set_tma(None)
+
+
+def test_allreduce_host_pipelined(comms):
+    """Host-resident message (the reference's calling convention): chunked H2D -> in-place allreduce -> D2H over three
+    streams; result equals the fp64 sum of the host inputs, in place and out of place, odd sizes, several chunk sizes."""
+    n = 4
+    c = comms(n)
+    c.set_algo("auto")
+    g = torch.Generator().manual_seed(5)
+    for count, chunk in ((1 << 20, 1 << 20), (300001, 256 << 10), (5000, 0), ((1 << 20) + 4, 1 << 20)):
+        xs = [torch.randn(count, generator=g).pin_memory() for _ in range(n)]
+        want = torch.stack(xs).double().sum(0)
+        outs = [torch.empty(count).pin_memory() for _ in range(n)]
+        c.allreduce_host(xs, outs=outs, chunk_bytes=chunk)
+        for r in range(n):
+            assert torch.allclose(outs[r].double(), want, rtol=1e-5, atol=1e-5), (count, r)
+            assert torch.equal(outs[r], outs[0])
+        c.allreduce_host(xs, scale=0.25, chunk_bytes=chunk)          # in place, fused scale
+        assert torch.allclose(xs[2].double(), want * 0.25, rtol=1e-5, atol=1e-5)
+    assert c.error() == 0
