@@ -157,6 +157,11 @@ class Communicator:
             raise FlexTreeError(f"flextree: device watchdog fired (error word {e:#x}: code {e & 0xff}, phase {(e >> 8) & 0xff}, "
                                 f"waiting for rank {(e >> 16) & 0xff}, on rank {e >> 24}); the results of that collective are invalid")
 
+    def set_tuning(self, key, value):
+        """Kernel-variant / launch-shape knobs for scans (ft_comm_set_tuning): nvls_variant, nvls_flags, nvls_ctas,
+        nvls_max_tile_bytes."""
+        _check(self._L, self._L.ft_comm_set_tuning(self._h, key.encode(), int(value)), "ft_comm_set_tuning")
+
     def inject_fault(self, rank):
         """Tests/drills: logical rank `rank` plays dead in the following collectives (None = off)."""
         _check(self._L, self._L.ft_comm_inject_fault(self._h, -1 if rank is None else int(rank)), "ft_comm_inject_fault")

@@ -431,7 +431,7 @@ struct StagedCta {
 
   // In-switch reduction of my block of tile t: one multimem.ld_reduce pulls and sums the N copies,
   // one multimem.st broadcasts the result into every rank's window.
-  template <int UNR> FT_DEV void nvls_reduce_tile(int t) {
+  template <int UNR, bool EMU> FT_DEV void nvls_reduce_tile(int t) {
     long long start;
     const long long n = tile_valid(r, t, &start);
     if (n <= 0) return;
@@ -447,7 +447,7 @@ struct StagedCta {
 #pragma unroll
       for (int u = 0; u < UNR; ++u) {
         const long long q = q0 + (long long)u * nth + tid;
-        if (q < nvec) v[u] = be.template mc_ld_reduce<T, Op, VE>(rc, base + q * (long long)sizeof(PackT), a.plan.nranks);
+        if (q < nvec) v[u] = be.template mc_ld_reduce<T, Op, VE, EMU>(rc, base + q * (long long)sizeof(PackT), a.plan.nranks);
       }
     };
     load(cur, 0);
@@ -468,13 +468,101 @@ struct StagedCta {
             for (int i = 0; i < VE; ++i) cur[u].e[i] = EL::down(acc[i]);
           }
         }
-        be.template mc_st<T, VE>(rc, base + q * (long long)sizeof(PackT), cur[u], a.plan.nranks);
+        be.template mc_st<T, VE, EMU>(rc, base + q * (long long)sizeof(PackT), cur[u], a.plan.nranks);
       }
       if (more) {
 #pragma unroll
         for (int u = 0; u < UNR; ++u) cur[u] = nxt[u];
       }
     }
+  }
+
+  // Same work without the software pipeline: UNR loads, then UNR stores. Half the payload registers of the
+  // pipelined form (no second buffer), so larger UNR fits without spilling. Also hosts the two measurement modes
+  // that take the switch path apart: NVLS_NO_ST keeps only the in-switch reduce (result lands in my window only),
+  // NVLS_NO_LD keeps only the multicast store (of my own unreduced block) - both give wrong sums by design.
+  enum { NVLS_NO_ST = 1, NVLS_NO_LD = 2, NVLS_KEEP_END = 4 };
+  template <int UNR, bool EMU> FT_DEV void nvls_reduce_tile_simple(int t) {
+    long long start;
+    const long long n = tile_valid(r, t, &start);
+    if (n <= 0) return;
+    const long long nvec = (n + VE - 1) / VE;
+    const int nth = be.nthr(), tid = be.tid();
+    const long long step = (long long)nth * UNR;
+    const long long base = woff + start * (long long)sizeof(T);
+    char* wr = rc.win[r];
+    const bool no_st = (a.nvls_flags & NVLS_NO_ST) != 0, no_ld = (a.nvls_flags & NVLS_NO_LD) != 0;
+    for (long long q0 = 0; q0 < nvec; q0 += step) {
+      PackT v[UNR];
+#pragma unroll
+      for (int u = 0; u < UNR; ++u) {
+        const long long q = q0 + (long long)u * nth + tid;
+        if (q < nvec) {
+          const long long off = base + q * (long long)sizeof(PackT);
+          v[u] = no_ld ? ld_win(wr, off, false) : be.template mc_ld_reduce<T, Op, VE, EMU>(rc, off, a.plan.nranks);
+        }
+      }
+#pragma unroll
+      for (int u = 0; u < UNR; ++u) {
+        const long long q = q0 + (long long)u * nth + tid;
+        if (q >= nvec) continue;
+        if constexpr (EL::is_float) {
+          if (a.apply_scale) {
+            A acc[VE];
+#pragma unroll
+            for (int i = 0; i < VE; ++i) acc[i] = EL::up(v[u].e[i]);
+            scale_acc(acc);
+#pragma unroll
+            for (int i = 0; i < VE; ++i) v[u].e[i] = EL::down(acc[i]);
+          }
+        }
+        const long long off = base + q * (long long)sizeof(PackT);
+        if (no_st) st_win(wr, off, v[u]);
+        else be.template mc_st<T, VE, EMU>(rc, off, v[u], a.plan.nranks);
+      }
+    }
+  }
+  // The in-switch reduce of one tile. Inner-loop variants (ft_comm_set_tuning "nvls_variant"; each one is its own
+  // kernel in kernels/nvls_kernel.cu so that it gets its own register allocation):
+  //   0  pipelined, 8 vectors per thread (two register buffers)      1  pipelined, 4 vectors
+  //   2  plain, 8 vectors     3  plain, 4 vectors     4  plain, 16 vectors
+  //   5  warp-specialised: half the warps run multimem.ld_reduce into a shared-memory ring, the other half drain it
+  //      with multimem.st (CUDA only; kernels/nvls_ws.cuh)
+  FT_DEV void nvls_tile(int t) {
+    // EMU: no multicast mapping (single-GPU emulation) - the back end plays the switch with a loop over the N
+    // windows. A template flag, not a branch inside the loops: the multi-GPU code carries no trace of it.
+    constexpr int U = (VE == 1) ? 1 : 4;
+    if (rc.mc) nvls_reduce_tile_simple<U, false>(t);
+    else nvls_reduce_tile_simple<U, true>(t);
+  }
+  // One variant, chosen at compile time (the dedicated registered-buffer kernel, kernels/nvls_kernel.cu).
+  template <int VARIANT, bool EMU> FT_DEV void nvls_tile_variant(int t) {
+    if constexpr (VARIANT == 1) nvls_reduce_tile<4, EMU>(t);
+    else if constexpr (VARIANT == 2) nvls_reduce_tile_simple<8, EMU>(t);
+    else if constexpr (VARIANT == 3) nvls_reduce_tile_simple<4, EMU>(t);
+    else if constexpr (VARIANT == 4) nvls_reduce_tile_simple<16, EMU>(t);
+    else if constexpr (VARIANT == 5 && BE::kTma) be.template nvls_tile_ws<T, IO, Op, VE, EMU>(*this, t);
+    else nvls_reduce_tile<8, EMU>(t);
+  }
+  // NVLS on registered (zero-copy) buffers of the wire type: the whole call for this CTA. Same protocol as the
+  // registered branch of run_nvls, without the code of the private-buffer roles around it.
+  template <int VARIANT, bool EMU> FT_DEV void run_nvls_registered() {
+    const int G = a.ctas, nt = a.lay.ntiles;
+    const int mine = cta < nt ? (nt - cta + G - 1) / G : 0;
+    signal_group(PH_IN, 0, E + mine);
+    for (int j = 0; j < mine; ++j) {
+      wait_group(PH_IN, 0, E + j + 1);
+      nvls_tile_variant<VARIANT, EMU>(cta + j * G);
+      be.sync();
+      signal_group(PH_RS0, 0, E + j + 1);
+    }
+    for (int j = 0; j < mine; ++j) wait_group(PH_RS0, 0, E + j + 1);
+    if (a.nvls_flags & NVLS_KEEP_END) {  // see run_nvls: the exit barrier is redundant
+      be.sync();
+      signal_group(PH_END, 0, E + 1);
+      wait_group(PH_END, 0, E + 1);
+    }
+    be.finish(cd, a.ctas);
   }
 
   // Local copy of every block of tile t from my window to the user buffer through the epilogue.
@@ -538,7 +626,6 @@ struct StagedCta {
   FT_DEV void run_nvls_private() {
     const int G = a.ctas, nt = a.lay.ntiles;
     constexpr int CU = (VE == 1) ? 1 : 8;
-    constexpr int RU = (VE == 1) ? 1 : 8;
     const int Gr = a.nvls_reducers > 0 && a.nvls_reducers < G ? a.nvls_reducers : 0;
     const int Gc = G - Gr;
     if (Gr == 0) {
@@ -559,7 +646,7 @@ struct StagedCta {
           signal_all_tile(PH_IN, t + G);
         }
         wait_all_tile(PH_IN, t);
-        nvls_reduce_tile<RU>(t);
+        nvls_tile(t);
         be.sync();
         signal_all_tile(PH_RS0, t);
         if (j > 0) {
@@ -595,7 +682,7 @@ struct StagedCta {
       const int q = cta - Gc;
       for (int t = q; t < nt; t += Gr) {
         wait_all_tile(PH_IN, t);
-        nvls_reduce_tile<RU>(t);
+        nvls_tile(t);
         be.sync();
         signal_all_tile(PH_RS0, t);
       }
@@ -608,7 +695,6 @@ struct StagedCta {
     const int G = a.ctas, nt = a.lay.ntiles;
     const int mine = cta < nt ? (nt - cta + G - 1) / G : 0;
     constexpr int CU = (VE == 1) ? 1 : 8;
-    constexpr int RU = (VE == 1) ? 1 : 8;
     if (a.mode == MODE_STAGING) {
       run_nvls_private();
       return;
@@ -617,7 +703,7 @@ struct StagedCta {
     signal_group(PH_IN, 0, E + mine);
     for (int j = 0; j < mine; ++j) {
       wait_group(PH_IN, 0, E + j + 1);
-      nvls_reduce_tile<RU>(cta + j * G);
+      nvls_tile(cta + j * G);
       be.sync();
       signal_group(PH_RS0, 0, E + j + 1);
     }
@@ -626,9 +712,16 @@ struct StagedCta {
       wait_group(PH_RS0, 0, E + j + 1);
       if (need_out) out_tile<CU>(cta + j * G);
     }
-    be.sync();
-    signal_group(PH_END, 0, E + 1);
-    wait_group(PH_END, 0, E + 1);
+    // No exit barrier: a peer reads my buffer only while it reduces its own block, and it signals PH_RS0 for a tile
+    // after that tile's reads (and broadcast stores) are done. Once every CTA of mine has passed its PH_RS0 waits -
+    // which is when this kernel can end - every peer has finished with my buffer. (The pairwise redundancy of the
+    // registered-NVLS waits was found by the wait-removal campaign on the CPU back end; NVLS_KEEP_END restores
+    // the barrier for A/B timing.)
+    if (a.nvls_flags & NVLS_KEEP_END) {
+      be.sync();
+      signal_group(PH_END, 0, E + 1);
+      wait_group(PH_END, 0, E + 1);
+    }
     be.finish(cd, a.ctas);
   }
 

@@ -178,7 +178,7 @@ struct CpuBE {
     }
   }
   // "switch" emulation: sum the N windows in rank order / write to all N windows
-  template <typename T, class Op, int VE>
+  template <typename T, class Op, int VE, bool EMU = false>
   Pack<T, VE> mc_ld_reduce(const RankCall& rc, long long off, int nranks) {
     using EL = Elem<T>;
     typename EL::acc acc[VE];
@@ -191,7 +191,7 @@ struct CpuBE {
     for (int i = 0; i < VE; ++i) o.e[i] = EL::down(acc[i]);
     return o;
   }
-  template <typename T, int VE>
+  template <typename T, int VE, bool EMU = false>
   void mc_st(const RankCall& rc, long long off, const Pack<T, VE>& v, int nranks) {
     for (int p = 0; p < nranks; ++p) memcpy(rc.win[p] + off, &v, sizeof(v));
   }

@@ -15,6 +15,7 @@
 #include "../core/comm_dev.h"
 #include "../core/types.h"
 #include "tma_tiles.cuh"
+#include "nvls_ws.cuh"
 
 namespace ft {
 
@@ -28,6 +29,8 @@ struct CudaBE {
   __device__ __forceinline__ void rs_tile_tma(Cta& c, int k, int t) { rs_tile_tma_impl<T, IO, Op, VE>(c, ring_, k, t); }
   template <typename T, typename IO, class Op, int VE, class Cta>
   __device__ __forceinline__ void ag_tile_tma(Cta& c, int k, int t) { ag_tile_tma_impl<T, IO, Op, VE>(c, ring_, k, t); }
+  template <typename T, typename IO, class Op, int VE, bool EMU, class Cta>
+  __device__ __forceinline__ void nvls_tile_ws(Cta& c, int t) { nvls_tile_ws_impl<T, IO, Op, VE, EMU>(c, ring_.ring, t); }
   __device__ __forceinline__ int tid() const { return (int)threadIdx.x; }
   __device__ __forceinline__ int nthr() const { return (int)blockDim.x; }
   __device__ __forceinline__ void sync() { __syncthreads(); }
@@ -154,9 +157,28 @@ struct CudaBE {
   }
 
   // ---- NVLS ---------------------------------------------------------------------------------------
+  // No multicast mapping (single-GPU emulation, where every "peer" is a slice of this GPU): the switch is played by
+  // a loop over the N windows - sum in rank order, store to all - so that the NVLS control flow (flags, tiles,
+  // inner-loop variants, graph replay) is testable on one GPU. Never taken on the multi-GPU path (rc.mc is set).
   template <typename T, class Op, int VE>
-  __device__ __forceinline__ Pack<T, VE> mc_ld_reduce(const RankCall& rc, long long off, int /*nranks*/) {
+  __device__ __forceinline__ Pack<T, VE> mc_ld_reduce_emulated(const RankCall& rc, long long off, int nranks) {
+    using EL = Elem<T>;
+    typename EL::acc acc[VE];
+    for (int p = 0; p < nranks; ++p) {
+      Pack<T, VE> v;
+      ld<(int)sizeof(Pack<T, VE>)>(&v, rc.win[p] + off, true);
+#pragma unroll
+      for (int i = 0; i < VE; ++i) acc[i] = p ? Op::apply(acc[i], EL::up(v.e[i])) : EL::up(v.e[i]);
+    }
     Pack<T, VE> o;
+#pragma unroll
+    for (int i = 0; i < VE; ++i) o.e[i] = EL::down(acc[i]);
+    return o;
+  }
+  template <typename T, class Op, int VE, bool EMU = false>
+  __device__ __forceinline__ Pack<T, VE> mc_ld_reduce(const RankCall& rc, long long off, int nranks) {
+    Pack<T, VE> o;
+    if constexpr (EMU) return mc_ld_reduce_emulated<T, Op, VE>(rc, off, nranks);
     const char* p = rc.mc + off;
     if constexpr (sizeof(Pack<T, VE>) == 16 && SameT<T, float>::v && SameT<Op, OpSum>::v) {
       uint4 v;
@@ -178,8 +200,12 @@ struct CudaBE {
     }
     return o;
   }
-  template <typename T, int VE>
-  __device__ __forceinline__ void mc_st(const RankCall& rc, long long off, const Pack<T, VE>& v, int /*nranks*/) {
+  template <typename T, int VE, bool EMU = false>
+  __device__ __forceinline__ void mc_st(const RankCall& rc, long long off, const Pack<T, VE>& v, int nranks) {
+    if constexpr (EMU) {  // emulation, see above
+      for (int p = 0; p < nranks; ++p) st<(int)sizeof(Pack<T, VE>)>(rc.win[p] + off, &v);
+      return;
+    }
     if constexpr (sizeof(Pack<T, VE>) == 16) {
       const uint4 u = *reinterpret_cast<const uint4*>(&v);
       asm volatile("multimem.st.relaxed.sys.global.v4.f32 [%0], {%1,%2,%3,%4};" ::"l"(rc.mc + off), "r"(u.x),

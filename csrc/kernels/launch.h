@@ -5,6 +5,10 @@
 #include "../core/comm_dev.h"
 
 #define FT_MAX_THREADS 512
+// The NVLS kernel runs 256-thread CTAs: at 512 threads the register cap is 128 and the 8-deep multimem pipeline
+// spilled (round 1: 109-179 LDL/STL); 256 threads may use 255 registers, and the switch path does not care whether the
+// same number of threads sits in 8 or in 16 CTAs (profiles/tune_n8.md: 594 us either way at 256 MiB on 8 GPUs).
+#define FT_NVLS_THREADS 256
 
 namespace ft {
 
@@ -20,6 +24,8 @@ struct LaunchCtx {
 
 // Returns false when (dtype, io_dtype, op) is not defined at all.
 bool cuda_launch(int dtype, int io_dtype, int op, bool vec, LaunchCtx* ctx);
+// NVLS in place on registered buffers of the wire type (kernels/nvls_kernel.cu); false = not applicable
+bool cuda_launch_nvls_registered(int dtype, int op, LaunchCtx* ctx);
 // true when the switch can reduce this (dtype, op) (multimem.ld_reduce): fp32/bf16/fp16 SUM
 bool nvls_supported(int dtype, int op);
 

@@ -123,6 +123,9 @@ struct ft_comm {
   unsigned* d_err = nullptr;       // [nlocal]
   uint64_t* d_trace = nullptr;     // [nlocal][FT_TRACE_SLOTS], allocated by ft_comm_trace_enable
   unsigned* h_err = nullptr;       // [nlocal] mapped pinned host mirror of d_err (written by the kernel that sets d_err)
+  long long nvls_max_tile = 0;  // registered NVLS: tile cap (0: env FT_NVLS_MAX_TILE_BYTES / 4 MiB)
+  int nvls_ctas = 0;            // registered NVLS: CTAs for large messages (0: 8)
+  int nvls_variant = -1, nvls_flags = 0;  // ft_comm_set_tuning; -1: env FT_NVLS_VARIANT / default
   int fault_rank = -1;             // ft_comm_inject_fault: this rank plays dead in the next calls (-1 = off)
 
   // policy
@@ -325,6 +328,7 @@ Shape pick_shape(const ft_comm* c, int algo, int mode, bool tma, size_t msg_byte
   Shape s;
   s.threads = c->threads_override ? c->threads_override : env_int("FT_THREADS", 512);
   if (s.threads > FT_MAX_THREADS) s.threads = FT_MAX_THREADS;
+  if (algo == ALGO_NVLS && mode == MODE_REGISTERED && s.threads > FT_NVLS_THREADS) s.threads = FT_NVLS_THREADS;  // launch bound of kernels/nvls_kernel.cu
   if (s.threads < 32) s.threads = 32;
   int max_ctas = c->sm_count;  // one resident CTA per SM at 512 threads x <=128 registers
   const int cap = c->max_ctas > 0 ? c->max_ctas : env_int("FT_MAX_CTAS", 0);
@@ -357,11 +361,12 @@ Shape pick_shape(const ft_comm* c, int algo, int mode, bool tma, size_t msg_byte
     // 256 MiB on 8 GPUs) and every tile boundary costs two system fences with multicast stores in
     // flight: few CTAs, one big tile each (profiles/tune_n8.md).
     if (mode == MODE_REGISTERED) {
-      long long want = block_bytes / (64 << 10);
-      ctas = (int)(want < 2 ? 2 : (want > 8 ? 8 : want));
+      long long want = block_bytes / (32 << 10);
+      const int top = c->nvls_ctas > 0 ? c->nvls_ctas : env_int("FT_NVLS_CTAS", 16);  // x 256 threads
+      ctas = (int)(want < 2 ? 2 : (want > top ? top : want));
       if (ctas > max_ctas) ctas = max_ctas;
       tile = (block_bytes + ctas - 1) / ctas;
-      const long long kNvlsMaxTile = env_ll("FT_NVLS_MAX_TILE_BYTES", 4 << 20);
+      const long long kNvlsMaxTile = c->nvls_max_tile > 0 ? c->nvls_max_tile : env_ll("FT_NVLS_MAX_TILE_BYTES", 4 << 20);
       if (tile > kNvlsMaxTile) tile = kNvlsMaxTile;
       if (tile < 4096) tile = 4096;
     } else {
@@ -414,6 +419,15 @@ Shape pick_shape(const ft_comm* c, int algo, int mode, bool tma, size_t msg_byte
   if (tile < esize) tile = esize;
   s.tile_bytes = tile;
   return s;
+}
+
+// NVLS in place on registered buffers of the wire type has a kernel of its own (kernels/nvls_kernel.cu).
+bool launch_any(int wire_dtype, int io_dtype, int op, bool vec, int mode, LaunchCtx* ctx) {
+  if (ctx->algo == ALGO_NVLS && mode == MODE_REGISTERED && wire_dtype == io_dtype && vec) {
+    ctx->err = cudaSuccess;
+    if (cuda_launch_nvls_registered(wire_dtype, op, ctx)) return true;
+  }
+  return cuda_launch(wire_dtype, io_dtype, op, vec, ctx);
 }
 
 // A device watchdog that fired during an EARLIER call left its error word in the mapped host mirror: refuse to
@@ -548,7 +562,7 @@ ft_result_t do_allreduce(ft_comm* c, const void* const* send, void* const* recv,
     ctx.threads = e.threads;
     ctx.cooperative = c->kind == COMM_EMULATED && N > 1;
     ctx.stream = stream;
-    if (!cuda_launch(wire_dtype, io_dtype, op, vec, &ctx) || !ctx.supported || ctx.err != cudaSuccess) {
+    if (!launch_any(wire_dtype, io_dtype, op, vec, e.mode, &ctx) || !ctx.supported || ctx.err != cudaSuccess) {
       set_last_error(std::string("kernel launch: ") + cudaGetErrorString(ctx.err));
       (void)cudaGetLastError();
       return FT_ERR_CUDA;
@@ -710,10 +724,12 @@ ft_result_t do_allreduce(ft_comm* c, const void* const* send, void* const* recv,
   }
   if (algo == ALGO_NVLS) {
     const char* mc = mode == MODE_REGISTERED ? c->user[(size_t)useg].seg[0].mc_base : c->win[0].mc_base;
-    if (!mc) {
+    if (!mc && c->kind == COMM_EMULATED && c->algo_override == ALGO_NVLS) {
+      // one GPU has no switch: the kernel plays it with a loop over the N windows (backend.cuh), which keeps the
+      // NVLS control flow - flags, tiles, inner-loop variants, graph replay - testable on a single device
+    } else if (!mc) {
       if (c->algo_override == ALGO_NVLS) {
-        set_last_error(c->kind == COMM_EMULATED ? "NVLS cannot be emulated on one GPU"
-                                                : "NVLS requested but this communicator has no multicast mapping");
+        set_last_error("NVLS requested but this communicator has no multicast mapping");
         return FT_ERR_UNSUPPORTED;
       }
       algo = ALGO_STAGED;  // multicast bind failed when the window was created: use the P2P stages
@@ -746,6 +762,8 @@ ft_result_t do_allreduce(ft_comm* c, const void* const* send, void* const* recv,
   }
 
   a.use_tma = tma ? 1 : 0;
+  a.nvls_variant = c->nvls_variant >= 0 ? c->nvls_variant : env_int("FT_NVLS_VARIANT", 0);
+  a.nvls_flags = c->nvls_flags | env_int("FT_NVLS_FLAGS", 0);
   a.fault_rank_plus1 = c->fault_rank + 1;
 
   LaunchCtx ctx;
@@ -754,7 +772,7 @@ ft_result_t do_allreduce(ft_comm* c, const void* const* send, void* const* recv,
   ctx.threads = sh.threads;
   ctx.cooperative = c->kind == COMM_EMULATED && N > 1;
   ctx.stream = stream;
-  if (!cuda_launch(wire_dtype, io_dtype, op, vec, &ctx) || !ctx.supported) {
+  if (!launch_any(wire_dtype, io_dtype, op, vec, mode, &ctx) || !ctx.supported) {
     set_last_error(std::string("no kernel for ") + op_name(op) + "/" + dtype_name(wire_dtype) + "/" + algo_name(algo));
     return FT_ERR_UNSUPPORTED;
   }
@@ -990,6 +1008,17 @@ ft_result_t ft_comm_clear_error(ft_comm_t* c) {
   FT_CHECK_RT(cudaMemset(c->d_err, 0, sizeof(unsigned) * (size_t)c->nlocal));
   if (c->h_err) memset(c->h_err, 0, sizeof(unsigned) * (size_t)c->nlocal);
   return FT_SUCCESS;
+}
+ft_result_t ft_comm_set_tuning(ft_comm_t* c, const char* key, long long value) {
+  if (!c || !key) return FT_ERR_INVALID;
+  c->policy_gen++;
+  const std::string k = key;
+  if (k == "nvls_variant") { c->nvls_variant = (int)value; return FT_SUCCESS; }
+  if (k == "nvls_flags") { c->nvls_flags = (int)value; return FT_SUCCESS; }
+  if (k == "nvls_max_tile_bytes") { c->nvls_max_tile = value; return FT_SUCCESS; }
+  if (k == "nvls_ctas") { c->nvls_ctas = (int)value; return FT_SUCCESS; }
+  set_last_error("ft_comm_set_tuning: unknown key " + k);
+  return FT_ERR_INVALID;
 }
 ft_result_t ft_comm_inject_fault(ft_comm_t* c, int rank) {
   if (!c || rank >= c->nranks) return FT_ERR_INVALID;

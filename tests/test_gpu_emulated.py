@@ -535,3 +535,76 @@ def test_allreduce_host_pipelined(comms):
         c.allreduce_host(xs, scale=0.25, chunk_bytes=chunk)          # in place, fused scale
         assert torch.allclose(xs[2].double(), want * 0.25, rtol=1e-5, atol=1e-5)
     assert c.error() == 0
+
+
+@pytest.mark.parametrize("variant", [0, 1, 2, 3, 4, 5])
+@pytest.mark.parametrize("dtype", [torch.float32, torch.bfloat16])
+def test_nvls_protocol_emulated_every_variant(comms, variant, dtype):
+    """The NVLS kernels (flags, tiles, every inner-loop variant incl. the warp-specialised one) with the switch played
+    by a loop over the N windows: registered buffers -> dedicated kernel (kernels/nvls_kernel.cu), private buffers ->
+    the role-split general path. Several tiles per CTA, ragged sizes, back-to-back calls."""
+    n = 4
+    c = comms(n)
+    c.set_algo("nvls")
+    c.set_tuning("nvls_variant", variant)
+    tol = dict(rtol=1e-5, atol=1e-5) if dtype == torch.float32 else dict(rtol=2e-2, atol=2e-2)
+    g = torch.Generator(device="cuda").manual_seed(11 + variant)
+    try:
+        for count, ctas, tile in ((1 << 18, 2, 16 << 10), (300000, 3, 8 << 10), (4096, 0, 0), (1 << 20, 4, 0)):
+            count -= count % 8
+            c.set_launch(ctas, 0, tile)
+            sym = c.symm_empty(count, dtype)
+            xs = [torch.randn(count, device="cuda", generator=g).to(dtype) for _ in range(n)]
+            want = torch.stack([x.double() for x in xs]).sum(0)
+            for rep in range(3):
+                for s_, x in zip(sym, xs):
+                    s_.copy_(x)
+                c.allreduce_multi(sym)
+                torch.cuda.synchronize()
+                assert c.error() == 0, hex(c.error())
+                info = c.last_call()
+                assert info["algo"] == "nvls" and info["mode"] == "registered", info
+                for r in range(n):
+                    assert torch.allclose(sym[r].double(), want, **tol), (variant, count, rep, r)
+                    assert torch.equal(sym[r], sym[0])
+            priv = [x.clone() for x in xs]       # private buffers: copy-in / reduce / copy-out roles
+            outs = [torch.empty_like(x) for x in xs]
+            c.allreduce_multi(priv, outs=outs, scale=0.5)
+            torch.cuda.synchronize()
+            assert c.error() == 0 and c.last_call()["mode"] == "staging"
+            for r in range(n):
+                assert torch.allclose(outs[r].double(), want * 0.5, **tol)
+                assert torch.equal(priv[r], xs[r])
+    finally:
+        c.set_launch(0, 0, 0)
+        c.set_tuning("nvls_variant", -1)
+        c.set_algo("auto")
+
+
+def test_nvls_registered_graph_replay_emulated(comms):
+    n, count = 4, 1 << 16
+    c = comms(n)
+    c.set_algo("nvls")
+    c.set_launch(2, 0, 8 << 10)
+    ts = c.symm_empty(count, torch.float32)
+    for t in ts:
+        t.fill_(1.0)
+    c.allreduce_multi(ts)
+    torch.cuda.synchronize()
+    g = torch.cuda.CUDAGraph()
+    s = torch.cuda.Stream()
+    with torch.cuda.stream(s):
+        g.capture_begin()
+        c.allreduce_multi(ts, stream=s)
+        g.capture_end()
+    for it in range(20):
+        for r in range(n):
+            ts[r].fill_(float(r + 1 + it))
+        g.replay()
+        torch.cuda.synchronize()
+        want = float(sum(r + 1 + it for r in range(n)))
+        for r in range(n):
+            assert torch.all(ts[r] == want), (it, r)
+    assert c.error() == 0
+    c.set_launch(0, 0, 0)
+    c.set_algo("auto")
