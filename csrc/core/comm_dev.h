@@ -89,8 +89,7 @@ struct StagedArgs {
   int phases;   // 0 = allreduce, 1 = reduce-scatter only (recv gets my block), 2 = all-gather only (send is my block)
   int nvls_reducers;  // NVLS with private buffers: CTAs per rank that only run the in-switch reduce (rest copy)
   int nvls_variant;   // inner loop of the in-switch reduce, see StagedCta::nvls_tile (tuning; 0 = default)
-  int nvls_flags;     // bit0/bit1: measurement only - leave out the multimem.st / the multimem.ld_reduce (wrong results);
-                      // bit2: keep the exit barrier of the registered path
+  int nvls_flags;     // 4: keep the exit barrier of the registered path (A/B timing)
   int fault_rank_plus1;  // fault injection (tests): rank + 1 of a rank that plays dead in this call, 0 = none
   RankCall rc[FT_MAX_LOCAL];
 };

@@ -458,16 +458,7 @@ struct StagedCta {
       for (int u = 0; u < UNR; ++u) {
         const long long q = q0 + (long long)u * nth + tid;
         if (q >= nvec) continue;
-        if constexpr (EL::is_float) {
-          if (a.apply_scale) {  // the switch returned the final sum: scale it once, before the broadcast
-            A acc[VE];
-#pragma unroll
-            for (int i = 0; i < VE; ++i) acc[i] = EL::up(cur[u].e[i]);
-            scale_acc(acc);
-#pragma unroll
-            for (int i = 0; i < VE; ++i) cur[u].e[i] = EL::down(acc[i]);
-          }
-        }
+        scale_pack(cur[u]);
         be.template mc_st<T, VE, EMU>(rc, base + q * (long long)sizeof(PackT), cur[u], a.plan.nranks);
       }
       if (more) {
@@ -477,11 +468,9 @@ struct StagedCta {
     }
   }
 
-  // Same work without the software pipeline: UNR loads, then UNR stores. Half the payload registers of the
-  // pipelined form (no second buffer), so larger UNR fits without spilling. Also hosts the two measurement modes
-  // that take the switch path apart: NVLS_NO_ST keeps only the in-switch reduce (result lands in my window only),
-  // NVLS_NO_LD keeps only the multicast store (of my own unreduced block) - both give wrong sums by design.
-  enum { NVLS_NO_ST = 1, NVLS_NO_LD = 2, NVLS_KEEP_END = 4 };
+  // Same work without the software pipeline: UNR loads, then UNR stores (general path: private buffers, casts,
+  // single-GPU emulation).
+  enum { NVLS_KEEP_END = 4 };
   template <int UNR, bool EMU> FT_DEV void nvls_reduce_tile_simple(int t) {
     long long start;
     const long long n = tile_valid(r, t, &start);
@@ -490,44 +479,114 @@ struct StagedCta {
     const int nth = be.nthr(), tid = be.tid();
     const long long step = (long long)nth * UNR;
     const long long base = woff + start * (long long)sizeof(T);
-    char* wr = rc.win[r];
-    const bool no_st = (a.nvls_flags & NVLS_NO_ST) != 0, no_ld = (a.nvls_flags & NVLS_NO_LD) != 0;
     for (long long q0 = 0; q0 < nvec; q0 += step) {
       PackT v[UNR];
 #pragma unroll
       for (int u = 0; u < UNR; ++u) {
         const long long q = q0 + (long long)u * nth + tid;
-        if (q < nvec) {
-          const long long off = base + q * (long long)sizeof(PackT);
-          v[u] = no_ld ? ld_win(wr, off, false) : be.template mc_ld_reduce<T, Op, VE, EMU>(rc, off, a.plan.nranks);
-        }
+        if (q < nvec) v[u] = be.template mc_ld_reduce<T, Op, VE, EMU>(rc, base + q * (long long)sizeof(PackT), a.plan.nranks);
       }
 #pragma unroll
       for (int u = 0; u < UNR; ++u) {
         const long long q = q0 + (long long)u * nth + tid;
         if (q >= nvec) continue;
-        if constexpr (EL::is_float) {
-          if (a.apply_scale) {
-            A acc[VE];
-#pragma unroll
-            for (int i = 0; i < VE; ++i) acc[i] = EL::up(v[u].e[i]);
-            scale_acc(acc);
-#pragma unroll
-            for (int i = 0; i < VE; ++i) v[u].e[i] = EL::down(acc[i]);
-          }
-        }
-        const long long off = base + q * (long long)sizeof(PackT);
-        if (no_st) st_win(wr, off, v[u]);
-        else be.template mc_st<T, VE, EMU>(rc, off, v[u], a.plan.nranks);
+        scale_pack(v[u]);
+        be.template mc_st<T, VE, EMU>(rc, base + q * (long long)sizeof(PackT), v[u], a.plan.nranks);
       }
     }
   }
+  FT_DEV void scale_pack(PackT& v) const {
+    if constexpr (EL::is_float) {
+      if (a.apply_scale) {  // the switch returned the final sum: scale it once, before the broadcast
+        A acc[VE];
+#pragma unroll
+        for (int i = 0; i < VE; ++i) acc[i] = EL::up(v.e[i]);
+        scale_acc(acc);
+#pragma unroll
+        for (int i = 0; i < VE; ++i) v.e[i] = EL::down(acc[i]);
+      }
+    }
+  }
+
+  // Streaming form for the dedicated kernel (fixed NTH threads per CTA). What it fixes, measured on 2 GPUs with the
+  // loops above at 256 MiB: 4.8 ms for "UNR loads, then UNR stores" whatever UNR was (4, 8, 16), i.e. ~2.3 us per
+  // multimem.ld_reduce per thread - one full switch round trip each, the loads of a thread did not overlap at all.
+  // The SASS showed why: every LDGMC of a thread took its address from the SAME register pair, recomputed between
+  // the loads, and a multimem load holds its address registers until it has been sent off, so the next address
+  // computation (a write-after-read on that pair) waited for the previous load. Here a batch is addressed as ONE base
+  // pointer per thread plus compile-time offsets (u * NTH * 16 bytes): the base is not written while the batch is
+  // in flight, the full batches carry no bounds checks, and only the ragged end of a tile goes through the checked
+  // loop. MODE: 0 = reduce + broadcast; 1 = measurement, reduce only (result stays local); 2 = measurement,
+  // broadcast only (of the unreduced local block). DEPTH 2 = software pipeline (next batch's loads before this
+  // batch's stores).
+  template <int UNR, int DEPTH, int MODE, int NTH, bool EMU> FT_DEV void nvls_tile_stream(int t) {
+    long long start;
+    const long long n = tile_valid(r, t, &start);
+    if (n <= 0) return;
+    const long long nvec = (n + VE - 1) / VE;
+    const int tid = be.tid();
+    constexpr long long kBatch = (long long)NTH * UNR;               // vectors per batch per CTA
+    constexpr long long kStride = (long long)NTH * (long long)sizeof(PackT);  // bytes between a thread's vectors
+    const long long full = nvec / kBatch;
+    const int nr = a.plan.nranks;
+    char* wr = rc.win[r];
+    long long off = woff + start * (long long)sizeof(T) + (long long)tid * (long long)sizeof(PackT);
+    auto ld = [&](PackT* v, long long o) {
+#pragma unroll
+      for (int u = 0; u < UNR; ++u) {
+        if constexpr (MODE == 2) v[u] = ld_win(wr, o + u * kStride, false);
+        else v[u] = be.template mc_ld_reduce<T, Op, VE, EMU>(rc, o + u * kStride, nr);
+      }
+    };
+    auto st = [&](PackT* v, long long o) {
+#pragma unroll
+      for (int u = 0; u < UNR; ++u) {
+        scale_pack(v[u]);
+        if constexpr (MODE == 1) st_win(wr, o + u * kStride, v[u]);
+        else be.template mc_st<T, VE, EMU>(rc, o + u * kStride, v[u], nr);
+      }
+    };
+    if constexpr (DEPTH == 2) {
+      PackT cur[UNR], nxt[UNR];
+      if (full > 0) ld(cur, off);
+      for (long long b = 0; b < full; ++b) {
+        const long long o = off + b * kBatch * (long long)sizeof(PackT);
+        if (b + 1 < full) ld(nxt, o + kBatch * (long long)sizeof(PackT));
+        st(cur, o);
+        if (b + 1 < full) {
+#pragma unroll
+          for (int u = 0; u < UNR; ++u) cur[u] = nxt[u];
+        }
+      }
+    } else {
+      for (long long b = 0; b < full; ++b) {
+        const long long o = off + b * kBatch * (long long)sizeof(PackT);
+        PackT v[UNR];
+        ld(v, o);
+        st(v, o);
+      }
+    }
+    // ragged end of the tile: fewer than kBatch vectors
+    for (long long q = full * kBatch + tid; q < nvec; q += NTH) {
+      const long long o = woff + start * (long long)sizeof(T) + q * (long long)sizeof(PackT);
+      PackT v;
+      if constexpr (MODE == 2) v = ld_win(wr, o, false);
+      else v = be.template mc_ld_reduce<T, Op, VE, EMU>(rc, o, nr);
+      scale_pack(v);
+      if constexpr (MODE == 1) st_win(wr, o, v);
+      else be.template mc_st<T, VE, EMU>(rc, o, v, nr);
+    }
+  }
+
   // The in-switch reduce of one tile. Inner-loop variants (ft_comm_set_tuning "nvls_variant"; each one is its own
-  // kernel in kernels/nvls_kernel.cu so that it gets its own register allocation):
-  //   0  pipelined, 8 vectors per thread (two register buffers)      1  pipelined, 4 vectors
-  //   2  plain, 8 vectors     3  plain, 4 vectors     4  plain, 16 vectors
+  // kernel in kernels/nvls_kernel.cu, with its own register allocation):
+  //   0  streaming, 8 vectors per batch            1  streaming, 16 vectors per batch
+  //   2  streaming, 8 vectors, software-pipelined  3  streaming, 4 vectors, software-pipelined
+  //   4  round-1 loop (pipelined, 8 vectors, per-vector addresses and bounds checks) - kept for A/B
   //   5  warp-specialised: half the warps run multimem.ld_reduce into a shared-memory ring, the other half drain it
-  //      with multimem.st (CUDA only; kernels/nvls_ws.cuh)
+  //      with multimem.st (kernels/nvls_ws.cuh)
+  //   6  plain loop (8 loads then 8 stores, per-vector addresses) - the form that serialises, kept as evidence
+  //   7  MEASUREMENT: in-switch reduce only    8  MEASUREMENT: multicast store only   (wrong sums by design)
   FT_DEV void nvls_tile(int t) {
     // EMU: no multicast mapping (single-GPU emulation) - the back end plays the switch with a loop over the N
     // windows. A template flag, not a branch inside the loops: the multi-GPU code carries no trace of it.
@@ -536,23 +595,27 @@ struct StagedCta {
     else nvls_reduce_tile_simple<U, true>(t);
   }
   // One variant, chosen at compile time (the dedicated registered-buffer kernel, kernels/nvls_kernel.cu).
-  template <int VARIANT, bool EMU> FT_DEV void nvls_tile_variant(int t) {
-    if constexpr (VARIANT == 1) nvls_reduce_tile<4, EMU>(t);
-    else if constexpr (VARIANT == 2) nvls_reduce_tile_simple<8, EMU>(t);
-    else if constexpr (VARIANT == 3) nvls_reduce_tile_simple<4, EMU>(t);
-    else if constexpr (VARIANT == 4) nvls_reduce_tile_simple<16, EMU>(t);
+  template <int VARIANT, int NTH, bool EMU> FT_DEV void nvls_tile_variant(int t) {
+    if constexpr (VE == 1) nvls_reduce_tile_simple<1, EMU>(t);
+    else if constexpr (VARIANT == 1) nvls_tile_stream<16, 1, 0, NTH, EMU>(t);
+    else if constexpr (VARIANT == 2) nvls_tile_stream<8, 2, 0, NTH, EMU>(t);
+    else if constexpr (VARIANT == 3) nvls_tile_stream<4, 2, 0, NTH, EMU>(t);
+    else if constexpr (VARIANT == 4) nvls_reduce_tile<8, EMU>(t);
     else if constexpr (VARIANT == 5 && BE::kTma) be.template nvls_tile_ws<T, IO, Op, VE, EMU>(*this, t);
-    else nvls_reduce_tile<8, EMU>(t);
+    else if constexpr (VARIANT == 6) nvls_reduce_tile_simple<8, EMU>(t);
+    else if constexpr (VARIANT == 7) nvls_tile_stream<8, 1, 1, NTH, EMU>(t);
+    else if constexpr (VARIANT == 8) nvls_tile_stream<8, 1, 2, NTH, EMU>(t);
+    else nvls_tile_stream<8, 1, 0, NTH, EMU>(t);
   }
   // NVLS on registered (zero-copy) buffers of the wire type: the whole call for this CTA. Same protocol as the
   // registered branch of run_nvls, without the code of the private-buffer roles around it.
-  template <int VARIANT, bool EMU> FT_DEV void run_nvls_registered() {
+  template <int VARIANT, int NTH, bool EMU> FT_DEV void run_nvls_registered() {
     const int G = a.ctas, nt = a.lay.ntiles;
     const int mine = cta < nt ? (nt - cta + G - 1) / G : 0;
     signal_group(PH_IN, 0, E + mine);
     for (int j = 0; j < mine; ++j) {
       wait_group(PH_IN, 0, E + j + 1);
-      nvls_tile_variant<VARIANT, EMU>(cta + j * G);
+      nvls_tile_variant<VARIANT, NTH, EMU>(cta + j * G);
       be.sync();
       signal_group(PH_RS0, 0, E + j + 1);
     }

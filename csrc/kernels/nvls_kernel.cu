@@ -36,7 +36,7 @@ __global__ void __launch_bounds__(FT_NVLS_THREADS, 1) ft_nvls_kernel(const __gri
     return;
   }
   StagedCta<CudaBE, T, T, Op, VecElems<T>::value> k(be, a, a.rc[lr], cta);
-  k.template run_nvls_registered<VARIANT, EMU>();
+  k.template run_nvls_registered<VARIANT, FT_NVLS_THREADS, EMU>();
 }
 
 namespace {
@@ -45,6 +45,16 @@ cudaError_t go(const LaunchCtx* c) {
   auto kern = ft_nvls_kernel<T, Op, VARIANT, EMU>;
   dim3 grid((unsigned)(c->args->nlocal * c->args->ctas)), block((unsigned)c->threads);
   const size_t smem = VARIANT == 5 ? (size_t)kNvlsWsSmemBytes : 0;
+  if (smem > (48u << 10)) {
+    static bool attr_set[64] = {};  // per instantiation, per device
+    int dev = 0;
+    cudaGetDevice(&dev);
+    if (dev >= 0 && dev < 64 && !attr_set[dev]) {
+      cudaError_t e = cudaFuncSetAttribute((const void*)kern, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem);
+      if (e != cudaSuccess) return e;
+      attr_set[dev] = true;
+    }
+  }
   if (c->cooperative) {
     void* params[] = {(void*)c->args};
     return cudaLaunchCooperativeKernel((const void*)kern, grid, block, params, smem, c->stream);
@@ -60,6 +70,9 @@ cudaError_t by_variant(const LaunchCtx* c) {
     case 3: return go<T, Op, 3, EMU>(c);
     case 4: return go<T, Op, 4, EMU>(c);
     case 5: return go<T, Op, 5, EMU>(c);
+    case 6: return go<T, Op, 6, EMU>(c);
+    case 7: return go<T, Op, 7, EMU>(c);
+    case 8: return go<T, Op, 8, EMU>(c);
     default: return go<T, Op, 0, EMU>(c);
   }
 }
@@ -71,7 +84,7 @@ cudaError_t by_emu(const LaunchCtx* c) {
 
 // Registered buffers, user type == wire type, fp32 / bf16 / fp16 SUM, whole 16-byte vectors. false = not my case.
 bool cuda_launch_nvls_registered(int dtype, int op, LaunchCtx* ctx) {
-  if (op != OP_SUM || ctx->threads > FT_NVLS_THREADS) return false;
+  if (op != OP_SUM || ctx->threads != FT_NVLS_THREADS) return false;  // the streaming loops are compiled for that CTA size
   ctx->supported = true;
   switch (dtype) {
     case DT_FLOAT: ctx->err = by_emu<float>(ctx); return true;

@@ -20,9 +20,9 @@
 
 namespace ft {
 
-constexpr int kNvlsWsStages = 4;
-constexpr int kNvlsWsUnroll = 4;
-// ring bytes = stages x (threads / 2) x unroll x 16 B  = 32 KiB at the 256 threads of the NVLS kernel
+constexpr int kNvlsWsStages = 2;
+constexpr int kNvlsWsUnroll = 16;  // a loader has one batch in flight at a time (it must see the data to park it)
+// ring bytes = stages x (threads / 2) x unroll x 16 B  = 64 KiB at the 256 threads of the NVLS kernel
 constexpr int kNvlsWsSmemBytes = kNvlsWsStages * (FT_NVLS_THREADS / 2) * kNvlsWsUnroll * 16;
 
 __device__ __forceinline__ void named_bar_sync(int id, int count) {
@@ -42,23 +42,30 @@ __device__ __forceinline__ void nvls_tile_ws_impl(Cta& c, char* smem, int t) {
   const long long n = c.tile_valid(c.r, t, &start);
   if (n <= 0) return;  // same decision in every thread of the CTA
   const long long nvec = (n + VE - 1) / VE;
-  const int nth = (int)blockDim.x, half = nth >> 1;
+  constexpr int nth = FT_NVLS_THREADS, half = nth >> 1;  // the dedicated kernel always runs FT_NVLS_THREADS threads
   const bool loader = (int)threadIdx.x < half;
   const int ltid = loader ? (int)threadIdx.x : (int)threadIdx.x - half;
-  const long long step = (long long)half * UNR;
+  constexpr long long step = (long long)half * UNR;
+  constexpr long long kStride = (long long)half * 16;  // bytes between a thread's vectors of one batch
   const long long iters = (nvec + step - 1) / step;
-  const long long base = c.woff + start * (long long)sizeof(T);
+  const long long full = nvec / step;                  // batches without a ragged end
+  const long long base = c.woff + start * (long long)sizeof(T) + (long long)ltid * 16;
   const int nranks = c.a.plan.nranks;
   // barrier ids: 0 is __syncthreads; full[s] = 1 + s, empty[s] = 1 + S + s
+  // Addresses: one base per batch plus compile-time offsets, see StagedCta::nvls_tile_stream for why.
   if (loader) {
     for (long long it = 0; it < iters; ++it) {
       const int s = (int)(it % S);
       if (it >= S) named_bar_sync(1 + S + s, nth);  // the storers have drained this stage
       PackT v[UNR];
+      const long long o = base + it * step * 16;
+      if (it < full) {
 #pragma unroll
-      for (int u = 0; u < UNR; ++u) {
-        const long long q = it * step + (long long)u * half + ltid;
-        if (q < nvec) v[u] = c.be.template mc_ld_reduce<T, Op, VE, EMU>(c.rc, base + q * (long long)sizeof(PackT), nranks);
+        for (int u = 0; u < UNR; ++u) v[u] = c.be.template mc_ld_reduce<T, Op, VE, EMU>(c.rc, o + u * kStride, nranks);
+      } else {
+#pragma unroll
+        for (int u = 0; u < UNR; ++u)
+          if (it * step + (long long)u * half + ltid < nvec) v[u] = c.be.template mc_ld_reduce<T, Op, VE, EMU>(c.rc, o + u * kStride, nranks);
       }
       char* slot = smem + (size_t)s * (size_t)half * UNR * 16;
 #pragma unroll
@@ -74,21 +81,12 @@ __device__ __forceinline__ void nvls_tile_ws_impl(Cta& c, char* smem, int t) {
 #pragma unroll
       for (int u = 0; u < UNR; ++u) v[u] = *reinterpret_cast<const PackT*>(slot + ((size_t)u * half + ltid) * 16);
       if (it + S < iters) named_bar_arrive(1 + S + s, nth);  // only if a later iteration waits for it
+      const long long o = base + it * step * 16;
 #pragma unroll
       for (int u = 0; u < UNR; ++u) {
-        const long long q = it * step + (long long)u * half + ltid;
-        if (q >= nvec) continue;
-        if constexpr (EL::is_float) {
-          if (c.a.apply_scale) {
-            A acc[VE];
-#pragma unroll
-            for (int i = 0; i < VE; ++i) acc[i] = EL::up(v[u].e[i]);
-            c.scale_acc(acc);
-#pragma unroll
-            for (int i = 0; i < VE; ++i) v[u].e[i] = EL::down(acc[i]);
-          }
-        }
-        c.be.template mc_st<T, VE, EMU>(c.rc, base + q * (long long)sizeof(PackT), v[u], nranks);
+        if (it >= full && it * step + (long long)u * half + ltid >= nvec) continue;
+        c.scale_pack(v[u]);
+        c.be.template mc_st<T, VE, EMU>(c.rc, o + u * kStride, v[u], nranks);
       }
     }
   }

@@ -149,8 +149,9 @@ unsigned ft_comm_error(ft_comm_t*);
 unsigned ft_comm_error_peek(const ft_comm_t*);
 ft_result_t ft_comm_clear_error(ft_comm_t*);
 /* Tuning knobs that have no place in the stable API (launch-shape scans, kernel-variant A/B runs). Keys:
- * "nvls_variant" (inner loop of the in-switch reduce, 0-5, see StagedCta::nvls_tile), "nvls_flags" (bit0/1: leave
- * out the multicast store / the in-switch load - measurement only, wrong sums; bit2: keep the exit barrier),
+ * "nvls_variant" (inner loop of the in-switch reduce on registered buffers, 0-6, see StagedCta::nvls_tile_variant;
+ * 7 / 8 are measurement kernels that leave out the multicast store / the in-switch load and give wrong sums),
+ * "nvls_flags" (4: keep the exit barrier),
  * "nvls_ctas", "nvls_max_tile_bytes" (shape of the registered NVLS path). */
 ft_result_t ft_comm_set_tuning(ft_comm_t*, const char* key, long long value);
 /* Fault injection for tests and drills: logical rank `rank` plays dead in every following collective (its kernel

@@ -537,7 +537,7 @@ def test_allreduce_host_pipelined(comms):
     assert c.error() == 0
 
 
-@pytest.mark.parametrize("variant", [0, 1, 2, 3, 4, 5])
+@pytest.mark.parametrize("variant", [0, 1, 2, 3, 4, 5, 6])
 @pytest.mark.parametrize("dtype", [torch.float32, torch.bfloat16])
 def test_nvls_protocol_emulated_every_variant(comms, variant, dtype):
     """The NVLS kernels (flags, tiles, every inner-loop variant incl. the warp-specialised one) with the switch played
