@@ -115,6 +115,7 @@ def _declare(L):
     sig("ft_comm_error_peek", C.c_uint, [vp])
     sig("ft_comm_inject_fault", i32, [vp, i32])
     sig("ft_comm_set_tuning", i32, [vp, cp, i64])
+    sig("ft_link_probe", i32, [vp, i32, i32, C.c_size_t, i32, vp])
     sig("ft_comm_set_widths", i32, [vp, pi32, i32])
     sig("ft_comm_set_algo", i32, [vp, i32])
     sig("ft_comm_set_link_model", i32, [vp, vp])

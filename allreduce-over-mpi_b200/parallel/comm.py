@@ -162,6 +162,12 @@ class Communicator:
         nvls_max_tile_bytes."""
         _check(self._L, self._L.ft_comm_set_tuning(self._h, key.encode(), int(value)), "ft_comm_set_tuning")
 
+    def link_probe(self, mode, npeers, bytes_per_peer, ctas, stream=None):
+        """Raw NVLink traffic (ft_link_probe): mode 'ldg_pull' | 'stg_push' | 'tma_pull' | 'tma_push'."""
+        m = {"ldg_pull": 0, "stg_push": 1, "tma_pull": 2, "tma_push": 3}[mode] if isinstance(mode, str) else int(mode)
+        _check(self._L, self._L.ft_link_probe(self._h, m, int(npeers), int(bytes_per_peer), int(ctas), self._stream(stream)),
+               "ft_link_probe")
+
     def inject_fault(self, rank):
         """Tests/drills: logical rank `rank` plays dead in the following collectives (None = off)."""
         _check(self._L, self._L.ft_comm_inject_fault(self._h, -1 if rank is None else int(rank)), "ft_comm_inject_fault")

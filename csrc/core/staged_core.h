@@ -27,6 +27,8 @@
 #include "comm_dev.h"
 #include "types.h"
 
+#define FT_MAX_THREADS_CORE 512  // == FT_MAX_THREADS (kernels/launch.h): CTA size the streaming NVLS tile of the general kernel is compiled for
+
 namespace ft {
 
 #if defined(__CUDACC__)
@@ -591,8 +593,16 @@ struct StagedCta {
     // EMU: no multicast mapping (single-GPU emulation) - the back end plays the switch with a loop over the N
     // windows. A template flag, not a branch inside the loops: the multi-GPU code carries no trace of it.
     constexpr int U = (VE == 1) ? 1 : 4;
-    if (rc.mc) nvls_reduce_tile_simple<U, false>(t);
-    else nvls_reduce_tile_simple<U, true>(t);
+    if (!rc.mc) {
+      nvls_reduce_tile_simple<U, true>(t);
+    } else {
+      // few reducer CTAs carry the whole switch traffic of a rank: they need deep batches (8 CTAs x 256 threads x 4
+      // vectors in flight ran at 727 us per 256 MiB on 8 GPUs against 575 us with twice the bytes in flight)
+      if constexpr (VE > 1) {
+        if (be.nthr() == FT_MAX_THREADS_CORE) { nvls_tile_stream<8, 1, 0, FT_MAX_THREADS_CORE, false>(t); return; }
+      }
+      nvls_reduce_tile_simple<U, false>(t);
+    }
   }
   // One variant, chosen at compile time (the dedicated registered-buffer kernel, kernels/nvls_kernel.cu).
   template <int VARIANT, int NTH, bool EMU> FT_DEV void nvls_tile_variant(int t) {

@@ -25,6 +25,8 @@
 #include "symm.h"
 
 namespace ft {
+cudaError_t launch_link_probe(char* const* d_table, int rank, int nranks, int npeers, long long bytes_per_peer, int mode,
+                              int ctas, unsigned* sink, cudaStream_t stream);  // kernels/link_probe.cu
 void set_last_error(const std::string& s);  // planner/c_api.cc
 void host_pipe_release(const ft_comm_t* c);  // runtime/host_pipe.cu
 }
@@ -379,7 +381,8 @@ Shape pick_shape(const ft_comm* c, int algo, int mode, bool tma, size_t msg_byte
         if (tile < (16 << 10)) tile = 16 << 10;
         const long long ntiles = (block_bytes + tile - 1) / tile;
         int gr = (int)(ntiles / 4);
-        gr = gr < 1 ? 1 : (gr > 8 ? 8 : gr);
+        const int gr_top = env_int("FT_NVLS_REDUCERS", 16);
+        gr = gr < 1 ? 1 : (gr > gr_top ? gr_top : gr);
         int cap2 = max_ctas < 64 ? max_ctas : 64;
         int gc = (int)(ntiles < (long long)(cap2 - gr) ? ntiles : (long long)(cap2 - gr));
         if (gc < 1) gc = 1;
@@ -1019,6 +1022,25 @@ ft_result_t ft_comm_set_tuning(ft_comm_t* c, const char* key, long long value) {
   if (k == "nvls_ctas") { c->nvls_ctas = (int)value; return FT_SUCCESS; }
   set_last_error("ft_comm_set_tuning: unknown key " + k);
   return FT_ERR_INVALID;
+}
+ft_result_t ft_link_probe(ft_comm_t* c, int mode, int npeers, size_t bytes_per_peer, int ctas, void* stream) {
+  if (!c || c->kind == COMM_EMULATED || mode < 0 || mode > 3 || npeers < 1 || npeers >= c->nranks || ctas < 1 ||
+      bytes_per_peer < 16 || bytes_per_peer % 16) {
+    set_last_error("ft_link_probe: needs a multi-GPU communicator, mode 0-3, 1 <= npeers < nranks, 16-byte multiple");
+    return FT_ERR_INVALID;
+  }
+  const size_t need = bytes_per_peer * (size_t)c->nranks;  // one slot per source rank
+  ft_result_t r = grow_window(c, (need + 1) / 2);            // the window has two parity halves: use both
+  if (r != FT_SUCCESS) return r;
+  FT_CHECK_RT(cudaSetDevice(c->device));
+  cudaError_t e = launch_link_probe(c->win[0].d_table, c->rank, c->nranks, npeers, (long long)bytes_per_peer, mode, ctas,
+                                    c->d_done /* never written in practice */, (cudaStream_t)stream);
+  if (e != cudaSuccess) {
+    set_last_error(std::string("ft_link_probe: ") + cudaGetErrorString(e));
+    (void)cudaGetLastError();
+    return FT_ERR_CUDA;
+  }
+  return FT_SUCCESS;
 }
 ft_result_t ft_comm_inject_fault(ft_comm_t* c, int rank) {
   if (!c || rank >= c->nranks) return FT_ERR_INVALID;

@@ -154,6 +154,12 @@ ft_result_t ft_comm_clear_error(ft_comm_t*);
  * "nvls_flags" (4: keep the exit barrier),
  * "nvls_ctas", "nvls_max_tile_bytes" (shape of the registered NVLS path). */
 ft_result_t ft_comm_set_tuning(ft_comm_t*, const char* key, long long value);
+/* Raw link traffic for the cost-model fit (kernels/link_probe.cu): this rank streams `bytes_per_peer` bytes from
+ * (mode 0: 16-byte loads, 2: TMA bulk loads) or to (1: 16-byte stores, 3: TMA bulk stores) each of its next `npeers`
+ * ranks' staging windows with `ctas` CTAs. No synchronisation between ranks and no meaningful data: time it with
+ * events while the other ranks run the pattern you want to measure (collective only in that the first call may
+ * grow the window). */
+ft_result_t ft_link_probe(ft_comm_t*, int mode, int npeers, size_t bytes_per_peer, int ctas, void* stream);
 /* Fault injection for tests and drills: logical rank `rank` plays dead in every following collective (its kernel
  * exits without touching a buffer or signalling anybody), so its peers run into the watchdog. rank < 0 = off. */
 ft_result_t ft_comm_inject_fault(ft_comm_t*, int rank);
