@@ -211,39 +211,50 @@ struct StagedCta {
     return n <= 0 ? 0 : (int)n;
   }
 
-  // ---- phase IN: private user buffer -> my window (only the blocks some peer will pull) -------------
-  template <int UNR> FT_DEV void copy_in_tile(int t) {
-    const Layout& L = a.lay;
-    const int N = a.plan.nranks, g1 = a.plan.gap[1];
-    const int CV = (int)((L.tile + VE - 1) / VE);
-    const int total = N * CV;
+  // Streaming copy of one contiguous run of a tile: n elements starting at element `start` (16-byte aligned in the
+  // window; the user side may be ragged only in the very last vector of the message). One base address per batch
+  // and no per-vector index arithmetic: the copy passes around the NVLS reduce (private buffers) were ALU-bound on
+  // `q / CV` divisions before (819 us per 256 MiB on 8 GPUs with the reduce itself at 575 us).
+  //   DIR 0: user send -> my window (io_to_wire)      DIR 1: my window -> user recv (wire_to_io)
+  template <int UNR, int DIR> FT_DEV void copy_run(long long start, int n) {
+    if (n <= 0) return;
     const IO* x = (const IO*)rc.send;
+    IO* y = (IO*)rc.recv;
     char* wr = rc.win[r] + woff;
     const int nth = be.nthr(), tid = be.tid();
-    for (int q0 = 0; q0 < total; q0 += nth * UNR) {
-      PackIO v[UNR];
-      long long el[UNR];
-      int nv[UNR];
+    const int nfull = n / VE;  // whole vectors; at most one ragged vector follows
+    int v0 = tid;
+    for (; v0 + (UNR - 1) * nth < nfull; v0 += UNR * nth) {
+      if constexpr (DIR == 0) {
+        PackIO v[UNR];
 #pragma unroll
-      for (int u = 0; u < UNR; ++u) {
-        const int q = q0 + u * nth + tid;
-        nv[u] = 0;
-        if (q < total) {
-          const int b = q / CV, vi = q - b * CV;
-          if ((b % g1) != (r % g1)) {  // blocks I own after stage 0 are read straight from `send`
-            long long start;
-            const int n = tile_valid32(b, t, &start) - vi * VE;
-            if (n > 0) {
-              nv[u] = n < VE ? n : VE;
-              el[u] = start + vi * VE;
-              v[u] = ld_user(x, el[u], nv[u]);
-            }
-          }
-        }
+        for (int u = 0; u < UNR; ++u) v[u] = ld_user(x, start + (long long)(v0 + u * nth) * VE, VE);
+#pragma unroll
+        for (int u = 0; u < UNR; ++u) st_win(wr, (start + (long long)(v0 + u * nth) * VE) * (long long)sizeof(T), io_to_wire(v[u]));
+      } else {
+        PackT v[UNR];
+#pragma unroll
+        for (int u = 0; u < UNR; ++u) v[u] = ld_win(wr, (start + (long long)(v0 + u * nth) * VE) * (long long)sizeof(T), true);
+#pragma unroll
+        for (int u = 0; u < UNR; ++u) st_user(y, start + (long long)(v0 + u * nth) * VE, wire_to_io(v[u]), VE);
       }
-#pragma unroll
-      for (int u = 0; u < UNR; ++u)
-        if (nv[u]) st_win(wr, el[u] * (long long)sizeof(T), io_to_wire(v[u]));
+    }
+    for (; v0 * VE < n; v0 += nth) {
+      const long long el = start + (long long)v0 * VE;
+      const int nv = n - v0 * VE < VE ? n - v0 * VE : VE;
+      if constexpr (DIR == 0) st_win(wr, el * (long long)sizeof(T), io_to_wire(ld_user(x, el, nv)));
+      else st_user(y, el, wire_to_io(ld_win(wr, el * (long long)sizeof(T), true)), nv);
+    }
+  }
+
+  // ---- phase IN: private user buffer -> my window (only the blocks some peer will pull) -------------
+  template <int UNR> FT_DEV void copy_in_tile(int t) {
+    const int N = a.plan.nranks, g1 = a.plan.gap[1];
+    for (int b = 0; b < N; ++b) {
+      if ((b % g1) == (r % g1)) continue;  // blocks I own after stage 0 are read straight from `send`
+      long long start;
+      const int n = tile_valid32(b, t, &start);
+      copy_run<UNR, 0>(start, n);
     }
   }
 
@@ -399,35 +410,11 @@ struct StagedCta {
   // ---- NVLS (multicast) pieces ---------------------------------------------------------------------------
   // Copy every block of tile t from the user buffer into my window (the switch reads all of them).
   template <int UNR> FT_DEV void copy_in_all_tile(int t) {
-    const Layout& L = a.lay;
     const int N = a.plan.nranks;
-    const int CV = (int)((L.tile + VE - 1) / VE);
-    const int total = N * CV;
-    const IO* x = (const IO*)rc.send;
-    char* wr = rc.win[r] + woff;
-    const int nth = be.nthr(), tid = be.tid();
-    for (int q0 = 0; q0 < total; q0 += nth * UNR) {
-      PackIO v[UNR];
-      long long el[UNR];
-      int nv[UNR];
-#pragma unroll
-      for (int u = 0; u < UNR; ++u) {
-        const int q = q0 + u * nth + tid;
-        nv[u] = 0;
-        if (q < total) {
-          const int b = q / CV, vi = q - b * CV;
-          long long start;
-          const int n = tile_valid32(b, t, &start) - vi * VE;
-          if (n > 0) {
-            nv[u] = n < VE ? n : VE;
-            el[u] = start + vi * VE;
-            v[u] = ld_user(x, el[u], nv[u]);
-          }
-        }
-      }
-#pragma unroll
-      for (int u = 0; u < UNR; ++u)
-        if (nv[u]) st_win(wr, el[u] * (long long)sizeof(T), io_to_wire(v[u]));
+    for (int b = 0; b < N; ++b) {
+      long long start;
+      const int n = tile_valid32(b, t, &start);
+      copy_run<UNR, 0>(start, n);
     }
   }
 
@@ -640,36 +627,11 @@ struct StagedCta {
 
   // Local copy of every block of tile t from my window to the user buffer through the epilogue.
   template <int UNR> FT_DEV void out_tile(int t) {
-    const Layout& L = a.lay;
     const int N = a.plan.nranks;
-    const int CV = (int)((L.tile + VE - 1) / VE);
-    const int total = N * CV;
-    IO* y = (IO*)rc.recv;
-    const char* wr = rc.win[r] + woff;
-    const int nth = be.nthr(), tid = be.tid();
-    for (int q0 = 0; q0 < total; q0 += nth * UNR) {
-      PackT v[UNR];
-      long long el[UNR];
-      int nv[UNR];
-#pragma unroll
-      for (int u = 0; u < UNR; ++u) {
-        const int q = q0 + u * nth + tid;
-        nv[u] = 0;
-        if (q < total) {
-          const int b = q / CV, vi = q - b * CV;
-          long long start;
-          const int n = tile_valid32(b, t, &start) - vi * VE;
-          if (n > 0) {
-            nv[u] = n < VE ? n : VE;
-            el[u] = start + vi * VE;
-            // written by the peers' multimem.st: read around L1
-            v[u] = ld_win(wr, el[u] * (long long)sizeof(T), true);
-          }
-        }
-      }
-#pragma unroll
-      for (int u = 0; u < UNR; ++u)
-        if (nv[u]) st_user(y, el[u], wire_to_io(v[u]), nv[u]);
+    for (int b = 0; b < N; ++b) {
+      long long start;
+      const int n = tile_valid32(b, t, &start);
+      copy_run<UNR, 1>(start, n);  // written by the peers' multimem.st: read around L1
     }
   }
 
