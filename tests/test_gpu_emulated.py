@@ -170,7 +170,11 @@ def test_auto_selection_small_is_oneshot_large_is_stages(comms):
     xs = [RNG.standard_normal(256).astype(np.float32) for _ in range(8)]
     run(c, xs)
     assert c.last_call()["algo"] == "oneshot"
-    xs = [RNG.standard_normal(1 << 20).astype(np.float32) for _ in range(8)]
+    xs = [RNG.standard_normal(1 << 18).astype(np.float32) for _ in range(8)]
+    got, _ = run(c, xs)
+    assert c.last_call()["algo"] in ("twoshot", "oneshot")     # 1 MiB: still an LL size
+    np.testing.assert_allclose(got[0], np.sum(np.stack(xs).astype(np.float64), 0), rtol=1e-5, atol=1e-5)
+    xs = [RNG.standard_normal(1 << 22).astype(np.float32) for _ in range(8)]   # 16 MiB: bandwidth kernels
     got, _ = run(c, xs)
     assert c.last_call()["algo"] == "stages"
     np.testing.assert_allclose(got[3], np.sum(np.stack(xs).astype(np.float64), 0), rtol=1e-4, atol=1e-4)
