@@ -1,7 +1,7 @@
 # Build of the flextree-b200 native libraries and tools.
 #   make host     -> build/libflextree_host.so  (planner + CPU world; g++ only, runs anywhere)
 #   make cuda     -> allreduce-over-mpi_b200/lib/libflextree.so (everything; nvcc, sm_100a)
-#   make tools    -> build/ft_plan, build/ft_bench, build/nccl_bench
+#   make tools    -> build/ft_plan, build/ft_bench (--comm-type nccl is the NCCL harness), build/ftrun
 # Capability parity with the reference build files: allreduce_over_mpi/CMakeLists.txt (flags, version
 # stamping), allreduce_over_mpi/Makefile (build/clean), cost_model/CMakeLists.txt.
 NVCC ?= nvcc
@@ -35,7 +35,7 @@ RT_CC_OBJ := $(RT_CC_SRC:%.cc=$(B)/%.o)
 all: host cuda tools
 host: $(B)/libflextree_host.so
 cuda: $(LIBDIR)/libflextree.so
-tools: $(B)/ft_plan $(B)/ft_bench
+tools: $(B)/ft_plan $(B)/ft_bench $(B)/ftrun
 
 $(B)/%.o: %.cc
 	@mkdir -p $(dir $@)
@@ -62,11 +62,12 @@ $(LIBDIR)/libflextree.so: $(PLANNER_OBJ) $(HOST_OBJ) $(RT_CC_OBJ) $(CUDA_OBJ)
 $(B)/ft_plan: csrc/tools/ft_plan.cc $(PLANNER_OBJ)
 	$(CXX) $(CXXFLAGS) -o $@ $^
 
+$(B)/ftrun: csrc/tools/ftrun.cc
+	@mkdir -p $(B)
+	$(CXX) $(CXXFLAGS) -o $@ $<
+
 $(B)/ft_bench: csrc/tools/ft_bench.cu $(LIBDIR)/libflextree.so
 	$(NVCC) $(NVFLAGS) -o $@ $< -L$(LIBDIR) -lflextree -ldl -Xlinker -rpath -Xlinker '$$ORIGIN/../$(LIBDIR)'
-
-$(B)/nccl_bench: csrc/tools/nccl_bench.cu
-	$(NVCC) $(NVFLAGS) -o $@ $< -lnccl
 
 # ThreadSanitizer run of the algorithm templates on the CPU world (the reference has no
 # sanitizer targets at all) and the SCM_RIGHTS fd-channel test.

@@ -32,6 +32,12 @@
 #include <vector>
 
 #include "flextree_host.h"
+// The GPU half of the library is optional here: a program linked against libflextree.so (the CUDA build) gets its
+// DEVICE buffers reduced by the NVLink kernels; linked against the host-only libflextree_host.so these symbols are
+// absent (weak, null) and every buffer is treated as host memory.
+#pragma weak ft_pointer_device
+#pragma weak ft_comm_create
+#pragma weak ft_allreduce_blocking
 #undef MPI_Allreduce_FT  // flextree.h aliases it to the GPU entry point under STANDALONE_TEST; here it is the function below
 
 static int FT_enabled() { return ft_enabled(); }
@@ -78,6 +84,8 @@ struct State {
   World world;
   ft_host_comm_t* hc = nullptr;
   size_t window = 0;
+  ft_comm_t* gpu = nullptr;  // created on the first call with device buffers
+  int gpu_device = -1;
 };
 
 inline long long env_ll(const char* name, long long dflt) {
@@ -136,6 +144,30 @@ inline State& state_for(MPI_Comm comm, size_t msg_bytes) {
   return s;
 }
 
+// Device buffers: one GPU communicator per MPI communicator (handles exchanged over the same MPI point-to-point
+// all-gather), created on first use. The MPI ranks must sit on one NVSwitch box, one GPU each.
+inline ft_comm_t* gpu_comm_for(MPI_Comm comm, int device) {
+  static std::map<MPI_Comm, State*> table;
+  State*& s = table[comm];
+  if (!s) {
+    s = new State;  // never freed, like the reference's staging buffer (:932-950)
+    s->world.comm = comm;
+    MPI_Comm_rank(comm, &s->world.rank);
+    MPI_Comm_size(comm, &s->world.size);
+  }
+  if (!s->gpu) {
+    if (ft_comm_create(&s->gpu, s->world.rank, s->world.size, device, allgather_bytes, &s->world, nullptr) != FT_SUCCESS) {
+      std::cerr << "flextree: cannot create the GPU communicator: " << ft_last_error() << std::endl;
+      exit(1);
+    }
+    s->gpu_device = device;
+  } else if (s->gpu_device != device) {
+    std::cerr << "flextree: a rank must keep using buffers of one GPU (was " << s->gpu_device << ", now " << device << ")" << std::endl;
+    exit(1);
+  }
+  return s->gpu;
+}
+
 }  // namespace detail
 }  // namespace FlexTree
 
@@ -157,6 +189,25 @@ inline int MPI_Allreduce_FT(const void* sendbuf, void* recvbuf, int count, MPI_D
   MPI_Type_size(datatype, &tsize);
   MPI_Comm_size(comm, &nranks);
   const bool in_place = sendbuf == MPI_IN_PLACE;
+  if (count > 0) {
+    // Where do the buffers live? Device memory goes to the NVLink kernels (FT_TOPO / FT_ALGO apply there as well).
+    if (ft_pointer_device && ft_comm_create && ft_allreduce_blocking) {
+      const int dev = ft_pointer_device(recvbuf);
+      const int sdev = in_place ? dev : ft_pointer_device(sendbuf);
+      if (dev >= 0 || sdev >= 0) {
+        if (dev != sdev) {
+          std::cerr << "flextree: sendbuf and recvbuf must both be device memory of the same GPU (or both host memory)" << std::endl;
+          exit(1);
+        }
+        ft_comm_t* g = gpu_comm_for(comm, dev);
+        if (ft_allreduce_blocking(in_place ? FT_IN_PLACE : sendbuf, recvbuf, (size_t)count, (ft_dtype_t)dt, (ft_op_t)rop, g) != FT_SUCCESS) {
+          std::cerr << "flextree: GPU allreduce failed: " << ft_last_error() << std::endl;
+          exit(1);
+        }
+        return 0;
+      }
+    }
+  }
   if (nranks <= 1 || count <= 0) {
     if (!in_place && count > 0) memcpy(recvbuf, sendbuf, (size_t)count * (size_t)tsize);
     return 0;

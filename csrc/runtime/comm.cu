@@ -168,6 +168,7 @@ void apply_options(ft_comm* c, const ft_comm_options_t* o) {
   if (o) d = *o;
   c->window_bytes = d.window_bytes ? d.window_bytes : (size_t)env_ll("FT_WINDOW_BYTES", 64ll << 20);
   c->ll_bytes = d.ll_bytes ? d.ll_bytes : (size_t)env_ll("FT_LL_BYTES", 32ll << 20);
+  if ((long long)c->window_bytes < (1 << 20)) c->window_bytes = 1 << 20;  // also catches 0 and negative env values
   c->window_bytes = (c->window_bytes + 4095) & ~(size_t)4095;
   c->ll_bytes = (c->ll_bytes + 4095) & ~(size_t)4095;
   int mc = d.use_multicast;
@@ -256,9 +257,15 @@ void destroy_segments(std::vector<Segment>* v) {
 ft_result_t grow_window(ft_comm* c, size_t need_per_parity) {
   if (need_per_parity <= c->window_bytes && !c->win.empty()) return FT_SUCCESS;
   c->policy_gen++;
-  if (c->group) for (auto* m : c->group->members) if (m) m->policy_gen++;
-  size_t nb = c->window_bytes;
-  while (nb < need_per_parity) nb *= 2;
+  if (c->group) {
+    std::lock_guard<std::mutex> lk(c->group->mu);
+    for (auto* m : c->group->members) if (m) m->policy_gen++;
+  }
+  size_t nb = c->window_bytes < 4096 ? 4096 : c->window_bytes;  // FT_WINDOW_BYTES=0 must not loop forever
+  while (nb < need_per_parity) {
+    if (nb > ((size_t)1 << 62)) { set_last_error("staging window request too large"); return FT_ERR_NOMEM; }
+    nb *= 2;
+  }
   nb = (nb + 4095) & ~(size_t)4095;
   FT_LOG(1, "rank %d: staging window -> %zu bytes per parity", c->rank, nb);
   std::string err;
@@ -272,7 +279,7 @@ ft_result_t grow_window(ft_comm* c, size_t need_per_parity) {
       cudaDeviceSynchronize();
     }
     std::vector<Segment> segs;
-    if (!segment_create_local(c->group->devices, 2 * nb, &segs, &err)) {
+    if (!segment_create_local(c->group->devices, 2 * nb, &segs, &err, &c->sopt)) {
       set_last_error(err);
       return FT_ERR_CUDA;
     }
@@ -905,8 +912,12 @@ ft_result_t ft_comm_create_local(ft_comm_t** comms, int nranks, const int* devic
     made.push_back(c);
   }
   group->members = made;
-  if (!segment_create_local(group->devices, FT_PAD_BYTES, &pads, &err) ||
-      !segment_create_local(group->devices, 2 * made[0]->ll_bytes, &lls, &err)) {
+  // flag pads and LL buffers: VMM when available (same kind of memory as the windows), never multicast-bound
+  SymmOptions nomc = made[0]->sopt;
+  nomc.try_multicast = false;
+  nomc.require_multicast = false;
+  if (!segment_create_local(group->devices, FT_PAD_BYTES, &pads, &err, &nomc) ||
+      !segment_create_local(group->devices, 2 * made[0]->ll_bytes, &lls, &err, &nomc)) {
     fail(&rc, FT_ERR_CUDA, "ft_comm_create_local: " + err);
     for (auto* c : made) delete c;
     return rc;
@@ -916,9 +927,15 @@ ft_result_t ft_comm_create_local(ft_comm_t** comms, int nranks, const int* devic
     made[(size_t)i]->ll.assign(1, lls[(size_t)i]);
     rc = finish_create(made[(size_t)i]);
     if (rc != FT_SUCCESS) return rc;
-    made[(size_t)i]->model.has_nvls = false;
     comms[i] = made[(size_t)i];
   }
+  // One process owns all the devices, so the multicast object can be built right here (cuMulticastCreate + AddDevice
+  // + BindMem for every device, no fd passing): C programs without a launcher get the NVLS kernels too.
+  bool mc = made[0]->sopt.try_multicast && nranks > 1 && pads[0].kind == SEG_LOCAL_VMM;
+  for (int i = 0; i < nranks && mc; ++i) mc = device_supports_multicast(devices[i]);
+  for (auto* c : made) c->model.has_nvls = mc;
+  FT_LOG(1, "local group of %d devices: segments via %s, multicast %s", nranks, pads[0].kind == SEG_LOCAL_VMM ? "VMM" : "cudaMalloc",
+         mc ? "available" : "off");
   return FT_SUCCESS;
 }
 
@@ -1155,7 +1172,7 @@ ft_result_t ft_symm_alloc(ft_comm_t* c, size_t bytes, void** ptr) {
     std::lock_guard<std::mutex> lk(c->group->mu);
     if (c->local_alloc_cursor == c->user.size()) {  // first member to ask allocates for everybody
       std::vector<Segment> segs;
-      if (!segment_create_local(c->group->devices, padded, &segs, &err)) {
+      if (!segment_create_local(c->group->devices, padded, &segs, &err, &c->sopt)) {
         set_last_error(err);
         return FT_ERR_CUDA;
       }
@@ -1226,6 +1243,30 @@ ft_result_t ft_allreduce_ex(const void* sendbuf, void* recvbuf, size_t count, ft
   const void* s[1] = {sendbuf};
   void* r[1] = {recvbuf};
   return do_allreduce(comm, s, r, count, (int)dtype, (int)wire_dtype, (int)op, scale, (cudaStream_t)stream);
+}
+
+// MPI-style blocking form on the default stream: when it returns, recvbuf holds the result (what a captured
+// MPI_Allreduce on device memory needs, compat/mpi_mod.hpp).
+ft_result_t ft_allreduce_blocking(const void* sendbuf, void* recvbuf, size_t count, ft_dtype_t dtype, ft_op_t op, ft_comm_t* comm) {
+  ft_result_t r = ft_allreduce(sendbuf, recvbuf, count, dtype, op, comm, nullptr);
+  if (r != FT_SUCCESS) return r;
+  FT_CHECK_RT(cudaStreamSynchronize(nullptr));
+  const unsigned e = ft_comm_error_peek(comm);
+  if (e) {
+    set_last_error("device watchdog fired during the collective");
+    return FT_ERR_TIMEOUT;
+  }
+  return FT_SUCCESS;
+}
+
+// -1: host (or unknown) memory; otherwise the ordinal of the device the allocation lives on.
+int ft_pointer_device(const void* p) {
+  cudaPointerAttributes a;
+  if (cudaPointerGetAttributes(&a, p) != cudaSuccess) {
+    (void)cudaGetLastError();
+    return -1;
+  }
+  return (a.type == cudaMemoryTypeDevice || a.type == cudaMemoryTypeManaged) ? a.device : -1;
 }
 
 ft_result_t ft_allreduce_multi(const void* const* sendbufs, void* const* recvbufs, size_t count, ft_dtype_t dtype,

@@ -127,6 +127,35 @@ static bool upload_table(Segment* seg, std::string* err) {
 }
 
 // ---- VMM provider ------------------------------------------------------------------------------------
+// Undo a partially built VMM segment: unmap what was mapped, release every handle (own and imported) and the
+// multicast mapping, so that a collective failure leaves nothing behind before the cudaIpc fallback.
+static void vmm_release(Segment* seg) {
+  if (seg->d_table) { cudaFree(seg->d_table); seg->d_table = nullptr; }
+  if (seg->mc_base) {
+    drv::p_cuMemUnmap((CUdeviceptr)seg->mc_base, seg->mapped_bytes);
+    drv::p_cuMemAddressFree((CUdeviceptr)seg->mc_base, seg->mapped_bytes);
+    CUdevice dev;
+    if (drv::p_cuDeviceGet(&dev, seg->device) == CUDA_SUCCESS)
+      drv::p_cuMulticastUnbind((CUmemGenericAllocationHandle)seg->mc_handle, dev, 0, seg->mapped_bytes);
+    drv::p_cuMemRelease((CUmemGenericAllocationHandle)seg->mc_handle);
+    seg->mc_base = nullptr;
+    seg->mc_handle = 0;
+  }
+  for (size_t p = 0; p < seg->base.size(); ++p) {
+    if (seg->base[p]) {
+      drv::p_cuMemUnmap((CUdeviceptr)seg->base[p], seg->mapped_bytes);
+      drv::p_cuMemAddressFree((CUdeviceptr)seg->base[p], seg->mapped_bytes);
+      seg->base[p] = nullptr;
+    }
+    if (p < seg->vmm_handles.size() && seg->vmm_handles[p]) {
+      drv::p_cuMemRelease((CUmemGenericAllocationHandle)seg->vmm_handles[p]);
+      seg->vmm_handles[p] = 0;
+    }
+  }
+  (void)cudaGetLastError();
+  seg->kind = SEG_NONE;
+}
+
 static bool vmm_create(const Bootstrap& bs, int device, size_t bytes, const SymmOptions& opt, Segment* seg,
                        std::string* err) {
   if (!drv::load()) { if (err) *err = "driver entry points unavailable"; return false; }
@@ -218,24 +247,46 @@ static bool vmm_create(const Bootstrap& bs, int device, size_t bytes, const Symm
   ::close(my_fd);
   if (!all_ok(bs, ok)) {
     ch.close_();
+    vmm_release(seg);
     if (err) *err = "fd exchange: " + cerr_;
-    return false;  // leaks imported handles of a broken setup; process is expected to fall back / exit
+    return false;
   }
 
-  // 4. map everything
+  // 4. map everything. A failure on ONE rank must fail the call on EVERY rank (the caller falls back to cudaIpc,
+  // whose bootstrap exchanges have a different size and order): accumulate a local flag, then agree.
   CUmemAccessDesc acc{};
   acc.location.type = CU_MEM_LOCATION_TYPE_DEVICE;
   acc.location.id = device;
   acc.flags = CU_MEM_ACCESS_FLAGS_PROT_READWRITE;
-  for (int p = 0; p < bs.nranks; ++p) {
+  std::string lerr;
+  bool ok4 = true;
+  for (int p = 0; p < bs.nranks && ok4; ++p) {
     CUdeviceptr va = 0;
-    FT_CU(drv::p_cuMemAddressReserve(&va, sz, align, 0, 0), "cuMemAddressReserve");
-    FT_CU(drv::p_cuMemMap(va, sz, 0, seg->vmm_handles[(size_t)p], 0), "cuMemMap");
-    FT_CU(drv::p_cuMemSetAccess(va, sz, &acc, 1), "cuMemSetAccess");
+    CUresult r = drv::p_cuMemAddressReserve(&va, sz, align, 0, 0);
+    if (r != CUDA_SUCCESS) { ok4 = false; lerr = "cuMemAddressReserve: " + drv::errstr(r); break; }
     seg->base[(size_t)p] = (char*)va;
+    r = drv::p_cuMemMap(va, sz, 0, seg->vmm_handles[(size_t)p], 0);
+    if (r != CUDA_SUCCESS) {
+      ok4 = false;
+      lerr = "cuMemMap: " + drv::errstr(r);
+      drv::p_cuMemAddressFree(va, sz);
+      seg->base[(size_t)p] = nullptr;
+      break;
+    }
+    r = drv::p_cuMemSetAccess(va, sz, &acc, 1);
+    if (r != CUDA_SUCCESS) { ok4 = false; lerr = "cuMemSetAccess: " + drv::errstr(r); }
   }
-  FT_RT(cudaMemset(seg->base[(size_t)bs.rank], 0, sz), "cudaMemset(segment)");
-  FT_RT(cudaDeviceSynchronize(), "sync");
+  if (ok4 && (cudaMemset(seg->base[(size_t)bs.rank], 0, sz) != cudaSuccess || cudaDeviceSynchronize() != cudaSuccess)) {
+    ok4 = false;
+    lerr = "cudaMemset(segment) failed";
+    (void)cudaGetLastError();
+  }
+  if (!all_ok(bs, ok4)) {
+    ch.close_();
+    vmm_release(seg);
+    if (err) *err = "mapping failed on some rank" + (lerr.empty() ? std::string() : ": " + lerr);
+    return false;
+  }
 
   // 5. multicast (optional)
   if (want_mc) {
@@ -275,15 +326,25 @@ static bool vmm_create(const Bootstrap& bs, int device, size_t bytes, const Symm
         seg->mc_handle = mch;
       }
     }
-    if (!seg->mc_base && opt.require_multicast) {
+    if (!seg->mc_base && mch) {  // agreed failure somewhere after the object existed: give it back
+      if (bound || all_added) drv::p_cuMulticastUnbind(mch, dev, 0, sz);
+      drv::p_cuMemRelease(mch);
+    }
+    if (!seg->mc_base && opt.require_multicast) {  // the same decision on every rank (mc_base is set after an all_ok)
       ch.close_();
+      vmm_release(seg);
       if (err) *err = "multicast requested but could not be set up";
       return false;
     }
   }
   ch.close_();
-  if (!upload_table(seg, err)) return false;
-  return bs.barrier();
+  const bool up = upload_table(seg, err);
+  if (!all_ok(bs, up)) {  // doubles as the exit barrier
+    vmm_release(seg);
+    if (err && up) *err = "device pointer table upload failed on some rank";
+    return false;
+  }
+  return true;
 }
 
 // ---- cudaIpc provider --------------------------------------------------------------------------------
@@ -379,51 +440,220 @@ void segment_destroy(Segment* seg) {
       if (p == seg->self) cudaFree(seg->base[(size_t)p]);
       else cudaIpcCloseMemHandle(seg->base[(size_t)p]);
     }
-  } else if (seg->kind == SEG_LOCAL) {
-    if (seg->base[(size_t)seg->self]) cudaFree(seg->base[(size_t)seg->self]);
   }
+  // SEG_LOCAL / SEG_LOCAL_VMM: the memory belongs to the group (seg->shared) and goes with its last view
   (void)cudaGetLastError();
   seg->kind = SEG_NONE;
   seg->base.clear();
   seg->d_table = nullptr;
   seg->mc_base = nullptr;
+  seg->shared.reset();
   if (prev >= 0) cudaSetDevice(prev);
 }
 
-bool segment_create_local(const std::vector<int>& devices, size_t bytes, std::vector<Segment>* segs,
-                          std::string* err) {
+// ---- one process, N devices ---------------------------------------------------------------------------------
+namespace {
+struct LocalShared {  // what the N views of a one-process segment share; freed with the last view
+  SegKind kind = SEG_NONE;
+  std::vector<int> devices;
+  std::vector<char*> bufs;                        // per rank
+  std::vector<unsigned long long> handles;        // SEG_LOCAL_VMM: CUmemGenericAllocationHandle per rank
+  unsigned long long mc_handle = 0;
+  char* mc_base = nullptr;
+  size_t mapped = 0;
+  ~LocalShared() {
+    int prev = -1;
+    cudaGetDevice(&prev);
+    // nobody may still be using the memory: wait for every device of the group
+    for (int d : devices) {
+      cudaSetDevice(d);
+      cudaDeviceSynchronize();
+    }
+    if (kind == SEG_LOCAL) {
+      for (size_t i = 0; i < bufs.size(); ++i) {
+        if (!bufs[i]) continue;
+        cudaSetDevice(devices[i]);
+        cudaFree(bufs[i]);
+      }
+    } else if (kind == SEG_LOCAL_VMM && drv::load()) {
+      if (mc_base) {
+        drv::p_cuMemUnmap((CUdeviceptr)mc_base, mapped);
+        drv::p_cuMemAddressFree((CUdeviceptr)mc_base, mapped);
+      }
+      if (mc_handle) {
+        for (int d : devices) {
+          CUdevice dev;
+          if (drv::p_cuDeviceGet(&dev, d) == CUDA_SUCCESS) drv::p_cuMulticastUnbind((CUmemGenericAllocationHandle)mc_handle, dev, 0, mapped);
+        }
+        drv::p_cuMemRelease((CUmemGenericAllocationHandle)mc_handle);
+      }
+      for (size_t i = 0; i < bufs.size(); ++i) {
+        if (bufs[i]) {
+          drv::p_cuMemUnmap((CUdeviceptr)bufs[i], mapped);
+          drv::p_cuMemAddressFree((CUdeviceptr)bufs[i], mapped);
+        }
+        if (i < handles.size() && handles[i]) drv::p_cuMemRelease((CUmemGenericAllocationHandle)handles[i]);
+      }
+    }
+    (void)cudaGetLastError();
+    if (prev >= 0) cudaSetDevice(prev);
+  }
+};
+
+bool distinct(const std::vector<int>& v) {
+  for (size_t i = 0; i < v.size(); ++i)
+    for (size_t j = i + 1; j < v.size(); ++j)
+      if (v[i] == v[j]) return false;
+  return true;
+}
+
+// VMM allocations on every device, each mapped ONCE with access for all devices (one process = one address space),
+// optionally bound to one multicast object. Returns false (nothing leaked) if any step is unavailable.
+bool local_vmm(const std::vector<int>& devices, size_t bytes, bool want_mc, std::shared_ptr<LocalShared>* out, std::string* err) {
+  if (!drv::load()) { if (err) *err = "driver entry points unavailable"; return false; }
   const int n = (int)devices.size();
-  if (bytes == 0) bytes = 16;
-  segs->assign((size_t)n, Segment());
-  std::vector<char*> bufs((size_t)n, nullptr);
-  int prev = -1;
-  cudaGetDevice(&prev);
+  auto sh = std::make_shared<LocalShared>();
+  sh->kind = SEG_LOCAL_VMM;
+  sh->devices = devices;
+  sh->bufs.assign((size_t)n, nullptr);
+  sh->handles.assign((size_t)n, 0);
+  std::vector<CUdevice> cudev((size_t)n);
   for (int i = 0; i < n; ++i) {
     FT_RT(cudaSetDevice(devices[(size_t)i]), "cudaSetDevice");
+    FT_RT(cudaFree(0), "context");
+    FT_CU(drv::p_cuDeviceGet(&cudev[(size_t)i], devices[(size_t)i]), "cuDeviceGet");
     for (int j = 0; j < n; ++j) {
-      if (devices[(size_t)j] == devices[(size_t)i]) continue;
+      if (i == j) continue;
       int can = 0;
       cudaDeviceCanAccessPeer(&can, devices[(size_t)i], devices[(size_t)j]);
       if (!can) { if (err) *err = "no peer access between devices"; return false; }
-      cudaError_t e = cudaDeviceEnablePeerAccess(devices[(size_t)j], 0);
-      if (e != cudaSuccess && e != cudaErrorPeerAccessAlreadyEnabled) {
-        if (err) *err = std::string("cudaDeviceEnablePeerAccess: ") + cudaGetErrorString(e);
-        return false;
-      }
-      (void)cudaGetLastError();
     }
-    FT_RT(cudaMalloc(&bufs[(size_t)i], bytes), "cudaMalloc(segment)");
-    FT_RT(cudaMemset(bufs[(size_t)i], 0, bytes), "cudaMemset(segment)");
+  }
+  want_mc = want_mc && n > 1;
+  for (int i = 0; i < n && want_mc; ++i) want_mc = device_supports_multicast(devices[(size_t)i]);
+  CUmemAllocationProp prop{};
+  prop.type = CU_MEM_ALLOCATION_TYPE_PINNED;
+  prop.location.type = CU_MEM_LOCATION_TYPE_DEVICE;
+  prop.location.id = devices[0];
+  prop.requestedHandleTypes = CU_MEM_HANDLE_TYPE_POSIX_FILE_DESCRIPTOR;  // same kind of allocation as the multi-process path
+  size_t gran = 0, mc_gran = 0;
+  FT_CU(drv::p_cuMemGetAllocationGranularity(&gran, &prop, CU_MEM_ALLOC_GRANULARITY_RECOMMENDED), "granularity");
+  CUmulticastObjectProp mcp{};
+  if (want_mc) {
+    mcp.numDevices = (unsigned)n;
+    mcp.handleTypes = CU_MEM_HANDLE_TYPE_POSIX_FILE_DESCRIPTOR;
+    mcp.size = bytes;
+    if (drv::p_cuMulticastGetGranularity(&mc_gran, &mcp, CU_MULTICAST_GRANULARITY_RECOMMENDED) != CUDA_SUCCESS) want_mc = false;
+  }
+  size_t align = gran > mc_gran ? gran : mc_gran;
+  if (align == 0) align = 2u << 20;
+  const size_t sz = (bytes + align - 1) / align * align;
+  sh->mapped = sz;
+  std::vector<CUmemAccessDesc> acc((size_t)n);
+  for (int i = 0; i < n; ++i) {
+    acc[(size_t)i].location.type = CU_MEM_LOCATION_TYPE_DEVICE;
+    acc[(size_t)i].location.id = devices[(size_t)i];
+    acc[(size_t)i].flags = CU_MEM_ACCESS_FLAGS_PROT_READWRITE;
+  }
+  for (int i = 0; i < n; ++i) {
+    prop.location.id = devices[(size_t)i];
+    CUmemGenericAllocationHandle h = 0;
+    FT_CU(drv::p_cuMemCreate(&h, sz, &prop, 0), "cuMemCreate");
+    sh->handles[(size_t)i] = h;
+    CUdeviceptr va = 0;
+    FT_CU(drv::p_cuMemAddressReserve(&va, sz, align, 0, 0), "cuMemAddressReserve");
+    sh->bufs[(size_t)i] = (char*)va;  // from here on ~LocalShared cleans up
+    FT_CU(drv::p_cuMemMap(va, sz, 0, h, 0), "cuMemMap");
+    FT_CU(drv::p_cuMemSetAccess(va, sz, acc.data(), (size_t)n), "cuMemSetAccess");
+    FT_RT(cudaSetDevice(devices[(size_t)i]), "cudaSetDevice");
+    FT_RT(cudaMemset((void*)va, 0, sz), "cudaMemset(segment)");
     FT_RT(cudaDeviceSynchronize(), "sync");
+  }
+  if (want_mc) {  // failure here only costs the NVLS path
+    mcp.size = sz;
+    CUmemGenericAllocationHandle mch = 0;
+    bool ok = drv::p_cuMulticastCreate(&mch, &mcp) == CUDA_SUCCESS;
+    for (int i = 0; i < n && ok; ++i) ok = drv::p_cuMulticastAddDevice(mch, cudev[(size_t)i]) == CUDA_SUCCESS;  // all devices before any bind
+    for (int i = 0; i < n && ok; ++i)
+      ok = drv::p_cuMulticastBindMem(mch, 0, (CUmemGenericAllocationHandle)sh->handles[(size_t)i], 0, sz, 0) == CUDA_SUCCESS;
+    CUdeviceptr va = 0;
+    if (ok) ok = drv::p_cuMemAddressReserve(&va, sz, align, 0, 0) == CUDA_SUCCESS;
+    if (ok) {
+      if (drv::p_cuMemMap(va, sz, 0, mch, 0) == CUDA_SUCCESS && drv::p_cuMemSetAccess(va, sz, acc.data(), (size_t)n) == CUDA_SUCCESS) {
+        sh->mc_base = (char*)va;
+        sh->mc_handle = mch;
+      } else {
+        drv::p_cuMemAddressFree(va, sz);
+        ok = false;
+      }
+    }
+    if (!ok && mch) {
+      if (!sh->mc_handle) {
+        for (int i = 0; i < n; ++i) drv::p_cuMulticastUnbind(mch, cudev[(size_t)i], 0, sz);
+        drv::p_cuMemRelease(mch);
+      }
+    }
+  }
+  *out = sh;
+  return true;
+}
+}  // namespace
+
+bool segment_create_local(const std::vector<int>& devices, size_t bytes, std::vector<Segment>* segs,
+                          std::string* err, const SymmOptions* opt) {
+  const int n = (int)devices.size();
+  if (bytes == 0) bytes = 16;
+  segs->assign((size_t)n, Segment());
+  int prev = -1;
+  cudaGetDevice(&prev);
+  std::shared_ptr<LocalShared> sh;
+  if (opt && opt->try_vmm && n > 1 && distinct(devices)) {
+    std::string verr;
+    if (!local_vmm(devices, bytes, opt->try_multicast, &sh, &verr)) {
+      sh.reset();
+      (void)cudaGetLastError();
+      if (opt->require_multicast) { if (err) *err = "multicast requested but VMM set-up failed: " + verr; return false; }
+    } else if (opt->require_multicast && !sh->mc_base) {
+      if (err) *err = "multicast requested but could not be set up";
+      return false;
+    }
+  }
+  if (!sh) {
+    sh = std::make_shared<LocalShared>();
+    sh->kind = SEG_LOCAL;
+    sh->devices = devices;
+    sh->bufs.assign((size_t)n, nullptr);
+    for (int i = 0; i < n; ++i) {
+      FT_RT(cudaSetDevice(devices[(size_t)i]), "cudaSetDevice");
+      for (int j = 0; j < n; ++j) {
+        if (devices[(size_t)j] == devices[(size_t)i]) continue;
+        int can = 0;
+        cudaDeviceCanAccessPeer(&can, devices[(size_t)i], devices[(size_t)j]);
+        if (!can) { if (err) *err = "no peer access between devices"; return false; }
+        cudaError_t e = cudaDeviceEnablePeerAccess(devices[(size_t)j], 0);
+        if (e != cudaSuccess && e != cudaErrorPeerAccessAlreadyEnabled) {
+          if (err) *err = std::string("cudaDeviceEnablePeerAccess: ") + cudaGetErrorString(e);
+          return false;
+        }
+        (void)cudaGetLastError();
+      }
+      FT_RT(cudaMalloc(&sh->bufs[(size_t)i], bytes), "cudaMalloc(segment)");
+      FT_RT(cudaMemset(sh->bufs[(size_t)i], 0, bytes), "cudaMemset(segment)");
+      FT_RT(cudaDeviceSynchronize(), "sync");
+    }
+    sh->mapped = bytes;
   }
   for (int i = 0; i < n; ++i) {
     Segment& s = (*segs)[(size_t)i];
-    s.kind = SEG_LOCAL;
-    s.bytes = s.mapped_bytes = bytes;
+    s.kind = sh->kind;
+    s.bytes = bytes;
+    s.mapped_bytes = sh->mapped;
     s.nranks = n;
     s.self = i;
     s.device = devices[(size_t)i];
-    s.base = bufs;
+    s.base = sh->bufs;
+    s.mc_base = sh->mc_base;
+    s.shared = sh;
     FT_RT(cudaSetDevice(s.device), "cudaSetDevice");
     if (!upload_table(&s, err)) return false;
   }

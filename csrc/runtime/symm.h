@@ -14,6 +14,7 @@
 #include <cuda_runtime.h>
 #include <stddef.h>
 
+#include <memory>
 #include <string>
 #include <vector>
 
@@ -40,7 +41,7 @@ struct Bootstrap {
   }
 };
 
-enum SegKind { SEG_NONE = 0, SEG_VMM = 1, SEG_IPC = 2, SEG_LOCAL = 3 };
+enum SegKind { SEG_NONE = 0, SEG_VMM = 1, SEG_IPC = 2, SEG_LOCAL = 3, SEG_LOCAL_VMM = 4 };
 
 struct Segment {
   SegKind kind = SEG_NONE;
@@ -55,6 +56,10 @@ struct Segment {
   size_t mapped_bytes = 0;
   int device = 0;
   int self = 0;
+  // One-process groups (SEG_LOCAL, SEG_LOCAL_VMM): the N per-rank views alias the same allocations and mappings.
+  // They are released when the LAST view is destroyed - a member that goes away early must not pull the memory from
+  // under peers whose kernels may still be reading it.
+  std::shared_ptr<void> shared;
 };
 
 struct SymmOptions {
@@ -70,9 +75,12 @@ bool segment_create(const Bootstrap& bs, int device, size_t bytes, const SymmOpt
 void segment_destroy(Segment* seg);
 
 // One-process segments: devices[i] hosts rank i (devices may repeat: single-GPU emulation). Fills
-// segs[i] with rank i's view.
+// segs[i] with rank i's view. With distinct devices and opt.try_vmm the buffers come from the VMM API (cuMemCreate,
+// one mapping visible to every device) and, if opt.try_multicast and the devices support it, are bound to ONE
+// multicast object, so that a single process driving all GPUs gets the NVLS kernels too (no fd passing needed:
+// everything happens in one address space). Otherwise cudaMalloc + cudaDeviceEnablePeerAccess.
 bool segment_create_local(const std::vector<int>& devices, size_t bytes, std::vector<Segment>* segs,
-                          std::string* err);
+                          std::string* err, const SymmOptions* opt = nullptr);
 
 bool device_supports_multicast(int device);
 

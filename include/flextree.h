@@ -126,6 +126,17 @@ void ft_comm_options_default(ft_comm_options_t*);
 /* One process per GPU (what torch.distributed / torchrun gives you). */
 ft_result_t ft_comm_create(ft_comm_t** out, int rank, int nranks, int device, ft_allgather_fn ag,
                            void* ag_ctx, const ft_comm_options_t* opts);
+/* One process per GPU started by the launcher `ftrun -np N prog args...` (build/ftrun; the stand-in for the reference's
+ * mpirun, benchmark.cpp:48-52): rank, size and a bootstrap token come from the environment (FT_RANK, FT_SIZE,
+ * FT_LOCAL_RANK, FT_BOOT_TOKEN) and the handle exchange runs over unix sockets - no Python, no MPI, and the same
+ * VMM + multicast segments as the torch path. device < 0: use FT_LOCAL_RANK. The ft_env_* helpers give a C program
+ * the few collectives it needs around the library (rank-ordered printing, max over ranks of a timing). */
+ft_result_t ft_comm_create_from_env(ft_comm_t** out, int device, const ft_comm_options_t* opts);
+int ft_env_rank(void);        /* -1 when not started by ftrun */
+int ft_env_size(void);
+int ft_env_local_rank(void);
+int ft_env_allgather(const void* send, void* recv, size_t bytes); /* 0 = ok */
+int ft_env_barrier(void);
 /* One process, one rank per listed device (cudaDeviceEnablePeerAccess); comms[i] is rank i. */
 ft_result_t ft_comm_create_local(ft_comm_t** comms, int nranks, const int* devices,
                                  const ft_comm_options_t* opts);
@@ -200,6 +211,13 @@ ft_result_t ft_symm_free(ft_comm_t*, void* ptr);
  * ---------------------------------------------------------------------------------------------- */
 ft_result_t ft_allreduce(const void* sendbuf, void* recvbuf, size_t count, ft_dtype_t dtype, ft_op_t op,
                          ft_comm_t* comm, void* stream);
+
+/* Blocking form on the default stream (MPI semantics: recvbuf is ready when the call returns) and a pointer
+ * classifier (-1 = host memory, else the device ordinal): together they let compat/mpi_mod.hpp route a captured
+ * MPI_Allreduce on cudaMalloc'ed buffers to the GPU kernels (mpi_mod.hpp:1167-1171 captures every MPI_Allreduce). */
+ft_result_t ft_allreduce_blocking(const void* sendbuf, void* recvbuf, size_t count, ft_dtype_t dtype, ft_op_t op,
+                                  ft_comm_t* comm);
+int ft_pointer_device(const void* ptr);
 
 /* Extended form used by the torch path: fp32 user buffers with a 16-bit wire (wire_dtype), and a
  * fused `out = cast(sum * scale)` epilogue (the DDP 1/N). wire_dtype == dtype and scale == 1 give

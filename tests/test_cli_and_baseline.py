@@ -106,3 +106,24 @@ def test_launcher_front_end(tmp_path):
                        capture_output=True, text=True, cwd=ROOT, timeout=300)
     assert p.returncode == 0, p.stderr[-500:]
     assert "RANK 0 2 2" in p.stdout and "RANK 1 2 2" in p.stdout
+
+
+def test_ftrun_launcher_and_env_bootstrap(tmp_path):
+    """`ftrun -np 4 prog`: the C launcher + unix-socket all-gather that bootstraps C programs (no Python, no MPI)."""
+    import flextree._lib as L
+    if not os.path.exists(L.CUDA_LIB):
+        pytest.skip("libflextree.so not built")
+    subprocess.check_call(["make", "-C", ROOT, "-j4", "tools"], stdout=subprocess.DEVNULL)
+    exe = str(tmp_path / "env_boot_test")
+    libdir = os.path.dirname(L.CUDA_LIB)
+    subprocess.check_call(["/usr/bin/g++", "-std=c++17", "-O1", "-I", os.path.join(ROOT, "include"), "-o", exe,
+                           os.path.join(ROOT, "tests", "cpp", "env_boot_test.cc"), "-L", libdir, "-lflextree",
+                           "-Wl,-rpath," + libdir])
+    p = subprocess.run([os.path.join(ROOT, "build", "ftrun"), "-np", "4", "--gpus", "2", exe], capture_output=True, text=True, timeout=120)
+    assert p.returncode == 0, p.stdout + p.stderr
+    lines = [ln for ln in p.stdout.splitlines() if ln.startswith("ENV_BOOT_OK")]
+    assert lines == [f"ENV_BOOT_OK {r}/4 local {r % 2}" for r in range(4)], p.stdout
+    # a failing rank takes the job down with its exit code
+    p = subprocess.run([os.path.join(ROOT, "build", "ftrun"), "-np", "2", "sh", "-c", "test $FT_RANK = 0 || exit 7; sleep 30"],
+                       capture_output=True, text=True, timeout=60)
+    assert p.returncode == 7
