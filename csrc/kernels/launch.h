@@ -26,6 +26,8 @@ struct LaunchCtx {
 bool cuda_launch(int dtype, int io_dtype, int op, bool vec, LaunchCtx* ctx);
 // NVLS in place on registered buffers of the wire type (kernels/nvls_kernel.cu); false = not applicable
 bool cuda_launch_nvls_registered(int dtype, int op, LaunchCtx* ctx);
+// P2P stages with a thread-block cluster of two CTAs per tile (kernels/cluster_kernel.cu); false = not applicable
+bool cuda_launch_cluster(int dtype, int io_dtype, int op, bool vec, LaunchCtx* ctx);
 // true when the switch can reduce this (dtype, op) (multimem.ld_reduce): fp32/bf16/fp16 SUM
 bool nvls_supported(int dtype, int op);
 

@@ -45,7 +45,7 @@ int legacy_choose(const std::vector<Widths>& trees, int total_nodes, double chun
 // ---------------------------------------------------------------------------------------------
 enum Algo { ALGO_AUTO = 0, ALGO_ONESHOT = 1, ALGO_STAGED = 2, ALGO_NVLS = 3, ALGO_RING = 4 };
 // internal kernel selector (not a user-visible algorithm): the P2P stages with TMA-staged tiles
-enum { ALGO_STAGED_TMA = 5, ALGO_TWOSHOT = 6 };  // 6: two-shot LL (user-visible as FT_ALGO_TWOSHOT / "twoshot")
+enum { ALGO_STAGED_TMA = 5, ALGO_TWOSHOT = 6, ALGO_STAGED_CLUSTER = 7 };  // 7: TMA stages, two-CTA cluster per tile (internal)  // 6: two-shot LL (user-visible as FT_ALGO_TWOSHOT / "twoshot")
 const char* algo_name(int a);
 int algo_from_name(const std::string& s);  // -1 if unknown
 

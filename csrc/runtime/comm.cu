@@ -127,6 +127,7 @@ struct ft_comm {
   unsigned* h_err = nullptr;       // [nlocal] mapped pinned host mirror of d_err (written by the kernel that sets d_err)
   long long nvls_max_tile = 0;  // registered NVLS: tile cap (0: env FT_NVLS_MAX_TILE_BYTES / 4 MiB)
   int nvls_ctas = 0;            // registered NVLS: CTAs for large messages (0: 8)
+  int cluster = -1;             // P2P stages with a two-CTA cluster per tile: -1 env FT_CLUSTER / off, 0 off, 1 on
   int nvls_variant = -1, nvls_flags = 0;  // ft_comm_set_tuning; -1: env FT_NVLS_VARIANT / default
   int fault_rank = -1;             // ft_comm_inject_fault: this rank plays dead in the next calls (-1 = off)
 
@@ -333,7 +334,7 @@ struct Shape {
 // system fence + a flag hop, so tiles should be as large as the message allows (512 KiB per block-chunk
 // was the sweet spot; 2 MiB starves the grid). Every rank must derive the same shape from the same
 // arguments.
-Shape pick_shape(const ft_comm* c, int algo, int mode, bool tma, size_t msg_bytes, int nranks, int esize) {
+Shape pick_shape(const ft_comm* c, int algo, int mode, bool tma, size_t msg_bytes, int nranks, int esize, bool cluster = false) {
   Shape s;
   s.threads = c->threads_override ? c->threads_override : env_int("FT_THREADS", 512);
   if (s.threads > FT_MAX_THREADS) s.threads = FT_MAX_THREADS;
@@ -343,10 +344,12 @@ Shape pick_shape(const ft_comm* c, int algo, int mode, bool tma, size_t msg_byte
   const int cap = c->max_ctas > 0 ? c->max_ctas : env_int("FT_MAX_CTAS", 0);
   if (cap > 0 && cap < max_ctas) max_ctas = cap;
   if (max_ctas > FT_MAX_CTAS) max_ctas = FT_MAX_CTAS;
+  if (cluster) max_ctas /= 2;  // a "CTA" of the plan is a cluster of two
   if (c->kind == COMM_EMULATED) {
     // cooperative launch: nranks*ctas CTAs must be co-resident
     int per_sm = (s.threads <= 256 && !tma) ? 2 : 1;  // the TMA ring takes the whole shared memory of an SM
     max_ctas = c->sm_count * per_sm / nranks;
+    if (cluster) max_ctas /= 2;
     if (max_ctas < 1) max_ctas = 1;
   }
   const long long block_bytes = ((long long)msg_bytes + nranks - 1) / nranks;
@@ -433,6 +436,10 @@ Shape pick_shape(const ft_comm* c, int algo, int mode, bool tma, size_t msg_byte
 
 // NVLS in place on registered buffers of the wire type has a kernel of its own (kernels/nvls_kernel.cu).
 bool launch_any(int wire_dtype, int io_dtype, int op, bool vec, int mode, LaunchCtx* ctx) {
+  if (ctx->algo == ALGO_STAGED_CLUSTER) {
+    if (cuda_launch_cluster(wire_dtype, io_dtype, op, vec, ctx)) return true;
+    ctx->algo = ALGO_STAGED_TMA;  // not available for this type / shape: the one-CTA TMA kernel
+  }
   if (ctx->algo == ALGO_NVLS && mode == MODE_REGISTERED && wire_dtype == io_dtype && vec) {
     ctx->err = cudaSuccess;
     if (cuda_launch_nvls_registered(wire_dtype, op, ctx)) return true;
@@ -673,7 +680,9 @@ ft_result_t do_allreduce(ft_comm* c, const void* const* send, void* const* recv,
                    (c->threads_override == 0 || c->threads_override >= 64) &&
                    (c->tma_override >= 0 ? c->tma_override : env_int("FT_TMA", 1)) != 0;
   const int T = N - lonely;  // ranks in the tree = number of blocks
-  Shape sh = pick_shape(c, algo, mode, tma, msg_bytes, T, es);
+  const bool cluster = tma && want_threads == FT_MAX_THREADS && phases == PHASES_ALLREDUCE &&
+                       (c->cluster >= 0 ? c->cluster : env_int("FT_CLUSTER", 0)) != 0 && dtype_is_float(wire_dtype) && es <= 4;
+  Shape sh = pick_shape(c, algo, mode, tma, msg_bytes, T, es, cluster);
   a.lay = make_layout((long long)count, T, es, sh.tile_bytes, vec);
   a.lonely = lonely;
   a.phases = phases;
@@ -778,7 +787,7 @@ ft_result_t do_allreduce(ft_comm* c, const void* const* send, void* const* recv,
 
   LaunchCtx ctx;
   ctx.args = &a;
-  ctx.algo = tma ? (int)ALGO_STAGED_TMA : algo;
+  ctx.algo = tma ? (cluster ? (int)ALGO_STAGED_CLUSTER : (int)ALGO_STAGED_TMA) : algo;
   ctx.threads = sh.threads;
   ctx.cooperative = c->kind == COMM_EMULATED && N > 1;
   ctx.stream = stream;
@@ -1037,6 +1046,7 @@ ft_result_t ft_comm_set_tuning(ft_comm_t* c, const char* key, long long value) {
   if (k == "nvls_flags") { c->nvls_flags = (int)value; return FT_SUCCESS; }
   if (k == "nvls_max_tile_bytes") { c->nvls_max_tile = value; return FT_SUCCESS; }
   if (k == "nvls_ctas") { c->nvls_ctas = (int)value; return FT_SUCCESS; }
+  if (k == "cluster") { c->cluster = (int)value; return FT_SUCCESS; }
   set_last_error("ft_comm_set_tuning: unknown key " + k);
   return FT_ERR_INVALID;
 }

@@ -612,3 +612,48 @@ def test_nvls_registered_graph_replay_emulated(comms):
     assert c.error() == 0
     c.set_launch(0, 0, 0)
     c.set_algo("auto")
+
+
+@pytest.mark.parametrize("n,widths", [(2, [2]), (4, [4]), (4, [2, 2]), (8, [8]), (8, [2, 4]), (6, [3, 2])])
+def test_cluster_pair_per_tile_matches_reference(comms, n, widths):
+    """Thread-block clusters: a pair of CTAs owns a tile, splits the stage's sources and combines the partial sums
+    through distributed shared memory (kernels/cluster_tiles.cuh). Same values as the one-CTA kernels up to the fp32
+    rounding of a different (but fixed) summation order; integers-in-float inputs must match exactly."""
+    c = comms(n)
+    c.set_algo("stages")
+    c.set_widths(widths)
+    c.set_tma(True)
+    c.set_tuning("cluster", 1)
+    try:
+        g = torch.Generator(device="cuda").manual_seed(3)
+        for count in (4096, 300000, (1 << 20) + 8):
+            xs = [torch.randint(-50, 50, (count,), device="cuda", generator=g).float() for _ in range(n)]
+            want = torch.stack(xs).sum(0)
+            outs = [torch.empty_like(x) for x in xs]
+            c.allreduce_multi(xs, outs=outs)             # private buffers, out of place
+            torch.cuda.synchronize()
+            assert c.error() == 0, hex(c.error())
+            for r in range(n):
+                assert torch.equal(outs[r], want), (widths, count, r)
+            sym = c.symm_empty(count, torch.float32)     # registered, in place, random data, fused scale
+            ys = [torch.randn(count, device="cuda", generator=g) for _ in range(n)]
+            for s_, y in zip(sym, ys):
+                s_.copy_(y)
+            c.allreduce_multi(sym, scale=0.5)
+            torch.cuda.synchronize()
+            assert c.error() == 0 and c.last_call()["mode"] == "registered"
+            ref = torch.stack(ys).double().sum(0) * 0.5
+            for r in range(n):
+                assert torch.allclose(sym[r].double(), ref, rtol=1e-5, atol=1e-5)
+                assert torch.equal(sym[r], sym[0])
+        zs = [torch.randn(65536, device="cuda", generator=g).bfloat16() for _ in range(n)]   # bf16 wire
+        ref = torch.stack([z.double() for z in zs]).sum(0)
+        c.allreduce_multi(zs)
+        torch.cuda.synchronize()
+        assert c.error() == 0
+        assert torch.allclose(zs[0].double(), ref, rtol=5e-2, atol=1e-1) and torch.equal(zs[0], zs[n - 1])  # bf16 is rounded once per stage
+    finally:
+        c.set_tuning("cluster", 0)
+        c.set_tma(None)
+        c.set_widths(None)
+        c.set_algo("auto")
