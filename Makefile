@@ -34,7 +34,7 @@ RT_CC_OBJ := $(RT_CC_SRC:%.cc=$(B)/%.o)
 .PHONY: all host cuda tools clean tsan asan fdtest memcheck racecheck dropin
 all: host cuda tools
 host: $(B)/libflextree_host.so
-cuda: $(LIBDIR)/libflextree.so
+cuda: $(LIBDIR)/libflextree.so $(LIBDIR)/_ftfast.so
 tools: $(B)/ft_plan $(B)/ft_bench $(B)/ftrun
 
 $(B)/%.o: %.cc
@@ -58,6 +58,11 @@ $(B)/libflextree_host.so: $(PLANNER_OBJ) $(HOST_OBJ)
 $(LIBDIR)/libflextree.so: $(PLANNER_OBJ) $(HOST_OBJ) $(RT_CC_OBJ) $(CUDA_OBJ)
 	@mkdir -p $(LIBDIR)
 	$(NVCC) -ccbin /usr/bin/g++ $(ARCH) -shared -o $@ $^ -lpthread -ldl
+
+# the per-call path of the Python API as a CPython extension (csrc/python/ftfast.c); links the CUDA library
+PYINC := $(shell python3 -c "import sysconfig;print(sysconfig.get_paths()['include'])" 2>/dev/null)
+$(LIBDIR)/_ftfast.so: csrc/python/ftfast.c $(LIBDIR)/libflextree.so
+	/usr/bin/gcc -O2 -fPIC -shared -Wall -Iinclude -I$(PYINC) -o $@ $< -L$(LIBDIR) -lflextree -Wl,-rpath,'$$ORIGIN'
 
 $(B)/ft_plan: csrc/tools/ft_plan.cc $(PLANNER_OBJ)
 	$(CXX) $(CXXFLAGS) -o $@ $^

@@ -51,6 +51,32 @@ def load():
     return _lib
 
 
+_fast = None
+_fast_tried = False
+
+
+def fast():
+    """The compiled per-call module (csrc/python/ftfast.c -> lib/_ftfast.so), or None when it is not built."""
+    global _fast, _fast_tried
+    if _fast_tried:
+        return _fast
+    _fast_tried = True
+    load()
+    path = os.path.join(_HERE, "lib", "_ftfast.so")
+    if _has_cuda_lib and os.path.exists(path) and os.environ.get("FT_NO_FASTCALL") != "1":
+        try:
+            import importlib.machinery
+            import importlib.util
+            loader = importlib.machinery.ExtensionFileLoader("_ftfast", path)
+            spec = importlib.util.spec_from_loader("_ftfast", loader)
+            mod = importlib.util.module_from_spec(spec)
+            loader.exec_module(mod)
+            _fast = mod
+        except Exception:  # e.g. built for another Python: the ctypes path still works
+            _fast = None
+    return _fast
+
+
 def has_cuda_lib():
     load()
     return _has_cuda_lib

@@ -19,11 +19,14 @@ import torch.distributed as dist
 from torch.nn.parallel import DistributedDataParallel as DDP
 
 sys.path.insert(0, os.path.dirname(os.path.dirname(os.path.dirname(os.path.abspath(__file__)))))
+import time  # noqa: E402
+
 import flextree as ft  # noqa: E402
 from flextree.models.zoo import build  # noqa: E402
+from flextree.utils.clocks import ClockSampler  # noqa: E402
 
 
-def run(args, backend, comm, dev, rank, world, local):
+def run(args, backend, comm, dev, rank, world, local, sampler=None):
     torch.manual_seed(1234)
     pdtype = torch.bfloat16 if args.param_dtype == "bf16" else torch.float32
     model, make_batch, loss_fn, per_sample = build(args.model, dev, pdtype)
@@ -61,11 +64,13 @@ def run(args, backend, comm, dev, rank, world, local):
     torch.cuda.synchronize()
     dist.barrier()
     ev0, ev1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+    t0 = time.perf_counter()
     ev0.record()
     for _ in range(args.steps):
         losses.append(step().detach())
     ev1.record()
     torch.cuda.synchronize()
+    t1 = time.perf_counter()
     ms = torch.tensor([ev0.elapsed_time(ev1) / args.steps], device=dev, dtype=torch.float64)
     dist.all_reduce(ms, op=dist.ReduceOp.MAX)
     nparam = sum(p.numel() for p in model.parameters())
@@ -73,6 +78,8 @@ def run(args, backend, comm, dev, rank, world, local):
            "ms_per_step": round(ms.item(), 3), "items_per_s": round(args.batch * per_sample * world / (ms.item() / 1e3), 1),
            "params": nparam, "param_dtype": args.param_dtype, "wire": args.wire if backend == "flextree" else "native",
            "final_loss": round(torch.stack(losses)[-3:].float().mean().item(), 5)}
+    if sampler is not None and rank == 0:
+        rec["clocks"] = sampler.window(t0, t1)  # SM clock + throttle reasons sampled during THIS timed loop
     if engine is not None:
         rec["buckets"] = len(engine.buckets)
         rec["device_error"] = comm.error()
@@ -106,9 +113,12 @@ def main():
     torch.backends.cudnn.benchmark = True
     comm = ft.init() if args.comm != "nccl" else None
     results, params = [], {}
+    sampler = ClockSampler(local)
+    if rank == 0:
+        sampler.start()
     order = {"both": ["nccl", "flextree"], "all": ["nccl", "flextree", "flextree-dp"]}.get(args.comm, [args.comm])
     for backend in order:
-        rec, flat = run(args, backend, comm, dev, rank, world, local)
+        rec, flat = run(args, backend, comm, dev, rank, world, local, sampler)
         results.append(rec)
         params[backend] = flat
         torch.cuda.empty_cache()

@@ -61,6 +61,8 @@ class Communicator:
         if not _lib.has_cuda_lib():
             raise FlexTreeError("flextree: the CUDA library (allreduce-over-mpi_b200/lib/libflextree.so) is not built")
         self._h = C.c_void_p()
+        self._fast = _lib.fast()     # compiled per-call path (no ctypes), None if not built
+        self._raw_stream = getattr(torch._C, "_cuda_getCurrentRawStream", None)
         self._cb = None
         self.emulated_ranks = 0
         self.device = None
@@ -148,6 +150,8 @@ class Communicator:
 
     def poll_error(self):
         """The same word without any synchronisation (mapped host mirror written by the failing kernel)."""
+        if self._fast is not None and self._h.value:
+            return self._fast.error_peek(self._h.value)
         return int(self._L.ft_comm_error_peek(self._h))
 
     def raise_if_failed(self):
@@ -283,8 +287,19 @@ class Communicator:
         # (the native call selects the communicator's device itself; no torch device context on the hot path)
         if _NVTX:  # FT_NVTX=1: one range per call for nsys / ncu timelines
             torch.cuda.nvtx.range_push(f"flextree.allreduce {tensor.numel() * tensor.element_size()} B")
-        rc = self._L.ft_allreduce_ex(tensor.data_ptr(), out.data_ptr(), tensor.numel(),
-                                     dt, wt, opc, float(scale), self._h, self._stream(stream))
+        if self._fast is not None:
+            # one vectorcall into the compiled module: plain integers in, result code out
+            if stream is not None:
+                sp = stream.cuda_stream
+            elif self._raw_stream is not None:
+                sp = self._raw_stream(self.device.index)
+            else:
+                sp = torch.cuda.current_stream(self.device).cuda_stream
+            rc = self._fast.allreduce_ex(self._h.value, tensor.data_ptr(), out.data_ptr(), tensor.numel(), dt, wt, opc,
+                                         float(scale), sp)
+        else:
+            rc = self._L.ft_allreduce_ex(tensor.data_ptr(), out.data_ptr(), tensor.numel(),
+                                         dt, wt, opc, float(scale), self._h, self._stream(stream))
         if _NVTX:
             torch.cuda.nvtx.range_pop()
         if rc:
