@@ -127,6 +127,11 @@ struct ft_comm {
   unsigned* h_err = nullptr;       // [nlocal] mapped pinned host mirror of d_err (written by the kernel that sets d_err)
   long long nvls_max_tile = 0;  // registered NVLS: tile cap (0: env FT_NVLS_MAX_TILE_BYTES / 4 MiB)
   int nvls_ctas = 0;            // registered NVLS: CTAs for large messages (0: 8)
+  // "-k" trees (cost_model/ChooseWidth.h:14-31 lists the trees of N+1 as candidates for N ranks): a tree with k more
+  // positions than there are GPUs; phantom j (logical rank N+j) is hosted by process j, see the phantom section below
+  struct PhantomWorld;
+  PhantomWorld* ph = nullptr;
+  int phantom_override = 0;     // widths_override multiplies to nranks + phantom_override
   int cluster = -1;             // P2P stages with a two-CTA cluster per tile: -1 env FT_CLUSTER / off, 0 off, 1 on
   int nvls_variant = -1, nvls_flags = 0;  // ft_comm_set_tuning; -1: env FT_NVLS_VARIANT / default
   int fault_rank = -1;             // ft_comm_inject_fault: this rank plays dead in the next calls (-1 = off)
@@ -467,6 +472,10 @@ ft_result_t check_device_error(ft_comm* c) {
   return FT_SUCCESS;
 }
 
+ft_result_t phantom_allreduce(ft_comm* c, const void* send, void* recv, size_t count, int io_dtype, int wire_dtype, int op,
+                              double scale, cudaStream_t stream, const std::vector<int>& widths, int k, bool vec);
+void phantom_release(ft_comm* c);
+
 // The one place a collective is resolved and launched. send/recv: per logical rank.
 ft_result_t do_allreduce(ft_comm* c, const void* const* send, void* const* recv, size_t count, int io_dtype,
                          int wire_dtype, int op, double scale, cudaStream_t stream, int phases = PHASES_ALLREDUCE) {
@@ -593,20 +602,35 @@ ft_result_t do_allreduce(ft_comm* c, const void* const* send, void* const* recv,
   int algo = c->algo_override;
   std::vector<int> widths = c->widths_override;
   int lonely = widths.empty() ? 0 : c->lonely_override;
+  int phantoms = widths.empty() ? 0 : c->phantom_override;
   if (widths.empty() && getenv("FT_TOPO") && *getenv("FT_TOPO")) {
     // "2,3+1": a tree of 6 plus one lonely rank (extension; the reference's parser has no lonely syntax)
     std::string topo = getenv("FT_TOPO");
-    size_t plus = topo.find('+');
+    size_t plus = topo.find('+'), minus = topo.find('-');
     int extra = 0;
     if (plus != std::string::npos) {
       extra = atoi(topo.c_str() + plus + 1);
       topo = topo.substr(0, plus);
+    } else if (minus != std::string::npos) {  // "2,4-1": a tree of 8 positions for 7 ranks (the reference prints 2*4-1)
+      extra = -atoi(topo.c_str() + minus + 1);
+      topo = topo.substr(0, minus);
     }
     int buf[FT_MAX_STAGES + 8];
     int k = ft_parse_topo(topo.c_str(), N - extra, buf, FT_MAX_STAGES + 8);
-    if (k < 0 || extra < 0) return FT_ERR_INVALID;  // product mismatch: the reference exits (mpi_mod.hpp:914-918)
+    if (k < 0) return FT_ERR_INVALID;  // product mismatch: the reference exits (mpi_mod.hpp:914-918)
     widths.assign(buf, buf + k);
+    if (extra < 0) {
+      phantoms = (k == 1 && buf[0] == 1) ? 0 : -extra;
+      extra = 0;
+    }
     lonely = (k == 1 && buf[0] == 1) ? 0 : extra;
+  }
+  if (phantoms > 0) {
+    if (phases != PHASES_ALLREDUCE || c->kind != COMM_PROCESS || phantoms > N) {
+      set_last_error("'-k' trees: allreduce on a one-process-per-GPU communicator, k <= world size");
+      return FT_ERR_UNSUPPORTED;
+    }
+    return phantom_allreduce(c, s[0], r[0], count, io_dtype, wire_dtype, op, scale, stream, widths, phantoms, vec);
   }
   if (!widths.empty() && widths[0] == 1 && N > 1) {  // "any 1 means ring" (mpi_mod.hpp:907-910)
     algo = ALGO_RING;
@@ -836,6 +860,243 @@ ft_result_t do_allreduce(ft_comm* c, const void* const* send, void* const* recv,
   return FT_SUCCESS;
 }
 
+// ---- "-k" trees: phantom ranks -------------------------------------------------------------------------------------
+// Capability parity: chooseWidth lists the trees of N+1 nodes, tagged "-1", as candidates for N nodes
+// (cost_model/ChooseWidth.h:14-31; worked cases cost_model/README.md:13-27: 2*2*2-1, 2*4-1, 4*2-1 for 7 nodes) and the
+// reference's data plane carries the hooks for it (mpi_mod.hpp:172-178, :208-211, :981-987, :1041-1099) without a
+// working implementation. Here: a tree of T = N + k positions runs on N GPUs; position N+j is a PHANTOM rank hosted by
+// process j. A phantom is a complete logical rank - own flag pad, own window slot, own epoch - whose input is the
+// operation's identity and whose output goes to a sink buffer; its host launches TWO logical ranks in one cooperative
+// launch (rc[0] = itself, rc[1] = the phantom), exactly like the CPU communicator does (csrc/host/host_comm.cc).
+// This is how 7 (or 5, or 3) GPUs get a multi-stage tree with no fold step; the price is that the hosts do double duty.
+// P2P stages on private buffers only (the multicast mapping covers slot 0 of every segment, not the phantom slots).
+}  // namespace
+
+struct ft_comm::PhantomWorld {
+  int k = 0;
+  size_t window_bytes = 0;         // per parity, per slot
+  Segment pad, win;                // 2 slots per process: [0] the process itself, [1] its phantom
+  char** d_win_table = nullptr;    // [T] window base of every logical rank
+  CommDev* d_comm = nullptr;       // [2]
+  uint64_t* d_epoch = nullptr;     // [2]
+  unsigned* d_done = nullptr;      // [2]
+  char* ident = nullptr;           // identity input of the hosted phantom
+  char* sink = nullptr;            // its discarded output
+  size_t io_bytes = 0;
+  int ident_dtype = -1, ident_op = -1;
+  size_t ident_count = 0;
+};
+
+namespace {
+
+__global__ void fill_pattern_kernel(char* p, size_t n, int es, unsigned long long pat) {
+  for (size_t i = (size_t)blockIdx.x * blockDim.x + threadIdx.x; i < n; i += (size_t)gridDim.x * blockDim.x) {
+    for (int b = 0; b < es; ++b) p[i * (size_t)es + b] = (char)((pat >> (8 * b)) & 0xff);
+  }
+}
+
+// Bit pattern of the identity element of `op` for one element of `dtype`.
+unsigned long long identity_pattern(int dtype, int op) {
+  const int es = dtype_size(dtype);
+  const unsigned long long ones = es >= 8 ? ~0ull : ((1ull << (8 * es)) - 1ull);
+  if (op == OP_SUM || op == OP_BOR) return 0;
+  if (dtype == DT_BOOL) return (op == OP_BAND || op == OP_MIN) ? 1 : 0;
+  if (op == OP_BAND) return ones;
+  const bool is_max = op == OP_MAX;
+  switch (dtype) {
+    case DT_FLOAT: return is_max ? 0xff800000ull : 0x7f800000ull;            // -inf / +inf
+    case DT_DOUBLE: return is_max ? 0xfff0000000000000ull : 0x7ff0000000000000ull;
+    case DT_HALF: return is_max ? 0xfc00ull : 0x7c00ull;
+    case DT_BFLOAT16: return is_max ? 0xff80ull : 0x7f80ull;
+    case DT_INT8: case DT_INT16: case DT_INT32: case DT_INT64: case DT_LONG_LONG:
+      return is_max ? (1ull << (8 * es - 1)) : (ones >> 1);                  // most negative / most positive
+    default: return is_max ? 0 : ones;                                       // unsigned
+  }
+}
+
+void phantom_free(ft_comm::PhantomWorld* w) {
+  if (!w) return;
+  segment_destroy(&w->pad);
+  segment_destroy(&w->win);
+  if (w->d_win_table) cudaFree(w->d_win_table);
+  if (w->d_comm) cudaFree(w->d_comm);
+  if (w->d_epoch) cudaFree(w->d_epoch);
+  if (w->d_done) cudaFree(w->d_done);
+  if (w->ident) cudaFree(w->ident);
+  if (w->sink) cudaFree(w->sink);
+  (void)cudaGetLastError();
+  delete w;
+}
+
+void phantom_release(ft_comm* c) {
+  phantom_free(c->ph);
+  c->ph = nullptr;
+}
+
+// (Re)build the phantom world for k phantoms and a window of at least `need` bytes per parity. Collective: every
+// process reaches it with the same arguments (they derive from the call's arguments).
+ft_result_t phantom_build(ft_comm* c, int k, size_t need) {
+  const int N = c->nranks, T = N + k;
+  size_t wb = c->ph && c->ph->k == k ? c->ph->window_bytes : (size_t)(16u << 20);
+  while (wb < need) wb *= 2;
+  FT_CHECK_RT(cudaSetDevice(c->device));
+  FT_CHECK_RT(cudaDeviceSynchronize());
+  if (!c->bs.barrier()) { set_last_error("bootstrap barrier failed"); return FT_ERR_INTERNAL; }
+  phantom_release(c);
+  auto* w = new ft_comm::PhantomWorld;
+  w->k = k;
+  w->window_bytes = wb;
+  std::string err;
+  SymmOptions nomc = c->sopt;
+  nomc.try_multicast = false;
+  nomc.require_multicast = false;
+  if (!segment_create(c->bs, c->device, 2 * FT_PAD_BYTES, nomc, &w->pad, &err) ||
+      !segment_create(c->bs, c->device, 2 * 2 * wb, nomc, &w->win, &err)) {
+    set_last_error("phantom world: " + err);
+    phantom_free(w);
+    return FT_ERR_CUDA;
+  }
+  // logical rank L lives in slot (L < N ? 0 : 1) of process (L < N ? L : L - N)
+  auto host_of = [&](int L) { return L < N ? L : L - N; };
+  auto slot_of = [&](int L) { return L < N ? 0 : 1; };
+  std::vector<char*> wt((size_t)T);
+  for (int L = 0; L < T; ++L) wt[(size_t)L] = w->win.base[(size_t)host_of(L)] + (size_t)slot_of(L) * 2 * wb;
+  FT_CHECK_RT(cudaMalloc(&w->d_win_table, sizeof(char*) * (size_t)T));
+  FT_CHECK_RT(cudaMemcpy(w->d_win_table, wt.data(), sizeof(char*) * (size_t)T, cudaMemcpyHostToDevice));
+  FT_CHECK_RT(cudaMalloc(&w->d_comm, sizeof(CommDev) * 2));
+  FT_CHECK_RT(cudaMalloc(&w->d_epoch, sizeof(uint64_t) * 2));
+  FT_CHECK_RT(cudaMalloc(&w->d_done, sizeof(unsigned) * 2));
+  FT_CHECK_RT(cudaMemset(w->d_epoch, 0, sizeof(uint64_t) * 2));
+  FT_CHECK_RT(cudaMemset(w->d_done, 0, sizeof(unsigned) * 2));
+  CommDev h[2];
+  for (int l = 0; l < 2; ++l) {
+    CommDev& d = h[l];
+    memset(&d, 0, sizeof d);
+    d.rank = l == 0 ? c->rank : N + c->rank;
+    d.nranks = T;
+    for (int L = 0; L < T; ++L) d.pad[L] = (uint64_t*)(w->pad.base[(size_t)host_of(L)] + (size_t)slot_of(L) * FT_PAD_BYTES);
+    d.epoch = w->d_epoch + l;
+    d.done = w->d_done + l;
+    d.err = c->d_err;  // one error word (and its host mirror) per process: a phantom's timeout is its host's
+    d.err_host = nullptr;
+  }
+  {  // reuse the communicator's host mirror for the real rank
+    CommDev real;
+    if (cudaMemcpy(&real, c->d_comm, sizeof real, cudaMemcpyDeviceToHost) == cudaSuccess) h[0].err_host = h[1].err_host = real.err_host;
+    (void)cudaGetLastError();
+  }
+  FT_CHECK_RT(cudaMemcpy(w->d_comm, h, sizeof h, cudaMemcpyHostToDevice));
+  c->ph = w;
+  FT_LOG(1, "rank %d: phantom world for %d+%d positions, window %zu bytes per parity", c->rank, N, k, wb);
+  return c->bs.barrier() ? FT_SUCCESS : FT_ERR_INTERNAL;
+}
+
+ft_result_t phantom_allreduce(ft_comm* c, const void* send, void* recv, size_t count, int io_dtype, int wire_dtype, int op,
+                              double scale, cudaStream_t stream, const std::vector<int>& widths, int k, bool vec) {
+  const int N = c->nranks, T = N + k;
+  if (wire_dtype == DT_FP8_BLOCK) { set_last_error("'-k' trees: no fp8 wire"); return FT_ERR_UNSUPPORTED; }
+  StagedArgs a;
+  memset(&a, 0, sizeof a);
+  if (!make_plan(widths.data(), (int)widths.size(), &a.plan) || a.plan.nranks != T) {
+    set_last_error("stage widths " + to_string(widths) + " do not multiply to " + std::to_string(T));
+    return FT_ERR_INVALID;
+  }
+  cudaStreamCaptureStatus cap = cudaStreamCaptureStatusNone;
+  cudaStreamIsCapturing(stream, &cap);
+  const int es = dtype_size(wire_dtype), ios = dtype_size(io_dtype);
+  const size_t msg_bytes = count * (size_t)es;
+  const bool hosting = c->rank < k;
+  const int want_threads = c->threads_override ? c->threads_override : env_int("FT_THREADS", 512);
+  const bool tma = vec && want_threads >= 64 && (count % (size_t)(16 / es) == 0) &&
+                   (c->tma_override >= 0 ? c->tma_override : env_int("FT_TMA", 1)) != 0;
+  // hosts run two logical ranks in one cooperative launch: every rank plans with half the CTA budget (the tile -> CTA
+  // mapping must be the same everywhere)
+  Shape sh = pick_shape(c, ALGO_STAGED, MODE_STAGING, tma, msg_bytes, T, es, /*halve the CTA budget=*/true);
+  a.lay = make_layout((long long)count, T, es, sh.tile_bytes, vec);
+  {
+    long long per_cta = (a.lay.ntiles + sh.ctas - 1) / sh.ctas;
+    while (per_cta >= (1LL << FT_EPOCH_SHIFT) - 2) {
+      sh.tile_bytes *= 2;
+      a.lay = make_layout((long long)count, T, es, sh.tile_bytes, vec);
+      per_cta = (a.lay.ntiles + sh.ctas - 1) / sh.ctas;
+    }
+  }
+  if (sh.ctas > a.lay.ntiles) sh.ctas = a.lay.ntiles;
+  const size_t need = (size_t)a.lay.block * (size_t)T * (size_t)es;
+  if (!c->ph || c->ph->k != k || c->ph->window_bytes < need) {
+    if (cap != cudaStreamCaptureStatusNone) { set_last_error("'-k' tree: first use / window growth during stream capture"); return FT_ERR_INVALID; }
+    ft_result_t r = phantom_build(c, k, need);
+    if (r != FT_SUCCESS) return r;
+  }
+  ft_comm::PhantomWorld* w = c->ph;
+  if (hosting) {
+    const size_t iob = count * (size_t)ios + 64;
+    if (w->io_bytes < iob) {
+      if (cap != cudaStreamCaptureStatusNone) { set_last_error("'-k' tree: buffer growth during stream capture"); return FT_ERR_INVALID; }
+      FT_CHECK_RT(cudaDeviceSynchronize());
+      if (w->ident) cudaFree(w->ident);
+      if (w->sink) cudaFree(w->sink);
+      w->ident = w->sink = nullptr;
+      FT_CHECK_RT(cudaMalloc(&w->ident, iob));
+      FT_CHECK_RT(cudaMalloc(&w->sink, iob));
+      w->io_bytes = iob;
+      w->ident_dtype = -1;
+    }
+    if (w->ident_dtype != io_dtype || w->ident_op != op || w->ident_count < count) {
+      fill_pattern_kernel<<<256, 256, 0, stream>>>(w->ident, count, ios, identity_pattern(io_dtype, op));
+      FT_CHECK_RT(cudaGetLastError());
+      w->ident_dtype = io_dtype;
+      w->ident_op = op;
+      w->ident_count = count;
+    }
+  }
+  const bool apply_scale = dtype_is_float(wire_dtype) && scale != 1.0;
+  a.nlocal = hosting ? 2 : 1;
+  a.ctas = sh.ctas;
+  a.mode = MODE_STAGING;
+  a.apply_scale = apply_scale ? 1 : 0;
+  a.scale = scale;
+  a.timeout_ns = c->timeout_ns;
+  a.win_off0 = 0;
+  a.win_stride = (long long)w->window_bytes;
+  a.use_tma = tma ? 1 : 0;
+  a.fault_rank_plus1 = c->fault_rank + 1;
+  for (int l = 0; l < a.nlocal; ++l) {
+    RankCall& rc = a.rc[l];
+    rc.comm = w->d_comm + l;
+    rc.send = l == 0 ? send : (const void*)w->ident;
+    rc.recv = l == 0 ? recv : (void*)w->sink;
+    rc.win = w->d_win_table;
+    rc.mc = nullptr;
+  }
+  LaunchCtx ctx;
+  ctx.args = &a;
+  ctx.algo = tma ? (int)ALGO_STAGED_TMA : (int)ALGO_STAGED;
+  ctx.threads = sh.threads;
+  ctx.cooperative = a.nlocal > 1;
+  ctx.stream = stream;
+  if (!cuda_launch(wire_dtype, io_dtype, op, vec, &ctx) || !ctx.supported) {
+    set_last_error("'-k' tree: no kernel for this dtype/op");
+    return FT_ERR_UNSUPPORTED;
+  }
+  if (ctx.err != cudaSuccess) {
+    set_last_error(std::string("kernel launch: ") + cudaGetErrorString(ctx.err));
+    (void)cudaGetLastError();
+    return FT_ERR_CUDA;
+  }
+  ft_call_info_t& li = c->last;
+  li = ft_call_info_t{};
+  li.algo = ALGO_STAGED;
+  li.nstages = a.plan.nstages;
+  for (int i = 0; i < a.plan.nstages && i < 8; ++i) li.widths[i] = a.plan.width[i];
+  li.ctas = sh.ctas;
+  li.threads = sh.threads;
+  li.tile_bytes = a.lay.tile * es;
+  li.mode = MODE_STAGING;
+  li.vectorized = vec;
+  return FT_SUCCESS;
+}
+
 ft_result_t finish_create(ft_comm* c) {
   // pads + LL buffers exist now; window is allocated lazily at first use (or ft_comm_reserve)
   return upload_comm_dev(c);
@@ -983,6 +1244,7 @@ ft_result_t ft_comm_destroy(ft_comm_t* c) {
   cudaSetDevice(c->device);
   cudaDeviceSynchronize();
   host_pipe_release(c);
+  phantom_release(c);
   if (c->kind == COMM_PROCESS) c->bs.barrier();
   destroy_segments(&c->win);
   destroy_segments(&c->pad);
@@ -1080,6 +1342,7 @@ ft_result_t ft_comm_set_widths(ft_comm_t* c, const int* widths, int nstages) {
   if (!widths || nstages <= 0) {
     c->widths_override.clear();
     c->lonely_override = 0;
+    c->phantom_override = 0;
     return FT_SUCCESS;
   }
   std::vector<int> w(widths, widths + nstages);
@@ -1091,10 +1354,24 @@ ft_result_t ft_comm_set_widths(ft_comm_t* c, const int* widths, int nstages) {
     return FT_SUCCESS;
   }
   Plan p;
-  if (!make_plan(w.data(), nstages, &p) || p.nranks > c->nranks) {
+  if (!make_plan(w.data(), nstages, &p)) {
     set_last_error("invalid widths " + to_string(w) + " for world size " + std::to_string(c->nranks));
     return FT_ERR_INVALID;
   }
+  if (p.nranks > c->nranks) {
+    // A tree LARGER than the world: the reference's "-k" trees (2*4-1 for 7 nodes, cost_model/README.md:13-27). The k
+    // extra positions are phantom ranks hosted by the first k processes (one process per GPU only).
+    if (c->kind != COMM_PROCESS || p.nranks > 2 * c->nranks || p.nranks > FT_MAX_RANKS) {
+      set_last_error("widths " + to_string(w) + " multiply to more than the world size " + std::to_string(c->nranks) +
+                     ": '-k' trees need a one-process-per-GPU communicator and k <= world size");
+      return FT_ERR_INVALID;
+    }
+    c->widths_override = w;
+    c->lonely_override = 0;
+    c->phantom_override = p.nranks - c->nranks;
+    return FT_SUCCESS;
+  }
+  c->phantom_override = 0;
   // A tree smaller than the world leaves N - T "lonely" ranks (the reference's "+k" trees,
   // cost_model/ChooseWidth.h:16-31): they feed their vector to the tree and gather the result from it.
   c->widths_override = w;

@@ -158,6 +158,7 @@ int main(int argc, char** argv) {
   std::vector<float*> data(L);
   std::vector<cudaStream_t> streams(L);
   std::vector<cudaEvent_t> e0(L), e1(L);
+  std::vector<float*> align_buf(L, nullptr);  // 1 KiB scratch per rank for the device-side start alignment, see timed()
   std::vector<float> host(max_len);
   for (long long i = 0; i < max_len; ++i) host[i] = (float)i;
   for (int r = 0; r < L; ++r) {
@@ -170,6 +171,8 @@ int main(int argc, char** argv) {
       CK(cudaMalloc(&data[r], sizeof(float) * (size_t)max_len));
     }
     CK(cudaMemcpy(data[r], host.data(), sizeof(float) * (size_t)max_len, cudaMemcpyHostToDevice));
+    CK(cudaMalloc(&align_buf[r], 1024));
+    CK(cudaMemset(align_buf[r], 0, 1024));
     CK(cudaStreamCreate(&streams[r]));
     CK(cudaEventCreate(&e0[r]));
     CK(cudaEventCreate(&e1[r]));
@@ -213,9 +216,26 @@ int main(int argc, char** argv) {
       }
     }
   };
+  // A tiny collective on scratch memory right before the timed one: host-side barriers (sockets, or one thread
+  // walking over the devices) leave the ranks' launches tens of microseconds apart, and a rank that launched early
+  // would bill that skew to the collective. The end of the aligning kernel is a device-side common start line.
+  auto align_start = [&]() {
+    if (emulate) return;
+    if (comm_type == "nccl") {
+      nccl.GroupStart();
+      for (int r = 0; r < L; ++r) nccl.AllReduce(align_buf[r], align_buf[r], 256, 7, 0, ncomms[r], streams[r]);
+      nccl.GroupEnd();
+    } else {
+      for (int r = 0; r < L; ++r) {
+        CK(cudaSetDevice(devs[r]));
+        FT(ft_allreduce(FT_IN_PLACE, align_buf[r], 256, FT_FLOAT, FT_SUM, comms[r], streams[r]));
+      }
+    }
+  };
   // device time of one call: max over ranks of (event stop - event start)
   auto timed = [&](long long len) {
     sync_all();
+    align_start();
     const int T = emulate ? 1 : L;
     for (int r = 0; r < T; ++r) { CK(cudaSetDevice(devs[r])); CK(cudaEventRecord(e0[r], streams[r])); }
     one_allreduce(len);

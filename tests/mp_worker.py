@@ -68,6 +68,41 @@ def main():
             check(out, ref, 1e-5, f"lonely tree {tree} count {count}")
         comm.set_widths(None)
 
+    # 1c. phantom ranks: a tree LARGER than the world (the reference's "-k" trees, e.g. 2*4-1 on 7 ranks): every ordered
+    # factorization of world+1 (and of world+2), fp32 SUM in/out of place, int32 MAX (non-zero identity), bf16, odd counts
+    comm.set_algo("stages")
+    for k in (1, 2):
+        if k > world:
+            continue
+        for widths in ft.enumerate_widths(world + k):
+            if max(widths) > 32:
+                continue
+            comm.set_widths(widths)
+            for count in (1, 1001, (1 << 20) + 3):
+                x = torch.randn(count, device=dev, generator=g)
+                ref = exact_sum(x)
+                out = torch.zeros_like(x)
+                comm.allreduce(x, out=out)
+                check(out, ref, 1e-5, f"phantom tree {widths}-{k} count {count} oop")
+                assert comm.last_call()["widths"] == widths
+                y = x.clone()
+                comm.allreduce(y, scale=0.5)
+                check(y, ref * 0.5, 1e-5, f"phantom tree {widths}-{k} count {count} in place, scaled")
+                chk = y.clone()
+                dist.broadcast(chk, 0)
+                assert torch.equal(chk, y), f"ranks differ for phantom tree {widths}"
+            xi = torch.randint(-10**6, -10, (4097,), device=dev, dtype=torch.int32, generator=g)   # all negative: a zero identity would win MAX
+            ri = xi.clone()
+            dist.all_reduce(ri, op=dist.ReduceOp.MAX)
+            comm.allreduce(xi, op="max")
+            torch.cuda.synchronize()
+            assert comm.error() == 0 and torch.equal(xi, ri), f"phantom tree {widths}: int32 MAX"
+            xb = torch.randn(70000, device=dev, generator=g).bfloat16()
+            rb = exact_sum(xb)
+            comm.allreduce(xb)
+            check(xb, rb, 3e-2, f"phantom tree {widths}: bf16")
+    comm.set_widths(None)
+
     # 2. one-shot, ring, (NVLS), auto
     algos = ["oneshot", "ring", "auto"] + (["nvls"] if comm.has_multicast else [])
     for algo in algos:
