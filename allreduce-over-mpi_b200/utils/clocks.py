@@ -96,6 +96,11 @@ class ClockSampler:
         if self._nvml is None:
             return {"sm_mhz": None, "sm_max_mhz": None, "reasons": [], "samples": 0, "window": "pynvml unavailable"}
         snap = list(self.samples)
+        for _ in range(50):  # the poller may not have produced its first sample yet (first row of a run)
+            if snap and snap[-1][0] >= t_end:
+                break
+            time.sleep(0.002)
+            snap = list(self.samples)
         use = [x for x in snap if t_begin <= x[0] <= t_end]
         label = "timed loop"
         if len(use) < 3:
