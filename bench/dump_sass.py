@@ -12,12 +12,21 @@ import subprocess
 
 ROOT = os.path.dirname(os.path.dirname(os.path.abspath(__file__)))
 K = "_ZN2ft19ft_allreduce_kernelI{t}NS_5OpSumELi{ve}ELi{algo}EEEvNS_10StagedArgsE"
+NV = "_ZN2ft14ft_nvls_kernelI{t}NS_5OpSumELi{v}ELb0EEEvNS_10StagedArgsE"
 KERNELS = {
     "f32_sum_oneshot_ll": K.format(t="ff", ve=4, algo=1),
+    "f32_sum_twoshot_ll": K.format(t="ff", ve=4, algo=6),
     "f32_sum_stages_ldg": K.format(t="ff", ve=4, algo=2),
     "f32_sum_stages_tma": K.format(t="ff", ve=4, algo=5),
-    "f32_sum_nvls": K.format(t="ff", ve=4, algo=3),
-    "bf16_sum_nvls": K.format(t="NS_6bf16_tES1_", ve=8, algo=3),
+    "f32_sum_stages_cluster_pair": "_ZN2ft17ft_cluster_kernelIffNS_5OpSumEEEvNS_10StagedArgsE",
+    # NVLS on registered buffers: the dedicated kernel, default variant (streaming 8) and the alternatives that were measured
+    "f32_sum_nvls_registered_stream8": NV.format(t="f", v=0),
+    "f32_sum_nvls_registered_stream16": NV.format(t="f", v=1),
+    "f32_sum_nvls_registered_stream8_pipelined": NV.format(t="f", v=2),
+    "f32_sum_nvls_registered_warp_specialised": NV.format(t="f", v=5),
+    "bf16_sum_nvls_registered_stream8": NV.format(t="NS_6bf16_tE", v=0),
+    # NVLS on private buffers (copy-in / reduce / copy-out roles) lives in the general kernel
+    "f32_sum_nvls_private": K.format(t="ff", ve=4, algo=3),
     "f32_sum_ring": K.format(t="ff", ve=4, algo=4),
     "fp8wire_f32_sum_stages": K.format(t="NS_5fp8_tEf", ve=16, algo=2),
 }
@@ -25,6 +34,7 @@ COLS = [("UBLKCP (TMA bulk copy)", r"\bUBLKCP"), ("SYNCS (mbarrier)", r"\bSYNCS"
         ("LDG.*STRONG.SYS (peer loads/flags)", r"\bLDG\.[A-Z0-9.]*STRONG\.SYS"),
         ("STG.*STRONG.SYS (flags, LL lines, multimem.st)", r"\bSTG\.[A-Z0-9.]*STRONG\.SYS"),
         ("MEMBAR.ALL.SYS", r"\bMEMBAR\.ALL\.SYS"), ("CCTL.IVALL", r"\bCCTL\.IVALL"), ("FENCE.VIEW.ASYNC", r"\bFENCE\.VIEW\.ASYNC"),
+        ("UCGABAR (cluster barrier)", r"\bUCGABAR"), ("F2FP e4m3 (hardware fp8 conversion)", r"\bF2FP\.[A-Z0-9._]*E4M3"),
         ("LDL+STL (local-memory accesses)", r"\b(?:LDL|STL)\b"), ("registers", None), ("stack bytes", "STACK")]
 
 
@@ -80,8 +90,8 @@ def main():
         f.write("\nNo tensor-core mnemonics (UTC*MMA / HMMA) appear: an allreduce has no matrix product; \"Blackwell-native\" "
                 "here is the async-copy (TMA), mbarrier and multimem ISA.\n")
         nz = sum(1 for v in stack.values() if v > 64)
-        f.write(f"\n{len(usage)} kernels in the library (`cuobjdump -res-usage`): at most {max(usage.values())} registers (the 512-thread "
-                f"launch bound), LOCAL:0 everywhere; {len(usage) - nz} keep <= 64 bytes of stack, {nz} keep more (peer-pointer "
+        f.write(f"\n{len(usage)} kernels in the library (`cuobjdump -res-usage`): at most {max(usage.values())} registers (128 is the cap of the 512-thread "
+                f"kernels, the 256-thread NVLS kernels may use 255), LOCAL:0 everywhere; {len(usage) - nz} keep <= 64 bytes of stack, {nz} keep more (peer-pointer "
                 f"tables and, for the 1-byte types at 16 elements per vector, accumulator arrays) - the widest is {max(stack.values())} bytes.\n")
     print(open(os.path.join(out_dir, "README.md")).read())
 

@@ -1114,6 +1114,21 @@ struct StagedCta {
   FT_DEV long long scale_off(long long el) const { return a.scale_plane_off + (el >> 4); }
   FT_DEV static void q_dequant(const PackT& p, uint8_t s, float* acc, bool first) {
     const float sc = fp8_scale_value(s);
+#if defined(__CUDA_ARCH__)
+    static_assert(VE != 16 || sizeof(PackT) == 16, "a block-scaled pack is 16 e4m3 bytes");
+    if constexpr (VE == 16) {  // four words of four e4m3 each, converted in hardware (no byte indexing, no local memory)
+      const uint4 w = *reinterpret_cast<const uint4*>(&p);
+      const uint32_t ws[4] = {w.x, w.y, w.z, w.w};
+#pragma unroll
+      for (int q = 0; q < 4; ++q) {
+        float f[4];
+        e4m3x4_to_float4(ws[q], f);
+#pragma unroll
+        for (int i = 0; i < 4; ++i) acc[4 * q + i] = first ? f[i] * sc : Op::apply(acc[4 * q + i], f[i] * sc);
+      }
+      return;
+    }
+#endif
 #pragma unroll
     for (int i = 0; i < VE; ++i) {
       const float v = e4m3_to_float(reinterpret_cast<const uint8_t*>(&p)[i]) * sc;
@@ -1130,9 +1145,20 @@ struct StagedCta {
     const uint8_t s = fp8_block_scale(amax);
     const float inv = fp8_scale_inverse(s);
     PackT o;
+    *s_out = s;
+#if defined(__CUDA_ARCH__)
+    if constexpr (VE == 16) {
+      uint4 w;
+      w.x = float4_to_e4m3x4(acc[0] * inv, acc[1] * inv, acc[2] * inv, acc[3] * inv);
+      w.y = float4_to_e4m3x4(acc[4] * inv, acc[5] * inv, acc[6] * inv, acc[7] * inv);
+      w.z = float4_to_e4m3x4(acc[8] * inv, acc[9] * inv, acc[10] * inv, acc[11] * inv);
+      w.w = float4_to_e4m3x4(acc[12] * inv, acc[13] * inv, acc[14] * inv, acc[15] * inv);
+      *reinterpret_cast<uint4*>(&o) = w;
+      return o;
+    }
+#endif
 #pragma unroll
     for (int i = 0; i < VE; ++i) reinterpret_cast<uint8_t*>(&o)[i] = float_to_e4m3(acc[i] * inv);
-    *s_out = s;
     return o;
   }
   FT_DEV static void q_load_user(const IO* x, long long el, int nvalid, float* acc) {
@@ -1146,90 +1172,126 @@ struct StagedCta {
     for (int i = 0; i < VE; ++i) o.e[i] = EU::down((typename EU::acc)acc[i]);
     st_user(y, el, o, nvalid);
   }
+  // The three tile functions walk one block at a time with a plain vector index (no per-vector divisions) and issue
+  // every load of a vector - the own contribution, the packs of ALL peers and their scale bytes - before the first
+  // conversion, like rs_tile<UNR, PB> does for the unquantised wire.
   FT_DEV void q_copy_in_tile(int t) {
     const int N = a.plan.nranks, g1 = a.plan.gap[1];
-    const int CV = (int)((a.lay.tile + VE - 1) / VE), total = N * CV;
     char* wr = rc.win[r] + woff;
-    for (int q = be.tid(); q < total; q += be.nthr()) {
-      const int b = q / CV, vi = q - b * CV;
+    for (int b = 0; b < N; ++b) {
       if ((b % g1) == (r % g1)) continue;
       long long start;
-      const int n = tile_valid32(b, t, &start) - vi * VE;
-      if (n <= 0) continue;
-      const long long el = start + vi * VE;
-      float acc[VE];
-      q_load_user((const IO*)rc.send, el, n < VE ? n : VE, acc);
-      uint8_t sc;
-      PackT p = q_quant(acc, &sc);
-      st_win(wr, el, p);
-      BE::template st<1>(wr + scale_off(el), &sc);
+      const int n = tile_valid32(b, t, &start);
+      const int nvec = (n + VE - 1) / VE;
+      for (int v = be.tid(); v < nvec; v += be.nthr()) {
+        const long long el = start + (long long)v * VE;
+        const int nv = n - v * VE < VE ? n - v * VE : VE;
+        float acc[VE];
+        q_load_user((const IO*)rc.send, el, nv, acc);
+        uint8_t sc;
+        PackT p = q_quant(acc, &sc);
+        st_win(wr, el, p);
+        BE::template st<1>(wr + scale_off(el), &sc);
+      }
     }
   }
+  static constexpr int kQPeers = 8;  // peers whose packs are in flight together (7 cover a stage of width 8)
   FT_DEV void q_rs_tile(int k, int t) {
     const Plan& P = a.plan;
     const int w = P.width[k], gn = P.gap[k + 1], nb = P.nranks / gn, rmod = r % gn, npeers = w - 1;
-    const int CV = (int)((a.lay.tile + VE - 1) / VE), total = nb * CV;
     const bool own_from_user = (k == 0) && (a.mode == MODE_STAGING);
     const bool final_stage = (k == P.nstages - 1) && a.lonely == 0;
     char* wr = rc.win[r] + woff;
-    for (int q = be.tid(); q < total; q += be.nthr()) {
-      const int bi = q / CV, vi = q - bi * CV;
-      long long start;
-      const int n = tile_valid32(rmod + bi * gn, t, &start) - vi * VE;
-      if (n <= 0) continue;
-      const long long el = start + vi * VE;
-      float acc[VE];
-      if (own_from_user) {
-        q_load_user((const IO*)rc.send, el, n < VE ? n : VE, acc);
-      } else {
-        uint8_t s0;
-        PackT p0 = ld_win(wr, el, false);
-        BE::template ld<1>(&s0, wr + scale_off(el), false);
-        q_dequant(p0, s0, acc, true);
-      }
-      for (int j = 0; j < npeers; ++j) {
-        const char* pw = rs_peer_ptr(k, j);
-        uint8_t sj;
-        PackT pj = ld_win(pw, el, true);
-        BE::template ld<1>(&sj, pw + scale_off(el), true);
-        q_dequant(pj, sj, acc, false);
-      }
-      if (final_stage && a.apply_scale) {
+    const char* pw[kQPeers];
 #pragma unroll
-        for (int i = 0; i < VE; ++i) acc[i] *= (float)a.scale;
+    for (int j = 0; j < kQPeers; ++j) pw[j] = j < npeers ? rs_peer_ptr(k, j) : nullptr;
+    for (int bi = 0; bi < nb; ++bi) {
+      long long start;
+      const int n = tile_valid32(rmod + bi * gn, t, &start);
+      const int nvec = (n + VE - 1) / VE;
+      for (int v = be.tid(); v < nvec; v += be.nthr()) {
+        const long long el = start + (long long)v * VE;
+        const int nv = n - v * VE < VE ? n - v * VE : VE;
+        // all loads first
+        PackT in[kQPeers];
+        uint8_t sj[kQPeers];
+#pragma unroll
+        for (int j = 0; j < kQPeers; ++j) {
+          if (j < npeers) {
+            in[j] = ld_win(pw[j], el, true);
+            BE::template ld<1>(&sj[j], pw[j] + scale_off(el), true);
+          }
+        }
+        float acc[VE];
+        if (own_from_user) {
+          q_load_user((const IO*)rc.send, el, nv, acc);
+        } else {
+          uint8_t s0;
+          PackT p0 = ld_win(wr, el, false);
+          BE::template ld<1>(&s0, wr + scale_off(el), false);
+          q_dequant(p0, s0, acc, true);
+        }
+#pragma unroll
+        for (int j = 0; j < kQPeers; ++j)
+          if (j < npeers) q_dequant(in[j], sj[j], acc, false);
+        for (int j = kQPeers; j < npeers; ++j) {  // widths beyond 9: one at a time
+          const char* pj = rs_peer_ptr(k, j);
+          uint8_t s1;
+          PackT p1 = ld_win(pj, el, true);
+          BE::template ld<1>(&s1, pj + scale_off(el), true);
+          q_dequant(p1, s1, acc, false);
+        }
+        if (final_stage && a.apply_scale) {
+#pragma unroll
+          for (int i = 0; i < VE; ++i) acc[i] *= (float)a.scale;
+        }
+        uint8_t sc;
+        PackT o = q_quant(acc, &sc);
+        st_win(wr, el, o);
+        BE::template st<1>(wr + scale_off(el), &sc);
       }
-      uint8_t sc;
-      PackT o = q_quant(acc, &sc);
-      st_win(wr, el, o);
-      BE::template st<1>(wr + scale_off(el), &sc);
     }
   }
   FT_DEV void q_ag_tile(int k, int t) {
     const Plan& P = a.plan;
     const int w = P.width[k], g = P.gap[k], gn = P.gap[k + 1], base = stage_base(P, r, k), nb = P.nranks / gn;
-    const int CV = (int)((a.lay.tile + VE - 1) / VE), total = nb * CV * w;
     const bool last = (k == 0);
     char* wr = rc.win[r] + woff;
-    for (int q = be.tid(); q < total; q += be.nthr()) {
-      const int rest = q / CV, vi = q - rest * CV;
-      const int bi = rest / w, s_ = rest - bi * w;
-      const int p = base + s_ * g;
-      if (p == r && !last) continue;
-      long long start;
-      const int n = tile_valid32((p % gn) + bi * gn, t, &start) - vi * VE;
-      if (n <= 0) continue;
-      const long long el = start + vi * VE;
-      const char* pw = rc.win[p] + woff;
-      uint8_t sc;
-      PackT v = ld_win(pw, el, p != r);
-      BE::template ld<1>(&sc, pw + scale_off(el), p != r);
-      if (last) {
-        float acc[VE];
-        q_dequant(v, sc, acc, true);
-        q_store_user((IO*)rc.recv, el, n < VE ? n : VE, acc);
-      } else {
-        st_win(wr, el, v);
-        BE::template st<1>(wr + scale_off(el), &sc);
+    for (int bi = 0; bi < nb; ++bi) {
+      for (int s_ = 0; s_ < w; ++s_) {
+        const int p = base + s_ * g;
+        if (p == r && !last) continue;
+        long long start;
+        const int n = tile_valid32((p % gn) + bi * gn, t, &start);
+        const int nvec = (n + VE - 1) / VE;
+        const char* pw = rc.win[p] + woff;
+        for (int v0 = be.tid(); v0 < nvec; v0 += 2 * be.nthr()) {  // two vectors per thread in flight
+          const int v1 = v0 + be.nthr();
+          const long long e0 = start + (long long)v0 * VE, e1 = start + (long long)v1 * VE;
+          uint8_t s0 = 0, s1 = 0;
+          PackT p0 = ld_win(pw, e0, p != r), p1;
+          BE::template ld<1>(&s0, pw + scale_off(e0), p != r);
+          if (v1 < nvec) {
+            p1 = ld_win(pw, e1, p != r);
+            BE::template ld<1>(&s1, pw + scale_off(e1), p != r);
+          }
+          if (last) {
+            float acc[VE];
+            q_dequant(p0, s0, acc, true);
+            q_store_user((IO*)rc.recv, e0, n - v0 * VE < VE ? n - v0 * VE : VE, acc);
+            if (v1 < nvec) {
+              q_dequant(p1, s1, acc, true);
+              q_store_user((IO*)rc.recv, e1, n - v1 * VE < VE ? n - v1 * VE : VE, acc);
+            }
+          } else {
+            st_win(wr, e0, p0);
+            BE::template st<1>(wr + scale_off(e0), &s0);
+            if (v1 < nvec) {
+              st_win(wr, e1, p1);
+              BE::template st<1>(wr + scale_off(e1), &s1);
+            }
+          }
+        }
       }
     }
   }

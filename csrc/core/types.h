@@ -171,6 +171,28 @@ FT_HD uint8_t fp8_block_scale(float amax) {
 FT_HD float fp8_scale_value(uint8_t s) { return bits_to_float(s == 0 ? 0x00400000u : ((uint32_t)s << 23)); }      // 2^(s-127)
 FT_HD float fp8_scale_inverse(uint8_t s) { return bits_to_float(s >= 254 ? 0x00400000u : ((uint32_t)(254 - s) << 23)); }  // 2^(127-s)
 
+#if defined(__CUDA_ARCH__)
+// Hardware conversions for the GPU side of the fp8 wire (sm_100a: F2FP.SATFINITE.E4M3 / F2FP.F16.E4M3 in SASS). They
+// agree bit for bit with the integer code above, which the CPU back end keeps using (round to nearest even, saturate
+// to +-448, NaN -> 0x7f; e4m3 -> f16 is exact), so CPU model and GPU still produce identical bytes.
+__device__ __forceinline__ void e4m3x4_to_float4(uint32_t w, float* f) {
+  uint32_t h01, h23;
+  asm("cvt.rn.f16x2.e4m3x2 %0, %1;" : "=r"(h01) : "h"((unsigned short)(w & 0xffffu)));
+  asm("cvt.rn.f16x2.e4m3x2 %0, %1;" : "=r"(h23) : "h"((unsigned short)(w >> 16)));
+  const __half2 a = *reinterpret_cast<const __half2*>(&h01), b = *reinterpret_cast<const __half2*>(&h23);
+  f[0] = __low2float(a);
+  f[1] = __high2float(a);
+  f[2] = __low2float(b);
+  f[3] = __high2float(b);
+}
+__device__ __forceinline__ uint32_t float4_to_e4m3x4(float f0, float f1, float f2, float f3) {
+  unsigned short lo, hi;  // cvt packs its FIRST source into the upper byte
+  asm("cvt.rn.satfinite.e4m3x2.f32 %0, %1, %2;" : "=h"(lo) : "f"(f1), "f"(f0));
+  asm("cvt.rn.satfinite.e4m3x2.f32 %0, %1, %2;" : "=h"(hi) : "f"(f3), "f"(f2));
+  return (uint32_t)lo | ((uint32_t)hi << 16);
+}
+#endif
+
 // ---- accumulator traits ---------------------------------------------------------------------------
 template <typename T> struct Elem {  // default: integers and fp32/fp64 accumulate in themselves
   using acc = T;
