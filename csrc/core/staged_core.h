@@ -459,7 +459,7 @@ struct StagedCta {
 
   // Same work without the software pipeline: UNR loads, then UNR stores (general path: private buffers, casts,
   // single-GPU emulation).
-  enum { NVLS_KEEP_END = 4 };
+  enum { NVLS_KEEP_END = 4, NVLS_DEEP_COPY = 8 };
   template <int UNR, bool EMU> FT_DEV void nvls_reduce_tile_simple(int t) {
     long long start;
     const long long n = tile_valid(r, t, &start);
@@ -661,6 +661,8 @@ struct StagedCta {
   FT_DEV void run_nvls_private() {
     const int G = a.ctas, nt = a.lay.ntiles;
     constexpr int CU = (VE == 1) ? 1 : 8;
+    constexpr int CD = (VE == 1) ? 1 : 16;           // deep copies (a.nvls_flags & NVLS_DEEP_COPY): twice the bytes in flight per CTA
+    const bool deep = (a.nvls_flags & NVLS_DEEP_COPY) != 0;
     const int Gr = a.nvls_reducers > 0 && a.nvls_reducers < G ? a.nvls_reducers : 0;
     const int Gc = G - Gr;
     if (Gr == 0) {
@@ -701,14 +703,16 @@ struct StagedCta {
       while (jout < mine) {
         if (jin < mine && jin - jout < kAhead) {
           const int t = cta + jin * Gc;
-          copy_in_all_tile<CU>(t);
+          if (deep) copy_in_all_tile<CD>(t);
+          else copy_in_all_tile<CU>(t);
           be.sync();
           signal_all_tile(PH_IN, t);
           ++jin;
         } else {
           const int t = cta + jout * Gc;
           wait_all_tile(PH_RS0, t);
-          out_tile<CU>(t);
+          if (deep) out_tile<CD>(t);
+          else out_tile<CU>(t);
           ++jout;
         }
       }

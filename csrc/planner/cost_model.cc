@@ -174,7 +174,10 @@ double predict_us(const LinkModel& m, int algo, const Widths& widths, int n, dou
       // three all-to-all flag hops (input ready, reduced, exit) + a constant for the multicast stores in flight
       double t = m.alpha_launch_us + 3.0 * hop(n) + m.alpha_nvls_us;
       // private buffers: copy-in and copy-out roles + two more flag hops per tile
-      if (!registered) t += 4.0 * hop(n) + 4.0 * S / (m.gamma_hbm_GBps * 1e3) * 0.25 + 10.0;
+      // (round-2 fit on 4 and 8 GPUs, 16 - 256 MiB: +21..28 us at 16 MiB, +48..92 us at 64 MiB, +83..127 us at 256 MiB over
+      // the zero-copy kernel - the copy passes run at about half the HBM copy rate and head / tail of the tile pipeline
+      // are not hidden)
+      if (!registered) t += 4.0 * hop(n) + 12.0 + S / (0.5 * m.gamma_hbm_GBps * 1e3);
       // per-GPU link traffic (each direction): every rank's copy of all N blocks goes up to the switch once
       // (S, including the requester's own copy) plus its reduced block broadcast (S/N)  ->  (1 + 1/N) S,
       // against 2 (N-1)/N S for the P2P stages: NVLS loses at N = 2 and wins from N = 4 up.

@@ -391,14 +391,15 @@ Shape pick_shape(const ft_comm* c, int algo, int mode, bool tma, size_t msg_byte
       if ((long long)msg_bytes >= env_ll("FT_NVLS_SPLIT_BYTES", 128ll << 20)) {
         // large: role split - up to 8 CTAs only reduce in the switch, the others copy; tiles small enough that
         // the pipeline fills quickly, large enough that the two fences per tile stay cheap
-        tile = block_bytes / 64;
-        if (tile > (256 << 10)) tile = 256 << 10;
+        tile = block_bytes / env_ll("FT_NVLS_PRIV_TILE_DIV", 64);
+        if (tile > env_ll("FT_NVLS_PRIV_TILE_MAX", 256 << 10)) tile = env_ll("FT_NVLS_PRIV_TILE_MAX", 256 << 10);
         if (tile < (16 << 10)) tile = 16 << 10;
         const long long ntiles = (block_bytes + tile - 1) / tile;
         int gr = (int)(ntiles / 4);
         const int gr_top = env_int("FT_NVLS_REDUCERS", 16);
         gr = gr < 1 ? 1 : (gr > gr_top ? gr_top : gr);
-        int cap2 = max_ctas < 64 ? max_ctas : 64;
+        const int cap_env = env_int("FT_NVLS_PRIV_CTAS", 64);
+        int cap2 = max_ctas < cap_env ? max_ctas : cap_env;
         int gc = (int)(ntiles < (long long)(cap2 - gr) ? ntiles : (long long)(cap2 - gr));
         if (gc < 1) gc = 1;
         ctas = gr + gc;
