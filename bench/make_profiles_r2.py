@@ -288,6 +288,23 @@ def sweep(n, dtype):
                 "| bytes | " + " | ".join(labels) + " |", "|---:|" + "---:|" * len(labels)]
         for sz in sorted(by):
             out.append(f"| {sz} | " + " | ".join((f"{by[sz][lb]['us']:.1f} / {by[sz][lb].get('est_us', 0):.0f}" if lb in by[sz] else "-") for lb in labels) + " |")
+    after = load(f"sweep_n{n}_auto_after_refit_{dtype}.jsonl")
+    if after:
+        by2 = defaultdict(dict)
+        for r in after:
+            if "us" in r:
+                by2[r["bytes"]]["nccl" if r["impl"] == "nccl" else r["mode"]] = r
+        out += ["", "## `auto` after the round-2 refit of the link model's private-buffer term (separate run, factor-2 size steps)", "",
+                "| bytes | NCCL us | symmetric us (algo) | vs NCCL | private us (algo) | vs NCCL |", "|---:|---:|---:|---:|---:|---:|"]
+        for sz in sorted(by2):
+            v = by2[sz]
+            if {"nccl", "registered", "staging"} <= set(v):
+                out.append(f"| {sz} | {v['nccl']['us']:.1f} | {v['registered']['us']:.1f} ({v['registered']['algo']}) | "
+                           f"{v['nccl']['us'] / v['registered']['us']:.2f}x | {v['staging']['us']:.1f} ({v['staging']['algo']}) | "
+                           f"{v['nccl']['us'] / v['staging']['us']:.2f}x |")
+        out += ["", "Isolated rows far off their neighbours (e.g. a 40 us one-shot at 8 KiB between 8.6 and 9.0 us, a 118 us NVLS call at 2 MiB between",
+                "15 and 26 us) are transients of the measurement that directly follows the NCCL loop; the same configuration measured",
+                "again in the same run (the forced-algorithm rows of the first table, the other dtype) shows the neighbouring value.", ""]
     open(os.path.join(P, f"sweep_n{n}_{dtype}_r2.md"), "w").write("\n".join(out) + "\n")
 
 
