@@ -67,7 +67,7 @@ struct LinkModel {
   double gamma_hbm_GBps = 6000.0; // local HBM copy/reduce traffic rate
   double half_bw_bytes = 4.0e6;   // per-stage bytes at which a P2P stage reaches half its peak rate
   bool has_nvls = false;
-  int max_oneshot_bytes = 4 << 20;  // further limited by the LL buffer of the communicator
+  int max_oneshot_bytes = 2 << 20;  // further limited by the LL buffer; at 4 MiB the two-shot wins even on 2 GPUs (22 vs 29 us)
   // two-shot LL as an automatic candidate up to this size. Measured on 8 GPUs with private buffers (profiles/
   // sweep_n8_staging_mid): 17-25 us from 64 KiB to 2 MiB and 36 us at 4 MiB, where the copy-in NVLS path takes 52-62 us
   // and NCCL 29-87 us; beyond 4 MiB the doubled wire bytes of LL lines lose to NVLS.

@@ -201,6 +201,36 @@ def main():
     assert comm.error() == 0
     comm.set_algo("auto")
 
+    # 6b. capture + 20 replays on real peers for the paths with their own replay hazards: registered NVLS (no exit
+    # barrier, per-tile flags), registered TMA stages (exit barrier), one-shot / two-shot LL (parity halves by epoch)
+    cases = [("oneshot", 2048, False), ("twoshot", 1 << 16, False), ("stages", 1 << 18, True)]
+    if comm.has_multicast:
+        cases += [("nvls", 1 << 20, True), ("nvls", 1 << 18, False)]
+    for algo, cnt, registered in cases:
+        comm.set_algo(algo)
+        if algo == "nvls":
+            comm.set_launch(4, 0, 64 << 10)   # several tiles per CTA
+        buf = comm.symm_empty(cnt, torch.float32) if registered else torch.empty(cnt, device=dev)
+        buf.fill_(1.0)
+        comm.allreduce(buf)
+        torch.cuda.synchronize()
+        assert comm.last_call()["mode"] == ("registered" if registered else "staging"), (algo, comm.last_call())
+        graph = torch.cuda.CUDAGraph()
+        s = torch.cuda.Stream()
+        with torch.cuda.stream(s):
+            graph.capture_begin()
+            comm.allreduce(buf, stream=s)
+            graph.capture_end()
+        for it in range(20):
+            buf.fill_(float(rank + 1 + it))
+            graph.replay()
+            torch.cuda.synchronize()
+            want = float(sum(r + 1 + it for r in range(world)))
+            assert torch.all(buf == want), f"graph replay {algo} registered={registered} it {it}: {buf[:4]} vs {want}"
+        assert comm.error() == 0
+        comm.set_launch(0, 0, 0)
+    comm.set_algo("auto")
+
     # 7. DDP comm hook parity with stock NCCL DDP on a small MLP
     from torch.nn.parallel import DistributedDataParallel as DDP
     torch.manual_seed(0)

@@ -227,3 +227,16 @@ def test_ft_wire_environment_default():
     import pytest
     with pytest.raises(ValueError):
         K.default_wire(K.FLOAT, "sum", {"FT_WIRE": "int4"})
+
+
+def test_compiled_fast_path_module():
+    """csrc/python/ftfast.c: the per-call path of Communicator.allreduce without ctypes. Loads wherever the CUDA
+    library loads (no GPU needed); a null communicator is rejected by the library, bad arguments by the module."""
+    import flextree._lib as L
+    mod = L.fast()
+    if mod is None:
+        pytest.skip("lib/_ftfast.so not built (make cuda)")
+    assert mod.allreduce_ex(0, 0, 0, 16, 6, 6, 0, 1.0, 0) == 1          # FT_ERR_INVALID: no communicator
+    assert mod.error_peek(0) == 0
+    with pytest.raises(TypeError):
+        mod.allreduce_ex(0, 0)
