@@ -353,6 +353,53 @@ def odd_world():
     open(os.path.join(P, "odd_world_n7.md"), "w").write("\n".join(out) + "\n")
 
 
+def cost_model_validation():
+    out = ["# Link model: pick vs measured best (BASELINE config #3), round 2", "",
+           "For every world size and message size: what `auto` (the link model, `csrc/planner/cost_model.cc:choose`) ran on symmetric",
+           "buffers, against the fastest of ALL forced candidates measured in the same run - every ordered factorization of N for the P2P",
+           "stages, ring, one-shot, two-shot, NVLS (`bench/sweep.py --all-widths`). Predicted / measured us for each candidate are in the",
+           "second table of `sweep_n{N}_fp32_r2.md`.", ""]
+    total = good = 0
+    for n in (8, 4, 2):
+        rows = load(f"sweep_n{n}_fp32.jsonl")
+        if not rows:
+            continue
+        by = defaultdict(dict)
+        for r in rows:
+            if "us" not in r or r["impl"] != "flextree" or r.get("mode") != "registered":
+                continue
+            key = "auto" if r["requested"] == "auto" else f"{r['requested']} {'x'.join(map(str, r['widths']))}"
+            by[r["bytes"]][key] = r
+        out += [f"## {n} x B200 (fp32 SUM, symmetric buffers)", "",
+                "| bytes | auto ran | auto us | model est us | fastest candidate | its us | auto / fastest | factorizations of N: us |",
+                "|---:|---|---:|---:|---|---:|---:|---|"]
+        for sz in sorted(by):
+            v = by[sz]
+            if "auto" not in v:
+                continue
+            a = v["auto"]
+            cands = {k: r for k, r in v.items() if k != "auto"}
+            if not cands:
+                continue
+            bk = min(cands, key=lambda k: cands[k]["us"])
+            ratio = a["us"] / cands[bk]["us"]
+            total += 1
+            good += ratio <= 1.10
+            trees = "; ".join(f"{k.split(' ')[1]} {r['us']:.0f}" for k, r in sorted(cands.items()) if k.startswith("stages"))
+            out.append(f"| {sz} | {a['algo']} {'x'.join(map(str, a['widths']))} | {a['us']:.1f} | {a.get('est_us', 0):.1f} | {bk} | {cands[bk]['us']:.1f} | "
+                       f"{ratio:.2f} | {trees} |")
+        out.append("")
+    out += [f"`auto` is within 10 % of the measured best at {good} of {total} (N, size) points. The misses are isolated transients of the row",
+            "measured directly after the NCCL loop (see the note in `sweep_n4_fp32_r2.md`) and the 1 MiB point on 8 GPUs where forced NVLS",
+            "(17.6 us) edges out the two-shot LL (19.4 us). On a uniform NVSwitch fabric every factorization moves the same bytes, so the",
+            "P2P trees differ by hop count (small messages: the flat tree wins, 26 us against 39-53 us at 1 KiB on 8 GPUs) and by fan-in",
+            "(large messages: fewer concurrent peers per stage win - 2x2x2 2970 us, 2x4 3074 us, 4x2 3135 us, flat 3285 us at 1 GiB; at",
+            "256 MiB all four are within 3 %). That is the reference's trade-off (CostModel.h: latency per layer vs incast per width)",
+            "re-measured on NVSwitch; the in-switch reduction beats all of them from 512 KiB up, which is why `auto` rarely lands on a",
+            "multi-stage tree on one box.", ""]
+    open(os.path.join(P, "cost_model_validation_r2.md"), "w").write("\n".join(out) + "\n")
+
+
 if __name__ == "__main__":
     nvls_limit()
     link_probe()
@@ -364,4 +411,5 @@ if __name__ == "__main__":
             sweep(n, dt)
     wire()
     odd_world()
+    cost_model_validation()
     print("profiles written")
