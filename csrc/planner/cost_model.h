@@ -58,8 +58,10 @@ struct LinkModel {
   double alpha_ll_us = 3.63;      // one LL (data+flag) hop
   double alpha_nvls_us = 5.3;     // extra fixed cost of the NVLS path on top of its three flag hops
   // bandwidths, GB/s
-  double beta_p2p_GBps = 616.0;        // TMA-staged pull bandwidth with >= fanin_knee concurrent peers
-  double beta_p2p_1peer_GBps = 615.0;  // ... from a single peer
+  // TMA-staged pull bandwidth. Round-2 fit (profiles/cost_model_validation_r2.md, 1 GiB on 8 GPUs): the flat tree pulls from 7
+  // peers at once and reaches 572 GB/s, 2x2x2 pulls from one peer per stage and reaches 633 GB/s (2 GPUs: 627, 4 GPUs: 629-637)
+  double beta_p2p_GBps = 575.0;        // ... with >= fanin_knee concurrent peers
+  double beta_p2p_1peer_GBps = 635.0;  // ... from a single peer
   int fanin_knee = 7;
   double beta_nvls_GBps = 539.0;  // link rate of multimem ld_reduce/st: bytes = (1 + 1/N) * S
   double beta_ll_GBps = 400.0;    // LL: rate at which the N-1 peer copies are pushed/polled (two-pass kernel) ...
