@@ -104,7 +104,7 @@ def main():
     comm.set_widths(None)
 
     # 2. one-shot, ring, (NVLS), auto
-    algos = ["oneshot", "ring", "auto"] + (["nvls"] if comm.has_multicast else [])
+    algos = ["oneshot", "twoshot", "ring", "auto"] + (["nvls"] if comm.has_multicast else [])
     for algo in algos:
         comm.set_algo(algo)
         for count in (3, 2048, 100000):
@@ -116,6 +116,17 @@ def main():
             ref = exact_sum(x)
             comm.allreduce(x)
             check(x, ref, 1e-5, f"{algo} count {count}")
+    comm.set_algo("twoshot")   # several CTAs, ragged blocks, out of place + fused scale, bf16
+    for count in (262144 + 3, 1 << 20):
+        x = torch.randn(count, device=dev, generator=g)
+        ref = exact_sum(x)
+        out = torch.zeros_like(x)
+        comm.allreduce(x, out=out, scale=0.5)
+        check(out, ref * 0.5, 1e-5, f"twoshot count {count} out of place, scaled")
+        xb = x.bfloat16()
+        rb = exact_sum(xb)
+        comm.allreduce(xb)
+        check(xb, rb, 3e-2, f"twoshot count {count} bf16")
     comm.set_algo("auto")
 
     # 3. dtypes / ops
