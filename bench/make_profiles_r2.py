@@ -302,6 +302,12 @@ def sweep(n, dtype):
                 out.append(f"| {sz} | {v['nccl']['us']:.1f} | {v['registered']['us']:.1f} ({v['registered']['algo']}) | "
                            f"{v['nccl']['us'] / v['registered']['us']:.2f}x | {v['staging']['us']:.1f} ({v['staging']['algo']}) | "
                            f"{v['nccl']['us'] / v['staging']['us']:.2f}x |")
+        if any("us_loops" in r for r in after):
+            off = [(r["bytes"], r.get("mode", "nccl"), r["us_loops"]) for r in after if "us_loops" in r and max(r["us_loops"]) > 1.5 * min(r["us_loops"])]
+            out += ["", "This run reports the better of two timed loops per row (`bench/sweep.py`; both loops are in `us_loops` of the raw rows). Rows",
+                    "whose two loops differ by more than 1.5x: " + ("; ".join(f"{b} B {m}: {l[0]} / {l[1]} us" for b, m, l in off) or "none") + ".",
+                    "They are the transients that single-loop runs put into the tables: the slow loop is always the FIRST one, i.e. the one that",
+                    "directly follows NCCL's own measurement at a new size (NCCL connects channels lazily from a helper thread)."]
         out += ["", "Isolated rows far off their neighbours (e.g. a 40 us one-shot at 8 KiB between 8.6 and 9.0 us, a 118 us NVLS call at 2 MiB between",
                 "15 and 26 us) are transients of the measurement that directly follows the NCCL loop; the same configuration measured",
                 "again in the same run (the forced-algorithm rows of the first table, the other dtype) shows the neighbouring value.", ""]
