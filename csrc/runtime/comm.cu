@@ -1245,8 +1245,10 @@ ft_result_t ft_comm_destroy(ft_comm_t* c) {
   cudaSetDevice(c->device);
   cudaDeviceSynchronize();
   host_pipe_release(c);
-  phantom_release(c);
+  // every rank has drained its device before anybody unmaps anything: a staging-mode kernel ends without an exit
+  // barrier (the next call's window parity protects it), so a peer may still be pulling from my windows right now
   if (c->kind == COMM_PROCESS) c->bs.barrier();
+  phantom_release(c);
   destroy_segments(&c->win);
   destroy_segments(&c->pad);
   destroy_segments(&c->ll);
