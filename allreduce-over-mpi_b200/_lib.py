@@ -111,6 +111,7 @@ def _declare(L):
     sig("ft_predict_us", dbl, [vp, i32, pi32, i32, i32, dbl, i32])
     sig("ft_choose", i32, [vp, i32, dbl, i32, pi32, pi32, i32, C.POINTER(dbl)])
     sig("ft_parse_topo", i32, [cp, i32, pi32, i32])
+    sig("ft_parse_topo_ex", i32, [cp, i32, pi32, i32, pi32, pi32])
     # CPU world
     sig("ft_host_world_create", vp, [i32, C.c_size_t, C.c_size_t])
     sig("ft_host_world_destroy", None, [vp])

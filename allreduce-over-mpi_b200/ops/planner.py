@@ -11,7 +11,7 @@ from .. import _lib
 
 __all__ = ["count_factorizations", "enumerate_widths", "candidates", "prime_factors", "is_prime",
            "is_prime_legacy", "legacy_cost", "legacy_choose", "plan_traffic", "print_ops", "LinkModel",
-           "parse_topo", "format_widths", "version"]
+           "parse_topo", "parse_topo_ex", "format_widths", "version"]
 
 
 def _arr(ws):
@@ -118,6 +118,17 @@ def parse_topo(text, nranks):
     if k < 0:
         raise ValueError(_lib.load().ft_last_error().decode())
     return list(buf[:k])
+
+
+def parse_topo_ex(text, nranks):
+    """FT_TOPO with the tree-size suffixes: '2,3+1' (one lonely rank), '2,4-1' (one phantom position).
+    Returns (widths, lonely, phantoms)."""
+    buf = (C.c_int * 64)()
+    lonely, phantoms = C.c_int(0), C.c_int(0)
+    k = _lib.load().ft_parse_topo_ex(None if text is None else text.encode(), nranks, buf, 64, C.byref(lonely), C.byref(phantoms))
+    if k < 0:
+        raise ValueError(_lib.load().ft_last_error().decode())
+    return list(buf[:k]), lonely.value, phantoms.value
 
 
 class LinkModel:

@@ -160,4 +160,30 @@ int ft_parse_topo(const char* text, int nranks, int* widths_out, int cap) {
   return (int)w.size();
 }
 
+// FT_TOPO with the tree-size suffixes: "2,3+1" = a tree of 6 plus one lonely rank, "2,4-1" = a tree of 8 positions of
+// which one is a phantom (the notation of the reference's tree listings, cost_model/PrintTreeStructure.h:20-53; its
+// own parser, mpi_mod.hpp:882-929, has no syntax for them). lonely_out / phantoms_out receive k (0 for a ring).
+int ft_parse_topo_ex(const char* text, int nranks, int* widths_out, int cap, int* lonely_out, int* phantoms_out) {
+  std::string s = text ? text : (getenv("FT_TOPO") ? getenv("FT_TOPO") : "");
+  int lonely = 0, phantoms = 0;
+  const size_t plus = s.find('+'), minus = s.find('-');
+  if (plus != std::string::npos) {
+    lonely = atoi(s.c_str() + plus + 1);
+    s = s.substr(0, plus);
+    if (lonely <= 0) { set_last_error("invalid FT_TOPO: '+k' needs k >= 1"); return -1; }
+  } else if (minus != std::string::npos) {
+    phantoms = atoi(s.c_str() + minus + 1);
+    s = s.substr(0, minus);
+    if (phantoms <= 0) { set_last_error("invalid FT_TOPO: '-k' needs k >= 1"); return -1; }
+  }
+  const int tree = nranks - lonely + phantoms;
+  if (tree < 1) { set_last_error("invalid FT_TOPO: more lonely ranks than ranks"); return -1; }
+  const int k = ft_parse_topo(s.c_str(), tree, widths_out, cap);
+  if (k < 0) return -1;
+  const bool ring = k == 1 && widths_out[0] == 1 && nranks > 1;
+  if (lonely_out) *lonely_out = ring ? 0 : lonely;
+  if (phantoms_out) *phantoms_out = ring ? 0 : phantoms;
+  return k;
+}
+
 }  // extern "C"

@@ -605,26 +605,12 @@ ft_result_t do_allreduce(ft_comm* c, const void* const* send, void* const* recv,
   int lonely = widths.empty() ? 0 : c->lonely_override;
   int phantoms = widths.empty() ? 0 : c->phantom_override;
   if (widths.empty() && getenv("FT_TOPO") && *getenv("FT_TOPO")) {
-    // "2,3+1": a tree of 6 plus one lonely rank (extension; the reference's parser has no lonely syntax)
-    std::string topo = getenv("FT_TOPO");
-    size_t plus = topo.find('+'), minus = topo.find('-');
-    int extra = 0;
-    if (plus != std::string::npos) {
-      extra = atoi(topo.c_str() + plus + 1);
-      topo = topo.substr(0, plus);
-    } else if (minus != std::string::npos) {  // "2,4-1": a tree of 8 positions for 7 ranks (the reference prints 2*4-1)
-      extra = -atoi(topo.c_str() + minus + 1);
-      topo = topo.substr(0, minus);
-    }
+    // "2,3+1": a tree of 6 plus one lonely rank, "2,4-1": a tree of 8 positions for 7 ranks (extensions; the reference's
+    // parser has neither syntax). A product mismatch is an error: the reference exits (mpi_mod.hpp:914-918).
     int buf[FT_MAX_STAGES + 8];
-    int k = ft_parse_topo(topo.c_str(), N - extra, buf, FT_MAX_STAGES + 8);
-    if (k < 0) return FT_ERR_INVALID;  // product mismatch: the reference exits (mpi_mod.hpp:914-918)
+    const int k = ft_parse_topo_ex(nullptr, N, buf, FT_MAX_STAGES + 8, &lonely, &phantoms);
+    if (k < 0) return FT_ERR_INVALID;
     widths.assign(buf, buf + k);
-    if (extra < 0) {
-      phantoms = (k == 1 && buf[0] == 1) ? 0 : -extra;
-      extra = 0;
-    }
-    lonely = (k == 1 && buf[0] == 1) ? 0 : extra;
   }
   if (phantoms > 0) {
     if (phases != PHASES_ALLREDUCE || c->kind != COMM_PROCESS || phantoms > N) {

@@ -104,6 +104,9 @@ int ft_choose(const ft_link_model_t*, int nranks, double bytes, int registered, 
 /* FT_TOPO semantics of the reference (mpi_mod.hpp:882-929): unset/empty -> {n}; any 1 -> ring ({1});
  * product != n -> error. text may be NULL to read the environment. Returns nstages or -1. */
 int ft_parse_topo(const char* text, int nranks, int* widths_out, int cap);
+/* The same with the tree-size suffixes of the reference's listings (PrintTreeStructure.h: "a*b+1", "a*b-1"):
+ * "2,3+1" = tree of nranks-1 plus one lonely rank, "2,4-1" = tree of nranks+1 with one phantom position. */
+int ft_parse_topo_ex(const char* text, int nranks, int* widths_out, int cap, int* lonely_out, int* phantoms_out);
 
 /* ------------------------------------------------------------------------------------------------
  * Communicators

@@ -657,3 +657,33 @@ def test_cluster_pair_per_tile_matches_reference(comms, n, widths):
         c.set_tma(None)
         c.set_widths(None)
         c.set_algo("auto")
+
+
+def test_ft_topo_environment_forms(monkeypatch):
+    """FT_TOPO as the reference reads it (mpi_mod.hpp:882-929) plus the tree-size suffixes: widths, ring, a lonely rank
+    ('2,3+1' on 7 ranks), errors for a wrong product and for a phantom tree on a communicator that cannot host one."""
+    n, count = 7, 20000
+    c = ft.Communicator.emulated(n, 0, window_bytes=1 << 20)
+    try:
+        xs = [torch.full((count,), float(r + 1), device="cuda") for r in range(n)]
+        want = float(sum(range(1, n + 1)))
+        for topo, algo, widths in (("7", "stages", [7]), ("2,3+1", "stages", [2, 3]), ("1", "ring", [7]), ("", None, None)):
+            monkeypatch.setenv("FT_TOPO", topo)
+            c.set_algo("auto")              # bumps the plan generation: FT_TOPO is read when a plan is built
+            ys = [x.clone() for x in xs]
+            c.allreduce_multi(ys)
+            torch.cuda.synchronize()
+            assert c.error() == 0
+            for y in ys:
+                assert torch.all(y == want), topo
+            if algo:
+                info = c.last_call()
+                assert info["algo"] == algo and info["widths"] == widths, (topo, info)
+        for bad in ("2,3", "2,4-1"):        # product != 7; '-k' trees need one process per GPU
+            monkeypatch.setenv("FT_TOPO", bad)
+            c.set_algo("auto")
+            with pytest.raises(ft.FlexTreeError):
+                c.allreduce_multi([x.clone() for x in xs])
+    finally:
+        monkeypatch.delenv("FT_TOPO", raising=False)
+        c.close()

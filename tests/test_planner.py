@@ -240,3 +240,18 @@ def test_compiled_fast_path_module():
     assert mod.error_peek(0) == 0
     with pytest.raises(TypeError):
         mod.allreduce_ex(0, 0)
+
+
+def test_parse_topo_tree_size_suffixes():
+    """'2,3+1' (a tree of N-1 plus one lonely rank) and '2,4-1' (a tree of N+1 with one phantom position): the notation of
+    the reference's tree listings (cost_model/PrintTreeStructure.h), accepted by FT_TOPO."""
+    assert ft.parse_topo_ex("2,3", 6) == ([2, 3], 0, 0)
+    assert ft.parse_topo_ex("2,3+1", 7) == ([2, 3], 1, 0)
+    assert ft.parse_topo_ex("2 4-1", 7) == ([2, 4], 0, 1)
+    assert ft.parse_topo_ex("2,2,2-1", 7) == ([2, 2, 2], 0, 1)
+    assert ft.parse_topo_ex("3-1", 2) == ([3], 0, 1)
+    assert ft.parse_topo_ex("", 5) == ([5], 0, 0)
+    assert ft.parse_topo_ex("1", 7) == ([1], 0, 0)            # ring: no tree, no suffix meaning
+    for bad, n in (("2,3+1", 6), ("2,4-1", 8), ("2,3+0", 6), ("2,3-0", 6), ("2,3+9", 7)):
+        with pytest.raises(ValueError):
+            ft.parse_topo_ex(bad, n)
