@@ -14,6 +14,7 @@
 #include <chrono>
 #include <string>
 
+#include "../../include/flextree.h"
 #include "../planner/cost_model.h"
 #include "../planner/factorize.h"
 #include "../planner/schedule.h"
@@ -25,7 +26,7 @@ static void usage() {
   fprintf(stderr,
           "ft_plan --count N | --enumerate N [--legacy-flat] | --candidates N | --legacy N [--chunk C]\n"
           "        | --print-ops --widths a,b,c --rank r [--lonely k] | --sweep [--max N] [--chunk C] [--out file]\n"
-          "        | --choose N --bytes S [--nvls] [--registered] [--model file.json] | --version\n");
+          "        | --choose N --bytes S [--nvls] [--registered] [--model file.json] | --topo TEXT --ranks N | --version\n");
 }
 
 int main(int argc, char** argv) {
@@ -39,6 +40,8 @@ int main(int argc, char** argv) {
     if (a == "--count" || a == "--enumerate" || a == "--candidates" || a == "--legacy" || a == "--choose") { mode = a; n = atoi(val()); }
     else if (a == "--print-ops" || a == "--sweep" || a == "--version") mode = a;
     else if (a == "--widths") widths_s = val();
+    else if (a == "--topo") { mode = a; widths_s = val(); }
+    else if (a == "--ranks") n = atoi(val());
     else if (a == "--rank") rank = atoi(val());
     else if (a == "--lonely") lonely = atoi(val());
     else if (a == "--chunk") chunk = atof(val());
@@ -52,6 +55,15 @@ int main(int argc, char** argv) {
     else { usage(); return 1; }
   }
   if (mode == "--version") { printf("%s\n", FT_VERSION_STRING); return 0; }
+  if (mode == "--topo") {  // how FT_TOPO=TEXT is read on N ranks (incl. the '+k' lonely / '-k' phantom suffixes)
+    int w[64], lone = 0, ph = 0;
+    const int k = ft_parse_topo_ex(widths_s.c_str(), n, w, 64, &lone, &ph);
+    if (k < 0) { fprintf(stderr, "%s\n", ft_last_error()); return 1; }
+    Widths ws(w, w + k);
+    if (k == 1 && w[0] == 1 && n > 1) printf("ring over %d ranks\n", n);
+    else printf("tree %s: %d positions on %d ranks, %d lonely, %d phantom\n", to_string(ws, lone ? lone : -ph).c_str(), n - lone + ph, n, lone, ph);
+    return 0;
+  }
   if (mode == "--count") { printf("%llu\n", (unsigned long long)count_factorizations((uint64_t)n)); return 0; }
   if (mode == "--enumerate") {
     for (auto& w : enumerate_widths(n, legacy_flat)) printf("%s\n", to_string(w).c_str());

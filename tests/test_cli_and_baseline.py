@@ -127,3 +127,16 @@ def test_ftrun_launcher_and_env_bootstrap(tmp_path):
     p = subprocess.run([os.path.join(ROOT, "build", "ftrun"), "-np", "2", "sh", "-c", "test $FT_RANK = 0 || exit 7; sleep 30"],
                        capture_output=True, text=True, timeout=60)
     assert p.returncode == 7
+
+
+def test_ft_plan_topo_mode():
+    """`ft_plan --topo TEXT --ranks N`: how FT_TOPO is read, incl. the '+k' / '-k' suffixes of the reference's listings."""
+    exe = os.path.join(ROOT, "build", "ft_plan")
+    if not os.path.exists(exe):
+        pytest.skip("ft_plan not built")
+    run = lambda *a: subprocess.run([exe, *a], capture_output=True, text=True)
+    assert run("--topo", "2,4-1", "--ranks", "7").stdout.strip() == "tree 2*4-1: 8 positions on 7 ranks, 0 lonely, 1 phantom"
+    assert run("--topo", "2 3+1", "--ranks", "7").stdout.strip() == "tree 2*3+1: 6 positions on 7 ranks, 1 lonely, 0 phantom"
+    assert run("--topo", "1", "--ranks", "5").stdout.strip() == "ring over 5 ranks"
+    bad = run("--topo", "2,3", "--ranks", "7")
+    assert bad.returncode == 1 and "invalid FT_TOPO" in bad.stderr
